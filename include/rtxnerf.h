@@ -1,0 +1,170 @@
+/*
+ * rtxnerf.h — C ABI of the B200-native rtx_nerf per-ray hot path (librtxnerf_b200.so).
+ *
+ * Drop-in boundary for owensgroup/rtx_nerf's sampler/, vol_render/ and rtx/ entry points.
+ * Every entry point cites the reference interface it replaces (paths relative to the
+ * reference checkout).  Conventions, unlike the reference's void launchers
+ * (SURVEY §8b "Errors"):
+ *   - every function returns int: 0 = RTXNERF_OK, >0 = a cudaError_t value,
+ *     <0 = an RTXNERF_E* argument error; nothing throws, exits or prints;
+ *   - all buffers are CALLER-OWNED raw device pointers unless a name ends in _host;
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream, which is
+ *     what vol_render.cu:155,179 launch on);
+ *   - launches are asynchronous on `stream`; nothing synchronises unless stated.
+ * The C++ shim headers in rtx_nerf_b200/compat/ re-expose the reference's exact C++
+ * signatures on top of this ABI so main.cu links unchanged.
+ */
+#ifndef RTXNERF_H
+#define RTXNERF_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RTXNERF_ABI_VERSION 1
+
+enum {
+    RTXNERF_OK = 0,
+    RTXNERF_EINVAL = -1,   /* null pointer / bad size */
+    RTXNERF_EGRID = -2,    /* grid resolution not a power of two in [2, 1024] */
+    RTXNERF_ECAPACITY = -3,/* caller-provided capacity too small */
+    RTXNERF_ENOMEM = -4,
+    RTXNERF_ECONFIG = -5   /* unsupported network / encoding configuration */
+};
+
+int rtxnerf_abi_version(void);
+/* Static string for a code returned by this library (CUDA codes map to cudaGetErrorString). */
+const char* rtxnerf_error_string(int code);
+
+/* ------------------------------------------------------------------------------------
+ * Occupancy grid — replaces RTXDataHolder::initAccelerationStructure
+ * (rtx/include/rtxFunctions.h:89, rtx/src/rtxFunctions.cpp:293-351) and make_grid
+ * (main.cu:154-174).  A cell p = (x*G+y)*G+z is "occupied" iff it would be an AABB
+ * primitive in the reference's GAS.  Bounds are make_grid's: min = -1 + i*(2/G).
+ * ---------------------------------------------------------------------------------- */
+typedef struct rtxnerf_grid rtxnerf_grid;
+
+/* occ_bits_host: G^3 bits, bit (p & 31) of word (p >> 5).  Synchronous (uploads). */
+int rtxnerf_grid_create(const uint32_t* occ_bits_host, int G, rtxnerf_grid** out);
+/* From the reference's own primitive list: n AABBs {minX,minY,minZ,maxX,maxY,maxZ} on the
+ * host (std::vector<OptixAabb>, main.cu:396-399); each must be a make_grid(G) cell. */
+int rtxnerf_grid_create_from_aabbs(const float* aabb6_host, int n_prims, int G, rtxnerf_grid** out);
+/* Re-upload the occupancy bits (device-side rebuild of the skip hierarchy), async. */
+int rtxnerf_grid_update(rtxnerf_grid* g, const uint32_t* occ_bits_host, void* stream);
+int rtxnerf_grid_destroy(rtxnerf_grid* g);
+int rtxnerf_grid_resolution(const rtxnerf_grid* g);
+/* Device AABB array of all G^3 make_grid cells (what initAccelerationStructure returns and
+ * main.cu:399,492 stores in Params.aabb); built lazily, owned by the grid. */
+int rtxnerf_grid_device_aabbs(rtxnerf_grid* g, float** d_aabb6_out);
+
+/* ------------------------------------------------------------------------------------
+ * Ray march — replaces optixLaunch(pipeline_ray_march, ...) (main.cu:506-508) and the
+ * device programs rtx/src/optixPrograms.cu:43-248.
+ * ---------------------------------------------------------------------------------- */
+
+/* Mirror of `struct Params` (rtx/include/params.h:14-42): same field order, OptiX types
+ * replaced by plain ones (OptixTraversableHandle -> uint64, OptixAabb* -> float*,
+ * float3 -> float[3], float2* / float3* -> float*).  Same size and offsets on LP64. */
+typedef struct rtxnerf_params {
+    uint64_t handle;            /* (uint64_t)(rtxnerf_grid*) — OptixTraversableHandle slot */
+    float* look_at;             /* device, 4x4 row-major pose */
+    int num_primitives;
+    int intersection_arr_size;  /* slots per ray (3*G at main.cu:486) */
+    float* aabb;                /* unused by the new kernels (grid handle carries geometry) */
+    float* start_points;        /* [W*H][arr][3] */
+    float* end_points;          /* [W*H][arr][3] */
+    float* ray_origins;         /* [W*H][3] */
+    float* t_start;             /* [W*H][arr] */
+    float* t_end;               /* [W*H][arr] */
+    int* num_hits;              /* [W*H] */
+    float* viewing_direction;   /* [W*H][2] (theta, phi) */
+    float focal_length;
+    float aspect_ratio;
+    float delta[3];
+    float min_point[3];
+    float max_point[3];
+    unsigned int width, height;
+} rtxnerf_params;
+
+/* Dense layout exactly as the reference writes it: hit j of ray r at slot
+ * r*intersection_arr_size + j (optixPrograms.cu:184).  Unlike the reference (Q11) a ray
+ * stops after intersection_arr_size hits.  `params_host` is read on the host. */
+int rtxnerf_ray_march_dense(const rtxnerf_params* params_host, void* stream);
+
+/* Camera block for the CSR entry points (the Params scalars + pose). */
+typedef struct rtxnerf_camera {
+    const float* look_at;   /* device, 16 floats row-major */
+    float focal_length;
+    float aspect_ratio;
+    unsigned int width, height;
+} rtxnerf_camera;
+
+/* CSR hit records of rays [ray_begin, ray_begin + n_rays) of one view; all arrays are
+ * indexed by LOCAL ray (ray - ray_begin) / local hit slot.  Replaces the dense buffers +
+ * thrust reduce/exclusive_scan + host gather of main.cu:517-543,631-676. */
+typedef struct rtxnerf_hits {
+    int* num_hits;        /* [n_rays]        optixPrograms.cu:241 */
+    int* indices;         /* [n_rays]        exclusive scan of num_hits (main.cu:634-637) */
+    float* view_dirs;     /* [n_rays][2]     optixPrograms.cu:71-73 */
+    float* ray_origins;   /* [n_rays][3]     optixPrograms.cu:75-82 (may be NULL) */
+    float* t_start;       /* [capacity]      (may be NULL) */
+    float* t_end;         /* [capacity]      (may be NULL) */
+    float* start_points;  /* [capacity][3] */
+    float* end_points;    /* [capacity][3] */
+    int* hit_cells;       /* [capacity]      primitive index (x*G+y)*G+z (may be NULL) */
+    long long* total_hits;/* [1] device: sum of num_hits */
+    long long capacity;   /* hit slots available in the arrays above */
+} rtxnerf_hits;
+
+/* Bytes of device scratch rtxnerf_ray_march_csr needs for n_rays. */
+size_t rtxnerf_ray_march_workspace_bytes(long long n_rays);
+
+/* count -> scan -> fill, all on `stream`.  max_hits caps hits per ray (H_max).  Hits
+ * beyond `capacity` are dropped and *total_hits still reports the true total, so the
+ * caller can detect overflow; rays are never split. */
+int rtxnerf_ray_march_csr(const rtxnerf_grid* grid, const rtxnerf_camera* cam,
+                          long long ray_begin, long long n_rays, int max_hits,
+                          const rtxnerf_hits* hits, void* workspace, size_t workspace_bytes,
+                          void* stream);
+
+/* ------------------------------------------------------------------------------------
+ * Sampler — replaces launchSampler (sampler/sampler.h:19-30, sampler/sampler.cu:105-131).
+ * samples_per_segment is the reference's NUM_SAMPLES_PER_SEGMENT (sampler.h:4, 32) made a
+ * run-time value.  sample_type: 0 REGULAR, 1 STRATIFIED_JITTERING, 2 UNIFORM (sampler.h:5-9).
+ * ---------------------------------------------------------------------------------- */
+int rtxnerf_launch_sampler(const float* d_start_points, const float* d_end_points,
+                           const float* d_view_dirs, float* d_t_vals, float* d_sampled_points,
+                           int batch_size, int grid_res, const int* d_num_hits,
+                           const int* d_indices, int sample_type, int samples_per_segment,
+                           void* stream);
+
+/* ------------------------------------------------------------------------------------
+ * Volume rendering — replaces launch_volrender_cuda / launch_volrender_backward_cuda
+ * (vol_render/vol_render.h:5-25, vol_render/vol_render.cu:144-190).  __half buffers are
+ * passed as uint16_t* (IEEE binary16 bits).  network_inputs / loss_values are accepted
+ * and ignored, as in the reference.
+ * ---------------------------------------------------------------------------------- */
+int rtxnerf_launch_volrender(const float* network_inputs, const float* network_outputs,
+                             const int* num_hits, const int* indices, const float* ray_hit,
+                             int batch_size, int num_samples_per_hit, float* pixels, void* stream);
+
+int rtxnerf_launch_volrender_backward(const float* loss_values, const uint16_t* loss_gradients,
+                                      const float* sampled_points_radiance, const float* t_hit,
+                                      const int* num_hits, const int* indices, int batch_size,
+                                      int num_samples_per_hit, uint16_t* radiance_gradients,
+                                      void* stream);
+
+/* Config-1 stand-in for the network (BASELINE.json configs[0]): every sample takes the
+ * fixed (r,g,b,sigma) of the cell its segment lies in.  n_hits is read from the device
+ * scalar d_total_hits; at most capacity_hits segments are processed. */
+int rtxnerf_cell_radiance(const int* d_hit_cells, const long long* d_total_hits,
+                          long long capacity_hits, int samples_per_segment,
+                          const float* d_cell_rgbs4, float* d_radiance, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RTXNERF_H */

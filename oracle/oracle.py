@@ -1,0 +1,347 @@
+"""numpy front-end of the CPU oracle (TEST INFRASTRUCTURE ONLY).
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs
+may import this module.  It loads oracle/liboracle.so (our C restatement) and, when
+present, oracle/_ref/libref_host.so (the reference's own sources compiled for the host).
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+_f32p = C.POINTER(C.c_float)
+_i32p = C.POINTER(C.c_int)
+_u16p = C.POINTER(C.c_uint16)
+_u8p = C.POINTER(C.c_uint8)
+
+
+class _MarchOut(C.Structure):
+    _fields_ = [("t_start", _f32p), ("t_end", _f32p), ("start_points", _f32p), ("end_points", _f32p),
+                ("hit_prims", _i32p), ("num_hits", _i32p), ("view_dirs", _f32p), ("ray_origins", _f32p),
+                ("indices", _i32p), ("arr_size", C.c_int), ("max_hits", C.c_int)]
+
+
+class _HashCfg(C.Structure):
+    _fields_ = [("n_levels", C.c_int), ("n_features", C.c_int), ("log2_hashmap_size", C.c_int),
+                ("base_resolution", C.c_int), ("per_level_scale", C.c_float)]
+
+
+def _ptr(a, typ):
+    return None if a is None else a.ctypes.data_as(typ)
+
+
+_lib = None
+_ref = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        path = os.path.join(HERE, "liboracle.so")
+        if not os.path.exists(path):
+            import importlib.util
+            spec = importlib.util.spec_from_file_location("oracle_build", os.path.join(HERE, "build.py"))
+            m = importlib.util.module_from_spec(spec)
+            spec.loader.exec_module(m)
+            m.build_oracle()
+        _lib = C.CDLL(path)
+        _lib.orc_exclusive_scan.restype = C.c_longlong
+        _lib.orc_hashgrid_offsets.restype = C.c_longlong
+        _lib.orc_f2h.restype = C.c_uint16
+        _lib.orc_h2f.restype = C.c_float
+        _lib.orc_h2f.argtypes = [C.c_uint16]
+        _lib.orc_f2h.argtypes = [C.c_float]
+    return _lib
+
+
+def ref_host():
+    """The reference's own code compiled for the host, or None when not built."""
+    global _ref
+    if _ref is None:
+        path = os.path.join(HERE, "_ref", "libref_host.so")
+        if not os.path.exists(path):
+            return None
+        _ref = C.CDLL(path)
+    return _ref
+
+
+def default_threads():
+    return os.cpu_count() or 1
+
+
+# --------------------------------------------------------------------------- grid / rays
+def make_grid(G):
+    aabb = np.empty((G ** 3, 6), np.float32)
+    lib().orc_make_grid(C.c_int(G), _ptr(aabb, _f32p))
+    return aabb
+
+
+def raygen(look_at, focal, aspect, W, H, x, y):
+    look_at = np.ascontiguousarray(look_at, np.float32).reshape(16)
+    o = np.empty(3, np.float32)
+    d = np.empty(3, np.float32)
+    vd = np.empty(2, np.float32)
+    lib().orc_raygen(_ptr(look_at, _f32p), C.c_float(focal), C.c_float(aspect), C.c_uint(W), C.c_uint(H),
+                     C.c_uint(x), C.c_uint(y), _ptr(o, _f32p), _ptr(d, _f32p), _ptr(vd, _f32p))
+    return o, d, vd
+
+
+class MarchResult:
+    """Hit records of one view.  Dense ([R][arr_size]) or CSR (indices set)."""
+
+    def __init__(self, R, slots, indices=None, arr_size=0, max_hits=0, want_records=True):
+        self.num_hits = np.zeros(R, np.int32)
+        self.view_dirs = np.empty((R, 2), np.float32)
+        self.ray_origins = np.empty((R, 3), np.float32)
+        self.indices = indices
+        self.arr_size = arr_size
+        self.max_hits = max_hits
+        if want_records:
+            self.t_start = np.full(slots, np.nan, np.float32)
+            self.t_end = np.full(slots, np.nan, np.float32)
+            self.start_points = np.full((slots, 3), np.nan, np.float32)
+            self.end_points = np.full((slots, 3), np.nan, np.float32)
+            self.hit_prims = np.full(slots, -1, np.int32)
+        else:
+            self.t_start = self.t_end = self.start_points = self.end_points = self.hit_prims = None
+        self.capped = 0
+
+    def c_struct(self):
+        return _MarchOut(_ptr(self.t_start, _f32p), _ptr(self.t_end, _f32p), _ptr(self.start_points, _f32p),
+                         _ptr(self.end_points, _f32p), _ptr(self.hit_prims, _i32p), _ptr(self.num_hits, _i32p),
+                         _ptr(self.view_dirs, _f32p), _ptr(self.ray_origins, _f32p),
+                         _ptr(self.indices, _i32p), self.arr_size, self.max_hits)
+
+
+def _march(fn, look_at, focal, aspect, W, H, geom_args, arr_size, max_hits, csr, rays, nthreads):
+    look_at = np.ascontiguousarray(look_at, np.float32).reshape(16)
+    R = W * H
+    rb, re = rays if rays is not None else (0, R)
+    nthreads = nthreads or default_threads()
+    cap = max_hits if max_hits > 0 else arr_size
+
+    def call(res):
+        st = res.c_struct()
+        rc = fn(_ptr(look_at, _f32p), C.c_float(focal), C.c_float(aspect), C.c_uint(W), C.c_uint(H),
+                *geom_args, C.c_uint(rb), C.c_uint(re), C.byref(st), C.c_int(nthreads))
+        if rc < 0:
+            raise ValueError("oracle march refused the grid (rc=%d)" % rc)
+        res.capped = rc
+        return res
+
+    if not csr:
+        return call(MarchResult(R, R * arr_size, None, arr_size, cap))
+    counts = call(MarchResult(R, 0, None, arr_size, cap, want_records=False))
+    indices = np.zeros(R, np.int32)
+    total = lib().orc_exclusive_scan(_ptr(counts.num_hits, _i32p), C.c_int(R), _ptr(indices, _i32p))
+    res = MarchResult(R, int(total), indices, arr_size, cap)
+    call(res)
+    res.total_hits = int(total)
+    return res
+
+
+def ray_march_brute(look_at, focal, aspect, W, H, aabb, prim_ids=None, arr_size=None, max_hits=0,
+                    csr=False, rays=None, nthreads=None):
+    """optixPrograms.cu:43-248 with every relaunch testing all primitives."""
+    aabb = np.ascontiguousarray(aabb, np.float32).reshape(-1, 6)
+    assert arr_size is not None, "arr_size (slots per ray) is required"
+    if prim_ids is not None:
+        prim_ids = np.ascontiguousarray(prim_ids, np.int32)
+    geom = (_ptr(aabb, _f32p), _ptr(prim_ids, _i32p), C.c_int(aabb.shape[0]))
+    return _march(lib().orc_ray_march_brute, look_at, focal, aspect, W, H, geom, arr_size, max_hits, csr,
+                  rays, nthreads)
+
+
+def ray_march_dda(look_at, focal, aspect, W, H, occ, G, arr_size=None, max_hits=0, csr=False, rays=None,
+                  nthreads=None):
+    """Same results by the exact interval sweep; occ = uint8 [G^3]."""
+    occ = np.ascontiguousarray(occ, np.uint8).reshape(-1)
+    assert occ.size == G ** 3
+    if arr_size is None:
+        arr_size = 3 * G
+    geom = (_ptr(occ, _u8p), C.c_int(G))
+    return _march(lib().orc_ray_march_dda, look_at, focal, aspect, W, H, geom, arr_size, max_hits, csr,
+                  rays, nthreads)
+
+
+def exclusive_scan(num_hits):
+    num_hits = np.ascontiguousarray(num_hits, np.int32)
+    idx = np.empty_like(num_hits)
+    total = lib().orc_exclusive_scan(_ptr(num_hits, _i32p), C.c_int(num_hits.size), _ptr(idx, _i32p))
+    return idx, int(total)
+
+
+def compact_hits(num_hits, indices, arr_size, dense, comps):
+    dense = np.ascontiguousarray(dense, np.float32)
+    total = int(num_hits.sum())
+    out = np.empty((total, comps) if comps > 1 else total, np.float32)
+    lib().orc_compact_hits(_ptr(num_hits, _i32p), _ptr(indices, _i32p), C.c_int(num_hits.size),
+                           C.c_int(arr_size), _ptr(dense, _f32p), C.c_int(comps), _ptr(out, _f32p))
+    return out
+
+
+# --------------------------------------------------------------------------- sampler / compositing
+def sampler(start_points, end_points, view_dirs, num_hits, indices, S=32, sample_type=0, nthreads=None):
+    start_points = np.ascontiguousarray(start_points, np.float32)
+    end_points = np.ascontiguousarray(end_points, np.float32)
+    view_dirs = np.ascontiguousarray(view_dirs, np.float32)
+    num_hits = np.ascontiguousarray(num_hits, np.int32)
+    indices = np.ascontiguousarray(indices, np.int32)
+    N = int(num_hits.sum()) * S
+    samples = np.empty((N, 5), np.float32)
+    t_vals = np.empty(N, np.float32)
+    lib().orc_sampler(_ptr(start_points, _f32p), _ptr(end_points, _f32p), _ptr(view_dirs, _f32p),
+                      _ptr(t_vals, _f32p), _ptr(samples, _f32p), C.c_int(num_hits.size),
+                      _ptr(num_hits, _i32p), _ptr(indices, _i32p), C.c_int(S), C.c_int(sample_type),
+                      C.c_int(nthreads or default_threads()))
+    return samples, t_vals
+
+
+def cell_radiance(hit_prims, S, cell_rgbs):
+    hit_prims = np.ascontiguousarray(hit_prims, np.int32)
+    cell_rgbs = np.ascontiguousarray(cell_rgbs, np.float32)
+    out = np.empty((hit_prims.size * S, 4), np.float32)
+    lib().orc_cell_radiance(_ptr(hit_prims, _i32p), C.c_longlong(hit_prims.size), C.c_int(S),
+                            _ptr(cell_rgbs, _f32p), _ptr(out, _f32p))
+    return out
+
+
+def volrender(radiance, num_hits, indices, t_vals, S, nthreads=None):
+    radiance = np.ascontiguousarray(radiance, np.float32)
+    t_vals = np.ascontiguousarray(t_vals, np.float32)
+    num_hits = np.ascontiguousarray(num_hits, np.int32)
+    indices = np.ascontiguousarray(indices, np.int32)
+    pixels = np.empty((num_hits.size, 3), np.float32)
+    lib().orc_volrender(_ptr(radiance, _f32p), _ptr(num_hits, _i32p), _ptr(indices, _i32p),
+                        _ptr(t_vals, _f32p), C.c_int(num_hits.size), C.c_int(S), _ptr(pixels, _f32p),
+                        C.c_int(nthreads or default_threads()))
+    return pixels
+
+
+def volrender_backward(loss_grad_h, radiance, t_vals, num_hits, indices, S, nthreads=None):
+    """loss_grad_h: float16 [B][3]; returns float16 [N][4]."""
+    lg = np.ascontiguousarray(loss_grad_h, np.float16).view(np.uint16)
+    radiance = np.ascontiguousarray(radiance, np.float32)
+    t_vals = np.ascontiguousarray(t_vals, np.float32)
+    num_hits = np.ascontiguousarray(num_hits, np.int32)
+    indices = np.ascontiguousarray(indices, np.int32)
+    out = np.zeros((t_vals.size, 4), np.uint16)
+    lib().orc_volrender_backward(_ptr(lg, _u16p), _ptr(radiance, _f32p), _ptr(t_vals, _f32p),
+                                 _ptr(num_hits, _i32p), _ptr(indices, _i32p), C.c_int(num_hits.size),
+                                 C.c_int(S), _ptr(out, _u16p), C.c_int(nthreads or default_threads()))
+    return out.view(np.float16)
+
+
+# --------------------------------------------------------------------------- encoding + MLP
+def hashgrid_offsets(n_levels, n_features, log2_hashmap_size, base_resolution, per_level_scale):
+    cfg = _HashCfg(n_levels, n_features, log2_hashmap_size, base_resolution, per_level_scale)
+    off = (C.c_longlong * (n_levels + 1))()
+    total = lib().orc_hashgrid_offsets(C.byref(cfg), off)
+    return np.array(list(off), np.int64), int(total)
+
+
+def hashgrid_geometry(n_levels, n_features, log2_hashmap_size, base_resolution, per_level_scale):
+    cfg = _HashCfg(n_levels, n_features, log2_hashmap_size, base_resolution, per_level_scale)
+    sc = np.empty(n_levels, np.float32)
+    rs = np.empty(n_levels, np.uint32)
+    sz = np.empty(n_levels, np.uint32)
+    lib().orc_hashgrid_geometry(C.byref(cfg), _ptr(sc, _f32p), _ptr(rs, C.POINTER(C.c_uint32)),
+                                _ptr(sz, C.POINTER(C.c_uint32)))
+    return sc, rs, sz
+
+
+def hashgrid_encode(levels, table_h, samples, nthreads=None):
+    """levels: dict from rtx_nerf_b200.synth.hashgrid_levels (scale/res/size/offset arrays)."""
+    L, F = levels["n_levels"], levels["n_features"]
+    sc = np.ascontiguousarray(levels["scale"], np.float32)
+    rs = np.ascontiguousarray(levels["res"], np.uint32)
+    sz = np.ascontiguousarray(levels["size"], np.uint32)
+    off = np.ascontiguousarray(levels["offset"], np.int64)
+    table = np.ascontiguousarray(table_h, np.float16).view(np.uint16)
+    samples = np.ascontiguousarray(samples, np.float32)
+    n = samples.shape[0]
+    out = np.empty((n, L * F), np.uint16)
+    u32p = C.POINTER(C.c_uint32)
+    lib().orc_hashgrid_encode(C.c_int(L), C.c_int(F), _ptr(sc, _f32p), _ptr(rs, u32p), _ptr(sz, u32p),
+                              _ptr(off, C.POINTER(C.c_longlong)), _ptr(table, _u16p), _ptr(samples, _f32p),
+                              C.c_int(samples.shape[1]), C.c_longlong(n), _ptr(out, _u16p),
+                              C.c_int(nthreads or default_threads()))
+    return out.view(np.float16)
+
+
+def mlp_forward(weights_h, in_dim, width, n_hidden, out_activation, x_h, nthreads=None):
+    w = np.ascontiguousarray(weights_h, np.float16).view(np.uint16)
+    x = np.ascontiguousarray(x_h, np.float16).view(np.uint16)
+    n = x.shape[0]
+    out16 = np.empty((n, 16), np.uint16)
+    rad = np.empty((n, 4), np.float32)
+    lib().orc_mlp_forward(_ptr(w, _u16p), C.c_int(in_dim), C.c_int(width), C.c_int(n_hidden),
+                          C.c_int(out_activation), _ptr(x, _u16p), C.c_longlong(n), _ptr(out16, _u16p),
+                          _ptr(rad, _f32p), C.c_int(nthreads or default_threads()))
+    return out16.view(np.float16), rad
+
+
+# --------------------------------------------------------------------------- the reference itself, on the host
+def ref_ray_march(look_at, focal, aspect, W, H, G, aabb, arr_size, rays=None):
+    """The reference's own OptiX programs over the emulated runtime (oracle/host_shim/optix.h)."""
+    r = ref_host()
+    look_at = np.ascontiguousarray(look_at, np.float32).reshape(16)
+    aabb = np.ascontiguousarray(aabb, np.float32).reshape(-1, 6)
+    R = W * H
+    rb, re = rays if rays is not None else (0, R)
+    res = MarchResult(R, R * arr_size, None, arr_size, arr_size)
+    res.hit_prims = None
+    rc = r.ref_optix_ray_march(_ptr(look_at, _f32p), C.c_float(focal), C.c_float(aspect), C.c_uint(W),
+                               C.c_uint(H), C.c_int(G), _ptr(aabb, _f32p), C.c_int(aabb.shape[0]),
+                               C.c_int(arr_size), _ptr(res.t_start, _f32p), _ptr(res.t_end, _f32p),
+                               _ptr(res.start_points, _f32p), _ptr(res.end_points, _f32p),
+                               _ptr(res.num_hits, _i32p), _ptr(res.view_dirs, _f32p),
+                               _ptr(res.ray_origins, _f32p), C.c_uint(rb), C.c_uint(re))
+    res.capped = rc
+    return res
+
+
+def ref_sampler(start_points, end_points, view_dirs, num_hits, indices, sample_type=0, grid_res=0):
+    r = ref_host()
+    S = r.ref_host_samples_per_segment()
+    start_points = np.ascontiguousarray(start_points, np.float32)
+    end_points = np.ascontiguousarray(end_points, np.float32)
+    view_dirs = np.ascontiguousarray(view_dirs, np.float32)
+    num_hits = np.ascontiguousarray(num_hits, np.int32)
+    indices = np.ascontiguousarray(indices, np.int32)
+    N = int(num_hits.sum()) * S
+    samples = np.empty((N, 5), np.float32)
+    t_vals = np.empty(N, np.float32)
+    r.ref_host_launchSampler(_ptr(start_points, _f32p), _ptr(end_points, _f32p), _ptr(view_dirs, _f32p),
+                             _ptr(t_vals, _f32p), _ptr(samples, _f32p), C.c_int(num_hits.size),
+                             C.c_int(grid_res), _ptr(num_hits, _i32p), _ptr(indices, _i32p),
+                             C.c_int(sample_type))
+    return samples, t_vals
+
+
+def ref_volrender(radiance, num_hits, indices, t_vals, S):
+    r = ref_host()
+    radiance = np.ascontiguousarray(radiance, np.float32)
+    t_vals = np.ascontiguousarray(t_vals, np.float32)
+    num_hits = np.ascontiguousarray(num_hits, np.int32)
+    indices = np.ascontiguousarray(indices, np.int32)
+    pixels = np.empty((num_hits.size, 3), np.float32)
+    r.ref_host_volrender(_ptr(radiance, _f32p), _ptr(num_hits, _i32p), _ptr(indices, _i32p),
+                         _ptr(t_vals, _f32p), C.c_int(num_hits.size), C.c_int(S), _ptr(pixels, _f32p))
+    return pixels
+
+
+def ref_volrender_backward(loss_grad_h, radiance, t_vals, num_hits, indices, S):
+    r = ref_host()
+    lg = np.ascontiguousarray(loss_grad_h, np.float16).view(np.uint16)
+    radiance = np.ascontiguousarray(radiance, np.float32)
+    t_vals = np.ascontiguousarray(t_vals, np.float32)
+    num_hits = np.ascontiguousarray(num_hits, np.int32)
+    indices = np.ascontiguousarray(indices, np.int32)
+    out = np.zeros((t_vals.size, 4), np.uint16)
+    r.ref_host_volrender_backward(_ptr(lg, _u16p), _ptr(radiance, _f32p), _ptr(t_vals, _f32p),
+                                  _ptr(num_hits, _i32p), _ptr(indices, _i32p), C.c_int(num_hits.size),
+                                  C.c_int(S), _ptr(out, _u16p))
+    return out.view(np.float16)

@@ -1,0 +1,261 @@
+"""Host-side mirror of the reference's operator interface for the per-ray hot path.
+
+Same names, argument order and meaning as the reference's C++ entry points, over the C ABI
+(include/rtxnerf.h).  torch is used only for device memory and streams.
+
+  launchSampler                    sampler/sampler.h:19-30
+  launch_volrender_cuda            vol_render/vol_render.h:5-13
+  launch_volrender_backward_cuda   vol_render/vol_render.h:15-25
+  make_grid                        main.cu:154-174
+  RTXDataHolder / Params / optixLaunch   rtx/include/rtxFunctions.h:56-100, params.h:14-42, main.cu:506-508
+"""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import Params  # noqa: F401  (re-exported: the reference's launch-parameter block)
+
+SAMPLING_REGULAR = 0               # sampler/sampler.h:5-9
+SAMPLING_STRATIFIED_JITTERING = 1
+SAMPLING_UNIFORM = 2
+NUM_SAMPLES_PER_SEGMENT = 32       # sampler/sampler.h:4
+
+
+def _p(t):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def _stream_ptr(stream):
+    if stream is None:
+        return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    if isinstance(stream, int):
+        return C.c_void_p(stream)
+    return C.c_void_p(stream.cuda_stream)
+
+
+def _chk_dev(t, dtype, name):
+    if not isinstance(t, torch.Tensor) or not t.is_cuda or t.dtype != dtype or not t.is_contiguous():
+        raise TypeError("%s must be a contiguous CUDA tensor of %s" % (name, dtype))
+
+
+# ----------------------------------------------------------------------------- sampler
+def launchSampler(d_start_points, d_end_points, d_view_dirs, d_t_vals, d_sampled_points, batch_size,
+                  grid_res, d_num_hits, d_indices, sample_type=SAMPLING_REGULAR, stream=None,
+                  samples_per_segment=NUM_SAMPLES_PER_SEGMENT):
+    """sampler/sampler.h:19-30.  Asynchronous on `stream`."""
+    for t, dt, n in ((d_start_points, torch.float32, "d_start_points"), (d_end_points, torch.float32, "d_end_points"),
+                     (d_view_dirs, torch.float32, "d_view_dirs"), (d_t_vals, torch.float32, "d_t_vals"),
+                     (d_sampled_points, torch.float32, "d_sampled_points"), (d_num_hits, torch.int32, "d_num_hits"),
+                     (d_indices, torch.int32, "d_indices")):
+        _chk_dev(t, dt, n)
+    lib = _lib.load()
+    _lib.check(lib.rtxnerf_launch_sampler(_p(d_start_points), _p(d_end_points), _p(d_view_dirs), _p(d_t_vals),
+                                          _p(d_sampled_points), int(batch_size), int(grid_res), _p(d_num_hits),
+                                          _p(d_indices), int(sample_type), int(samples_per_segment),
+                                          _stream_ptr(stream)), "launchSampler")
+    _lib.count_launches(1 if batch_size > 0 else 0)
+
+
+# ----------------------------------------------------------------------------- vol_render
+def launch_volrender_cuda(network_inputs, network_outputs, num_hits, indices, ray_hit, batch_size,
+                          num_samples_per_hit, pixels, stream=None):
+    """vol_render/vol_render.h:5-13 (network_inputs is unused, as in the reference)."""
+    for t, dt, n in ((network_outputs, torch.float32, "network_outputs"), (num_hits, torch.int32, "num_hits"),
+                     (indices, torch.int32, "indices"), (ray_hit, torch.float32, "ray_hit"),
+                     (pixels, torch.float32, "pixels")):
+        _chk_dev(t, dt, n)
+    lib = _lib.load()
+    _lib.check(lib.rtxnerf_launch_volrender(_p(network_inputs), _p(network_outputs), _p(num_hits), _p(indices),
+                                            _p(ray_hit), int(batch_size), int(num_samples_per_hit), _p(pixels),
+                                            _stream_ptr(stream)), "launch_volrender_cuda")
+    _lib.count_launches(1 if batch_size > 0 else 0)
+
+
+def launch_volrender_backward_cuda(loss_values, loss_gradients, sampled_points_radiance, t_hit, num_hits,
+                                   indices, batch_size, num_samples_per_hit, radiance_gradients, stream=None):
+    """vol_render/vol_render.h:15-25 (loss_values is unused, as in the reference)."""
+    for t, dt, n in ((loss_gradients, torch.float16, "loss_gradients"),
+                     (sampled_points_radiance, torch.float32, "sampled_points_radiance"),
+                     (t_hit, torch.float32, "t_hit"), (num_hits, torch.int32, "num_hits"),
+                     (indices, torch.int32, "indices"), (radiance_gradients, torch.float16, "radiance_gradients")):
+        _chk_dev(t, dt, n)
+    lib = _lib.load()
+    _lib.check(lib.rtxnerf_launch_volrender_backward(_p(loss_values), _p(loss_gradients),
+                                                     _p(sampled_points_radiance), _p(t_hit), _p(num_hits),
+                                                     _p(indices), int(batch_size), int(num_samples_per_hit),
+                                                     _p(radiance_gradients), _stream_ptr(stream)),
+               "launch_volrender_backward_cuda")
+    _lib.count_launches(1 if batch_size > 0 else 0)
+
+
+# ----------------------------------------------------------------------------- grid + ray march
+def make_grid(resolution):
+    """main.cu:154-174 on the host: [res^3][6] float32 AABBs, prim = (x*res+y)*res+z."""
+    L = np.float32(2.0) / np.float32(resolution)
+    i = np.arange(resolution, dtype=np.float32)
+    lo = (np.float32(-1.0) + i * L).astype(np.float32)
+    hi = (lo + L).astype(np.float32)
+    g = np.empty((resolution, resolution, resolution, 6), np.float32)
+    g[..., 0] = lo[:, None, None]
+    g[..., 1] = lo[None, :, None]
+    g[..., 2] = lo[None, None, :]
+    g[..., 3] = hi[:, None, None]
+    g[..., 4] = hi[None, :, None]
+    g[..., 5] = hi[None, None, :]
+    return g.reshape(-1, 6)
+
+
+class OccupancyGrid:
+    """Device occupancy bitfield + handle.  Replaces the GAS built by
+    RTXDataHolder::initAccelerationStructure (rtx/src/rtxFunctions.cpp:293-351)."""
+
+    def __init__(self, handle, G):
+        self._h = handle
+        self.G = G
+
+    @classmethod
+    def from_bits(cls, occ_bits, G):
+        bits = np.ascontiguousarray(occ_bits, np.uint32)
+        if bits.size != (G ** 3 + 31) // 32:
+            raise ValueError("occ_bits must hold G^3 bits")
+        h = C.c_void_p()
+        _lib.check(_lib.load().rtxnerf_grid_create(bits.ctypes.data_as(C.c_void_p), int(G), C.byref(h)), "grid_create")
+        return cls(h, G)
+
+    @classmethod
+    def from_occupancy(cls, occ_u8, G):
+        from .synth import pack_bits
+        return cls.from_bits(pack_bits(occ_u8), G)
+
+    @classmethod
+    def from_aabbs(cls, aabbs, G):
+        a = np.ascontiguousarray(aabbs, np.float32).reshape(-1, 6)
+        h = C.c_void_p()
+        _lib.check(_lib.load().rtxnerf_grid_create_from_aabbs(a.ctypes.data_as(C.c_void_p), a.shape[0], int(G),
+                                                              C.byref(h)), "grid_create_from_aabbs")
+        return cls(h, G)
+
+    @property
+    def handle(self):
+        return self._h.value
+
+    def update(self, occ_bits, stream=None):
+        bits = np.ascontiguousarray(occ_bits, np.uint32)
+        _lib.check(_lib.load().rtxnerf_grid_update(self._h, bits.ctypes.data_as(C.c_void_p), _stream_ptr(stream)),
+                   "grid_update")
+
+    def device_aabbs(self):
+        p = C.c_void_p()
+        _lib.check(_lib.load().rtxnerf_grid_device_aabbs(self._h, C.byref(p)), "grid_device_aabbs")
+        return p.value
+
+    def destroy(self):
+        if self._h is not None and self._h.value:
+            _lib.load().rtxnerf_grid_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.destroy()
+        except Exception:
+            pass
+
+
+class RTXDataHolder:
+    """Interface mirror of the reference's OptiX host wrapper (rtx/include/rtxFunctions.h:56-100).
+    The OptiX context / module / pipeline / SBT steps have nothing to build on a GPU without RT
+    cores and are kept as no-ops so the reference's call sequence (main.cu:381-399) still reads."""
+
+    def __init__(self):
+        self.gas_handle = 0
+        self.pipeline_ray_march = "ray_march"
+        self.sbt_ray_march = None
+        self.grid = None
+
+    def initContext(self):
+        _lib.load()
+
+    def createModule(self, ptx_filename=None):
+        pass
+
+    def createProgramGroups(self):
+        pass
+
+    def linkPipeline(self, debug=False):
+        pass
+
+    def buildSBT(self):
+        pass
+
+    def initAccelerationStructure(self, grid_aabbs, resolution=None):
+        """Takes the host AABB list (std::vector<OptixAabb>), returns the DEVICE AABB array
+        pointer the caller stores in Params.aabb (main.cu:399,492)."""
+        a = np.ascontiguousarray(grid_aabbs, np.float32).reshape(-1, 6)
+        if resolution is None:
+            resolution = int(round(2.0 / float(a[0, 3] - a[0, 0])))
+        self.grid = OccupancyGrid.from_aabbs(a, resolution)
+        self.gas_handle = self.grid.handle
+        return self.grid.device_aabbs()
+
+
+def optixLaunch(pipeline, stream, params, params_size=None, sbt=None, width=None, height=None, depth=1):
+    """main.cu:506-508.  `params` is the host copy of the launch block (the reference passes a
+    device copy; the new kernels take their arguments by value).  Dense output layout."""
+    if width is not None:
+        params.width = width
+    if height is not None:
+        params.height = height
+    _lib.check(_lib.load().rtxnerf_ray_march_dense(C.byref(params), _stream_ptr(stream)), "optixLaunch(ray_march)")
+    _lib.count_launches(1)
+
+
+class HitBuffers:
+    """Caller-owned CSR hit records for up to n_rays rays and `capacity` hits."""
+
+    def __init__(self, n_rays, capacity, device="cuda", want_t=True, want_cells=True, want_origins=True):
+        dev = torch.device(device)
+        self.n_rays, self.capacity = n_rays, capacity
+        self.num_hits = torch.empty(n_rays, dtype=torch.int32, device=dev)
+        self.indices = torch.empty(n_rays, dtype=torch.int32, device=dev)
+        self.view_dirs = torch.empty((n_rays, 2), dtype=torch.float32, device=dev)
+        self.ray_origins = torch.empty((n_rays, 3), dtype=torch.float32, device=dev) if want_origins else None
+        self.t_start = torch.empty(capacity, dtype=torch.float32, device=dev) if want_t else None
+        self.t_end = torch.empty(capacity, dtype=torch.float32, device=dev) if want_t else None
+        self.start_points = torch.empty((capacity, 3), dtype=torch.float32, device=dev)
+        self.end_points = torch.empty((capacity, 3), dtype=torch.float32, device=dev)
+        self.hit_cells = torch.empty(capacity, dtype=torch.int32, device=dev) if want_cells else None
+        self.total_hits = torch.zeros(1, dtype=torch.int64, device=dev)
+        ws = _lib.load().rtxnerf_ray_march_workspace_bytes(n_rays)
+        self.workspace = torch.empty(ws, dtype=torch.uint8, device=dev)
+
+    def c_struct(self):
+        return _lib.Hits(_p(self.num_hits), _p(self.indices), _p(self.view_dirs), _p(self.ray_origins),
+                         _p(self.t_start), _p(self.t_end), _p(self.start_points), _p(self.end_points),
+                         _p(self.hit_cells), _p(self.total_hits), self.capacity)
+
+
+def ray_march_csr(grid, look_at_dev, focal_length, aspect_ratio, width, height, hits, max_hits, ray_begin=0,
+                  n_rays=None, stream=None):
+    """Ray-grid intersection straight to CSR: replaces optixLaunch + D2H + thrust reduce/scan +
+    host gather (main.cu:506-543,631-676).  Asynchronous."""
+    _chk_dev(look_at_dev, torch.float32, "look_at")
+    if n_rays is None:
+        n_rays = width * height - ray_begin
+    if n_rays > hits.n_rays:
+        raise ValueError("HitBuffers too small for %d rays" % n_rays)
+    cam = _lib.Camera(_p(look_at_dev), float(focal_length), float(aspect_ratio), int(width), int(height))
+    st = hits.c_struct()
+    _lib.check(_lib.load().rtxnerf_ray_march_csr(grid._h, C.byref(cam), int(ray_begin), int(n_rays), int(max_hits),
+                                                 C.byref(st), _p(hits.workspace), hits.workspace.numel(),
+                                                 _stream_ptr(stream)), "ray_march_csr")
+    _lib.count_launches(3 if n_rays > 0 else 0)
+
+
+def cell_radiance(hit_cells, total_hits, capacity_hits, samples_per_segment, cell_rgbs, radiance, stream=None):
+    """BASELINE config 1: fixed per-cell (r,g,b,sigma) stands in for the network."""
+    _lib.check(_lib.load().rtxnerf_cell_radiance(_p(hit_cells), _p(total_hits), int(capacity_hits),
+                                                 int(samples_per_segment), _p(cell_rgbs), _p(radiance),
+                                                 _stream_ptr(stream)), "cell_radiance")
+    _lib.count_launches(1 if capacity_hits > 0 else 0)

@@ -1,0 +1,65 @@
+// common.cuh — shared helpers for the sm_100a kernels of librtxnerf_b200.so.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <cuda_fp16.h>
+#include <stdint.h>
+
+#include "../../include/rtxnerf.h"
+
+#define RTX_NUM_SMS 148  // B200: 2 dies x 74 SMs; grids are sized in multiples of this
+
+#define RTX_CUDA_TRY(expr)                      \
+    do {                                        \
+        cudaError_t _e = (expr);                \
+        if (_e != cudaSuccess) return (int)_e;  \
+    } while (0)
+
+static inline int rtx_launch_status() { return (int)cudaGetLastError(); }
+
+// ---------------------------------------------------------------------------------------
+// Bit-defined fp32 arithmetic.  The hit-cell lists must equal the reference's bit for bit,
+// so everything that feeds a comparison is spelled with the _rn intrinsics: nvcc never
+// contracts or reorders them, and the CPU oracle spells the same sequence with fmaf().
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ float rn_add(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ float rn_sub(float a, float b) { return __fsub_rn(a, b); }
+__device__ __forceinline__ float rn_mul(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ float rn_div(float a, float b) { return __fdiv_rn(a, b); }
+__device__ __forceinline__ float rn_fma(float a, float b, float c) { return __fmaf_rn(a, b, c); }
+
+// streaming (read-once / write-once) global accesses: keep them out of L1
+__device__ __forceinline__ float4 ld_stream_f4(const float4* p)
+{
+    float4 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                 : "l"(p));
+    return v;
+}
+__device__ __forceinline__ float ld_stream_f1(const float* p)
+{
+    float v;
+    asm volatile("ld.global.nc.L1::no_allocate.f32 %0, [%1];" : "=f"(v) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ void st_stream_f4(float4* p, float4 v)
+{
+    asm volatile("st.global.L1::no_allocate.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y),
+                 "f"(v.z), "f"(v.w)
+                 : "memory");
+}
+__device__ __forceinline__ void st_stream_f1(float* p, float v)
+{
+    asm volatile("st.global.L1::no_allocate.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
+}
+
+__device__ __forceinline__ int warp_incl_scan_i32(int v, int lane)
+{
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        int n = __shfl_up_sync(0xffffffffu, v, o);
+        if (lane >= o) v += n;
+    }
+    return v;
+}

@@ -1,0 +1,188 @@
+// composite.cu — alpha compositing forward / backward for sm_100a.
+//
+// Replaces volrender_cuda / volrender_backward_cuda and their launchers
+// (vol_render/vol_render.cu:19-190).  Quirks kept literally:
+//   Q15  delta = |t - t_prev| with t_prev carried ACROSS segments (starts at 0), the
+//        optical depth includes the current sample, no early termination (:55-63)
+//   Q16  the backward pass is the reference's own formula, not the analytic gradient (:118-135)
+//
+// The reference runs one thread per ray, serial over the ray's samples, with strided
+// 16-byte reads.  Here one warp owns one ray: lanes read 32 consecutive samples (512 B of
+// rgb-sigma + 128 B of t, coalesced), the optical depth is an inclusive warp scan of
+// delta*sigma carried across chunks, and the colour is a warp reduction.  The backward pass
+// has no scan at all (its "transmittance" is the local delta*sigma, :118) and writes 8 B of
+// half4 per sample.  HBM-bound: fwd 20 B/sample read; bwd 20 B read + 8 B written.
+#include "common.cuh"
+
+#define COMP_WARPS 8
+
+__global__ void __launch_bounds__(COMP_WARPS * 32)
+volrender_kernel(const float* __restrict__ network_outputs, const int* __restrict__ num_hits,
+                 const int* __restrict__ indices, const float* __restrict__ ray_hit, int batch_size, int S,
+                 float* __restrict__ pixels)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int warps_total = gridDim.x * COMP_WARPS;
+    for (int ray = blockIdx.x * COMP_WARPS + warp; ray < batch_size; ray += warps_total) {
+        const long long n = (long long)num_hits[ray] * S;
+        const long long base = (long long)indices[ray] * S;   // :50-55 sample index of (j=0,i=0)
+        const float4* rad = reinterpret_cast<const float4*>(network_outputs) + base;
+        const float* tv = ray_hit + base;
+        float carry_tau = 0.0f, carry_t = 0.0f;               // :32-33 transmittance = 0, t_initial = 0
+        float ax = 0.0f, ay = 0.0f, az = 0.0f;
+        for (long long q0 = 0; q0 < n; q0 += 32) {
+            const long long q = q0 + lane;
+            const bool valid = q < n;
+            float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
+            float t = carry_t;
+            if (valid) {
+                c = ld_stream_f4(rad + q);
+                t = ld_stream_f1(tv + q);
+            }
+            float t_prev = __shfl_up_sync(0xffffffffu, t, 1);
+            if (lane == 0) t_prev = carry_t;
+            const float delta = valid ? fabsf(t - t_prev) : 0.0f;      // :56
+            const float ds = delta * c.w;
+            float tau = ds;                                             // :60 inclusive prefix of delta*sigma
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                float nb = __shfl_up_sync(0xffffffffu, tau, o);
+                if (lane >= o) tau += nb;
+            }
+            tau += carry_tau;
+            const float w = expf(-tau) * (1.0f - expf(-ds));            // :61-63
+            ax = fmaf(c.x, w, ax);                                      // :65-67
+            ay = fmaf(c.y, w, ay);
+            az = fmaf(c.z, w, az);
+            carry_tau = __shfl_sync(0xffffffffu, tau, 31);
+            carry_t = __shfl_sync(0xffffffffu, t, 31);
+        }
+#pragma unroll
+        for (int o = 16; o; o >>= 1) {
+            ax += __shfl_xor_sync(0xffffffffu, ax, o);
+            ay += __shfl_xor_sync(0xffffffffu, ay, o);
+            az += __shfl_xor_sync(0xffffffffu, az, o);
+        }
+        if (lane == 0) {
+            float* p = pixels + 3 * (long long)ray;                     // :70-72
+            p[0] = ax;
+            p[1] = ay;
+            p[2] = az;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(COMP_WARPS * 32)
+volrender_backward_kernel(const __half* __restrict__ loss_gradients, const float* __restrict__ radiance,
+                          const float* __restrict__ t_hit, const int* __restrict__ num_hits,
+                          const int* __restrict__ indices, int batch_size, int S,
+                          __half* __restrict__ radiance_gradients)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int warps_total = gridDim.x * COMP_WARPS;
+    for (int ray = blockIdx.x * COMP_WARPS + warp; ray < batch_size; ray += warps_total) {
+        const long long n = (long long)num_hits[ray] * S;
+        if (n <= 0) continue;
+        const long long base = (long long)indices[ray] * S;
+        const float4* rad = reinterpret_cast<const float4*>(radiance) + base;
+        const float* tv = t_hit + base;
+        uint2* out = reinterpret_cast<uint2*>(radiance_gradients) + base;   // 4 halves per sample
+        const float gx = __half2float(loss_gradients[3 * (long long)ray]);  // :121-123
+        const float gy = __half2float(loss_gradients[3 * (long long)ray + 1]);
+        const float gz = __half2float(loss_gradients[3 * (long long)ray + 2]);
+        float carry_t = 0.0f;
+        for (long long q0 = 0; q0 < n; q0 += 32) {
+            const long long q = q0 + lane;
+            const bool valid = q < n;
+            float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
+            float t = carry_t;
+            if (valid) {
+                c = ld_stream_f4(rad + q);
+                t = ld_stream_f1(tv + q);
+            }
+            float t_prev = __shfl_up_sync(0xffffffffu, t, 1);
+            if (lane == 0) t_prev = carry_t;
+            carry_t = __shfl_sync(0xffffffffu, t, 31);
+            if (!valid) continue;
+            const float delta = fabsf(t - t_prev);                      // :115
+            const float tp = rn_mul(c.w, delta);                        // :118 transmittance = delta*sigma
+            const float a0 = rn_mul(gx, tp), a1 = rn_mul(tp, gy), a2 = rn_mul(tp, gz);
+            const float e = expf(rn_mul(delta, -c.w));                  // exp(-sigma*delta)
+            float ds = rn_fma(rn_mul(delta, rn_mul(c.x, a0)), e, 0.0f); // :127-129
+            ds = rn_fma(rn_mul(delta, rn_mul(c.y, a1)), e, ds);
+            ds = rn_fma(rn_mul(delta, rn_mul(c.z, a2)), e, ds);
+            const float om = rn_sub(1.0f, e);                           // :133-135
+            __half2 lo = __floats2half2_rn(rn_mul(a0, om), rn_mul(a1, om));
+            __half2 hi = __floats2half2_rn(rn_mul(a2, om), ds);
+            uint2 pk;
+            pk.x = *reinterpret_cast<unsigned*>(&lo);
+            pk.y = *reinterpret_cast<unsigned*>(&hi);
+            out[q] = pk;                                                // :136-139
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256)
+cell_radiance_kernel(const int* __restrict__ hit_cells, const long long* __restrict__ total_hits,
+                     long long capacity_hits, int S, const float4* __restrict__ cell_rgbs,
+                     float4* __restrict__ radiance)
+{
+    long long nh = *total_hits;
+    if (nh > capacity_hits) nh = capacity_hits;
+    const long long n = nh * S;
+    for (long long s = (long long)blockIdx.x * blockDim.x + threadIdx.x; s < n;
+         s += (long long)gridDim.x * blockDim.x) {
+        const int cell = hit_cells[s / S];
+        radiance[s] = __ldg(cell_rgbs + cell);
+    }
+}
+
+static unsigned ray_warp_blocks(int batch_size)
+{
+    long long blocks = ((long long)batch_size + COMP_WARPS - 1) / COMP_WARPS;
+    const long long max_blocks = (long long)RTX_NUM_SMS * 64;
+    return (unsigned)(blocks > max_blocks ? max_blocks : blocks);
+}
+
+extern "C" int rtxnerf_launch_volrender(const float* network_inputs, const float* network_outputs,
+                                        const int* num_hits, const int* indices, const float* ray_hit,
+                                        int batch_size, int num_samples_per_hit, float* pixels, void* stream)
+{
+    (void)network_inputs;  // unused by the reference too (vol_render.cu:20)
+    if (!network_outputs || !num_hits || !indices || !ray_hit || !pixels) return RTXNERF_EINVAL;
+    if (batch_size < 0 || num_samples_per_hit < 1) return RTXNERF_EINVAL;
+    if (batch_size == 0) return RTXNERF_OK;
+    volrender_kernel<<<ray_warp_blocks(batch_size), COMP_WARPS * 32, 0, (cudaStream_t)stream>>>(
+        network_outputs, num_hits, indices, ray_hit, batch_size, num_samples_per_hit, pixels);
+    return rtx_launch_status();
+}
+
+extern "C" int rtxnerf_launch_volrender_backward(const float* loss_values, const uint16_t* loss_gradients,
+                                                 const float* sampled_points_radiance, const float* t_hit,
+                                                 const int* num_hits, const int* indices, int batch_size,
+                                                 int num_samples_per_hit, uint16_t* radiance_gradients,
+                                                 void* stream)
+{
+    (void)loss_values;  // unused by the reference too (vol_render.cu:76)
+    if (!loss_gradients || !sampled_points_radiance || !t_hit || !num_hits || !indices || !radiance_gradients)
+        return RTXNERF_EINVAL;
+    if (batch_size < 0 || num_samples_per_hit < 1) return RTXNERF_EINVAL;
+    if (batch_size == 0) return RTXNERF_OK;
+    volrender_backward_kernel<<<ray_warp_blocks(batch_size), COMP_WARPS * 32, 0, (cudaStream_t)stream>>>(
+        reinterpret_cast<const __half*>(loss_gradients), sampled_points_radiance, t_hit, num_hits, indices,
+        batch_size, num_samples_per_hit, reinterpret_cast<__half*>(radiance_gradients));
+    return rtx_launch_status();
+}
+
+extern "C" int rtxnerf_cell_radiance(const int* d_hit_cells, const long long* d_total_hits,
+                                     long long capacity_hits, int samples_per_segment,
+                                     const float* d_cell_rgbs4, float* d_radiance, void* stream)
+{
+    if (!d_hit_cells || !d_total_hits || !d_cell_rgbs4 || !d_radiance) return RTXNERF_EINVAL;
+    if (capacity_hits < 0 || samples_per_segment < 1) return RTXNERF_EINVAL;
+    if (capacity_hits == 0) return RTXNERF_OK;
+    cell_radiance_kernel<<<RTX_NUM_SMS * 8, 256, 0, (cudaStream_t)stream>>>(
+        d_hit_cells, d_total_hits, capacity_hits, samples_per_segment,
+        reinterpret_cast<const float4*>(d_cell_rgbs4), reinterpret_cast<float4*>(d_radiance));
+    return rtx_launch_status();
+}

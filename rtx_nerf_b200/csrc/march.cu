@@ -1,0 +1,465 @@
+// march.cu — occupancy-grid ray march for sm_100a.
+//
+// Replaces the reference's OptiX pipeline (rtx/src/optixPrograms.cu:43-248, launched at
+// main.cu:506-508) — B200 has no RT cores.  Semantics reproduced bit for bit:
+//   raygen           optixPrograms.cu:43-82   (u,v in double; d normalised with IEEE sqrt/div)
+//   relaunch loop    optixPrograms.cu:99-115  (next origin = previous exit point, t local to it)
+//   slab predicate   optixPrograms.cu:132-169 (tmax > tmin; clamp to 0 when tmin<0 && tmax>1e-6)
+//   acceptance       ray interval [0, 102]    (optixPrograms.cu:79-80)
+//   closest hit      optixPrograms.cu:180-248 (entry/exit points, t_start/t_end, num_hits++)
+//
+// Method: for a power-of-two G the make_grid planes (main.cu:154-174) are exact and shared
+// by neighbouring cells, so per axis the slab intervals computed with the reference's own
+// expression (plane - o)/d tile the t line.  The cells the reference predicate can report
+// are exactly those whose three intervals overlap with positive length; they are visited
+// in increasing tmin by always advancing the axis whose interval ends first (a 3-way
+// sorted-interval sweep = an exact 3D-DDA).  Every visited OCCUPIED cell is then judged by
+// the literal predicate: the sweep proposes, the reference's arithmetic decides.
+// All arithmetic that feeds a comparison uses the _rn intrinsics (common.cuh).
+#include "common.cuh"
+
+#include <math.h>
+#include <new>
+#include <vector>
+
+struct rtxnerf_grid {
+    int G;
+    size_t n_words;
+    uint32_t* d_bits;   // G^3 bits, bit (p&31) of word (p>>5), p = (x*G+y)*G+z
+    float* d_aabb;      // lazily built make_grid list (compat with Params.aabb)
+};
+
+#define RAY_TMAX 102.0f              // optixPrograms.cu:80: (max.z - min.z) + 100
+#define CLAMP_EPS 9.99999997e-07f    // (float)1e-6: for float t, (double)t > 1e-6  <=>  t > (float)1e-6
+#define MARCH_BLOCK 128
+
+// ------------------------------------------------------------------------------------ raygen
+struct RayGen {
+    float ox, oy, oz, dx, dy, dz, theta, phi;
+};
+
+// optixPrograms.cu:43-82; FMA placement follows the reference's PTX:
+//   xd = fma(l0,u, l1*v) - l2*focal ; norm = sqrt(fma(zd,zd, fma(xd,xd, yd*yd)))
+__device__ __forceinline__ RayGen raygen(const float* __restrict__ l, float focal, float aspect,
+                                         unsigned width, unsigned height, unsigned x, unsigned y)
+{
+    double ud = __dadd_rn((double)x, 0.5);
+    ud = __dadd_rn(ud, ud);
+    ud = __ddiv_rn(ud, (double)width);
+    ud = __dadd_rn(ud, -1.0);
+    ud = __dmul_rn(ud, (double)aspect);
+    float u = __double2float_rn(ud);
+    double vd = __dadd_rn((double)y, 0.5);
+    vd = __dadd_rn(vd, vd);
+    vd = __ddiv_rn(vd, (double)height);
+    vd = __dadd_rn(vd, -1.0);
+    float v = __double2float_rn(vd);
+
+    float xd = rn_sub(rn_fma(l[0], u, rn_mul(l[1], v)), rn_mul(l[2], focal));
+    float yd = rn_sub(rn_fma(l[4], u, rn_mul(l[5], v)), rn_mul(l[6], focal));
+    float zd = rn_sub(rn_fma(l[8], u, rn_mul(l[9], v)), rn_mul(l[10], focal));
+    float norm = __fsqrt_rn(rn_fma(zd, zd, rn_fma(xd, xd, rn_mul(yd, yd))));
+    RayGen r;
+    r.dx = rn_div(xd, norm);
+    r.dy = rn_div(yd, norm);
+    r.dz = rn_div(zd, norm);
+    r.theta = atan2f(__fsqrt_rn(rn_fma(r.dx, r.dx, rn_mul(r.dy, r.dy))), r.dz);
+    r.phi = atan2f(r.dy, r.dx);
+    r.ox = rn_div(l[3], 10.0f);
+    r.oy = rn_div(l[7], 10.0f);
+    r.oz = rn_div(l[11], 10.0f);
+    return r;
+}
+
+// ------------------------------------------------------------------------------------ sweep
+__device__ __forceinline__ float plane_at(int i, float L) { return rn_fma((float)i, L, -1.0f); }  // exact
+
+__device__ __forceinline__ int locate_cell(float ok, int G, float L, float half_g)
+{
+    int i = (int)floorf(rn_mul(rn_add(ok, 1.0f), half_g));
+    i = max(0, min(G - 1, i));
+    while (i > 0 && ok < plane_at(i, L)) i--;
+    while (i < G - 1 && ok >= plane_at(i + 1, L)) i++;
+    return i;
+}
+
+struct HitRecord {
+    float t_start, t_end;
+    float sx, sy, sz, ex, ey, ez;
+    int cell;
+};
+
+// Marches one ray; calls emit(j, HitRecord) for hit j.  Returns the number of hits (<= cap).
+template <bool WANT_START, class Emit>
+__device__ __forceinline__ int march_ray(const uint32_t* __restrict__ bits, int G, float ox, float oy,
+                                         float oz, float dx, float dy, float dz, int cap, Emit emit)
+{
+    const float L = 2.0f / (float)G;
+    const float half_g = 0.5f * (float)G;
+    int nh = 0;
+    while (nh < cap) {
+        int ix = locate_cell(ox, G, L, half_g);
+        int iy = locate_cell(oy, G, L, half_g);
+        int iz = locate_cell(oz, G, L, half_g);
+        float tlx = rn_div(rn_sub(plane_at(ix, L), ox), dx), thx = rn_div(rn_sub(plane_at(ix + 1, L), ox), dx);
+        float tly = rn_div(rn_sub(plane_at(iy, L), oy), dy), thy = rn_div(rn_sub(plane_at(iy + 1, L), oy), dy);
+        float tlz = rn_div(rn_sub(plane_at(iz, L), oz), dz), thz = rn_div(rn_sub(plane_at(iz + 1, L), oz), dz);
+        bool found = false;
+        for (;;) {
+            if ((unsigned)ix >= (unsigned)G || (unsigned)iy >= (unsigned)G || (unsigned)iz >= (unsigned)G) break;
+            // optixPrograms.cu:143-156 (fminf/fmaxf == PTX min/max: a NaN operand yields the other)
+            float txx = fmaxf(tlx, thx), txy = fmaxf(tly, thy), txz = fmaxf(tlz, thz);
+            float tmin = fmaxf(fmaxf(fmaxf(-INFINITY, fminf(tlx, thx)), fminf(tly, thy)), fminf(tlz, thz));
+            float tmax = fminf(fminf(fminf(INFINITY, txx), txy), txz);
+            unsigned p = ((unsigned)ix * (unsigned)G + (unsigned)iy) * (unsigned)G + (unsigned)iz;
+            bool occ = (__ldg(bits + (p >> 5)) >> (p & 31u)) & 1u;
+            if (occ && tmax > tmin) {                                  // :164
+                float t = (tmin < 0.0f && tmax > CLAMP_EPS) ? 0.0f : tmin;  // :165-166
+                if (t >= 0.0f && t <= RAY_TMAX) {                      // OptiX ray interval
+                    HitRecord h;
+                    h.t_start = t;                                      // :188-189
+                    if (WANT_START) {
+                        h.sx = rn_fma(t, dx, ox);                       // :194-196
+                        h.sy = rn_fma(t, dy, oy);
+                        h.sz = rn_fma(t, dz, oz);
+                    }
+                    // :201-207 exit plane by the sign of d: (lo-o)/d when d<0 else (hi-o)/d
+                    float t_e = fminf(fminf(dx < 0.0f ? tlx : thx, dy < 0.0f ? tly : thy), dz < 0.0f ? tlz : thz);
+                    h.t_end = t_e;
+                    h.ex = rn_fma(dx, t_e, ox);                         // :209-211
+                    h.ey = rn_fma(dy, t_e, oy);
+                    h.ez = rn_fma(dz, t_e, oz);
+                    h.cell = (int)p;
+                    emit(nh, h);
+                    nh++;                                               // :241
+                    ox = h.ex;                                          // :245-247 relaunch from the exit point
+                    oy = h.ey;
+                    oz = h.ez;
+                    found = true;
+                    break;
+                }
+            }
+            // advance the axis whose interval ends first (ties: lowest axis; NaN/inf never advance)
+            int ks = -1;
+            float best = INFINITY;
+            if (txx < best) { best = txx; ks = 0; }
+            if (txy < best) { best = txy; ks = 1; }
+            if (txz < best) { best = txz; ks = 2; }
+            if (ks < 0 || best > RAY_TMAX) break;
+            float os = ks == 0 ? ox : (ks == 1 ? oy : oz);
+            float ds = ks == 0 ? dx : (ks == 1 ? dy : dz);
+            int is = ks == 0 ? ix : (ks == 1 ? iy : iz);
+            float tls = ks == 0 ? tlx : (ks == 1 ? tly : tlz);
+            float ths = ks == 0 ? thx : (ks == 1 ? thy : thz);
+            if (ds > 0.0f) {
+                is++;
+                tls = ths;
+                ths = rn_div(rn_sub(plane_at(is + 1, L), os), ds);
+            } else {
+                is--;
+                ths = tls;
+                tls = rn_div(rn_sub(plane_at(is, L), os), ds);
+            }
+            if (ks == 0) { ix = is; tlx = tls; thx = ths; }
+            else if (ks == 1) { iy = is; tly = tls; thy = ths; }
+            else { iz = is; tlz = tls; thz = ths; }
+        }
+        if (!found) break;
+    }
+    return nh;
+}
+
+// ------------------------------------------------------------------------------------ kernels
+struct CamArgs {
+    const float* look_at;
+    float focal, aspect;
+    unsigned width, height;
+};
+
+// Pass 1: count hits per ray, write per-ray outputs and one partial sum per block.
+__global__ void __launch_bounds__(MARCH_BLOCK)
+march_count_kernel(const uint32_t* __restrict__ bits, int G, CamArgs cam, long long ray_begin, long long n_rays,
+                   int cap, int* __restrict__ num_hits, float* __restrict__ view_dirs,
+                   float* __restrict__ ray_origins, int* __restrict__ block_sums)
+{
+    __shared__ int warp_sums[MARCH_BLOCK / 32];
+    long long lr = (long long)blockIdx.x * MARCH_BLOCK + threadIdx.x;
+    int nh = 0;
+    if (lr < n_rays) {
+        unsigned long long ray = (unsigned long long)(ray_begin + lr);
+        RayGen r = raygen(cam.look_at, cam.focal, cam.aspect, cam.width, cam.height,
+                          (unsigned)(ray % cam.width), (unsigned)(ray / cam.width));
+        nh = march_ray<false>(bits, G, r.ox, r.oy, r.oz, r.dx, r.dy, r.dz, cap, [](int, const HitRecord&) {});
+        num_hits[lr] = nh;
+        reinterpret_cast<float2*>(view_dirs)[lr] = make_float2(r.theta, r.phi);
+        if (ray_origins) {
+            ray_origins[3 * lr] = r.ox;
+            ray_origins[3 * lr + 1] = r.oy;
+            ray_origins[3 * lr + 2] = r.oz;
+        }
+    }
+    int s = nh;
+#pragma unroll
+    for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if ((threadIdx.x & 31) == 0) warp_sums[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int t = 0;
+#pragma unroll
+        for (int w = 0; w < MARCH_BLOCK / 32; w++) t += warp_sums[w];
+        block_sums[blockIdx.x] = t;
+    }
+}
+
+// Pass 2: exclusive scan of the block sums (one CTA; nb is a few thousand).
+__global__ void __launch_bounds__(1024)
+block_scan_kernel(const int* __restrict__ block_sums, int nb, long long* __restrict__ block_offsets,
+                  long long* __restrict__ total)
+{
+    __shared__ long long warp_tot[32];
+    __shared__ long long carry_s;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) carry_s = 0;
+    __syncthreads();
+    for (int base = 0; base < nb; base += 1024) {
+        int i = base + threadIdx.x;
+        long long v = i < nb ? block_sums[i] : 0;
+        long long inc = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            long long n = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += n;
+        }
+        if (lane == 31) warp_tot[warp] = inc;
+        __syncthreads();
+        if (warp == 0) {
+            long long w = warp_tot[lane];
+            long long winc = w;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                long long n = __shfl_up_sync(0xffffffffu, winc, o);
+                if (lane >= o) winc += n;
+            }
+            warp_tot[lane] = winc - w;  // exclusive
+        }
+        __syncthreads();
+        long long carry = carry_s;
+        if (i < nb) block_offsets[i] = carry + warp_tot[warp] + inc - v;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry_s = carry + warp_tot[31] + inc;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *total = carry_s;
+}
+
+struct FillOut {
+    float* t_start;
+    float* t_end;
+    float* start_points;
+    float* end_points;
+    int* hit_cells;
+    long long capacity;
+};
+
+__device__ __forceinline__ void store_hit(const FillOut& o, long long slot, const HitRecord& h)
+{
+    if (slot >= o.capacity) return;
+    if (o.t_start) o.t_start[slot] = h.t_start;
+    if (o.t_end) o.t_end[slot] = h.t_end;
+    float* s = o.start_points + 3 * slot;
+    s[0] = h.sx; s[1] = h.sy; s[2] = h.sz;
+    float* e = o.end_points + 3 * slot;
+    e[0] = h.ex; e[1] = h.ey; e[2] = h.ez;
+    if (o.hit_cells) o.hit_cells[slot] = h.cell;
+}
+
+// Pass 3: block-local scan of the counts + block offset = CSR index; march again and store.
+__global__ void __launch_bounds__(MARCH_BLOCK)
+march_fill_kernel(const uint32_t* __restrict__ bits, int G, CamArgs cam, long long ray_begin, long long n_rays,
+                  int cap, const int* __restrict__ num_hits, const long long* __restrict__ block_offsets,
+                  int* __restrict__ indices, FillOut out)
+{
+    __shared__ int warp_sums[MARCH_BLOCK / 32];
+    long long lr = (long long)blockIdx.x * MARCH_BLOCK + threadIdx.x;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int nh = lr < n_rays ? num_hits[lr] : 0;
+    int inc = warp_incl_scan_i32(nh, lane);
+    if (lane == 31) warp_sums[warp] = inc;
+    __syncthreads();
+    int woff = 0;
+#pragma unroll
+    for (int w = 0; w < MARCH_BLOCK / 32; w++) woff += (w < warp) ? warp_sums[w] : 0;
+    long long base = block_offsets[blockIdx.x] + woff + inc - nh;
+    if (lr >= n_rays) return;
+    indices[lr] = (int)base;
+    if (nh == 0) return;
+    unsigned long long ray = (unsigned long long)(ray_begin + lr);
+    RayGen r = raygen(cam.look_at, cam.focal, cam.aspect, cam.width, cam.height, (unsigned)(ray % cam.width),
+                      (unsigned)(ray / cam.width));
+    march_ray<true>(bits, G, r.ox, r.oy, r.oz, r.dx, r.dy, r.dz, nh,
+                    [&](int j, const HitRecord& h) { store_hit(out, base + j, h); });
+}
+
+// Dense layout of the reference (slot = ray*arr + j, optixPrograms.cu:184), one pass.
+__global__ void __launch_bounds__(MARCH_BLOCK)
+march_dense_kernel(const uint32_t* __restrict__ bits, int G, CamArgs cam, long long n_rays, int arr_size,
+                   int* __restrict__ num_hits, float* __restrict__ view_dirs, float* __restrict__ ray_origins,
+                   FillOut out)
+{
+    long long ray = (long long)blockIdx.x * MARCH_BLOCK + threadIdx.x;
+    if (ray >= n_rays) return;
+    RayGen r = raygen(cam.look_at, cam.focal, cam.aspect, cam.width, cam.height, (unsigned)(ray % cam.width),
+                      (unsigned)(ray / cam.width));
+    if (view_dirs) reinterpret_cast<float2*>(view_dirs)[ray] = make_float2(r.theta, r.phi);
+    if (ray_origins) {
+        ray_origins[3 * ray] = r.ox;
+        ray_origins[3 * ray + 1] = r.oy;
+        ray_origins[3 * ray + 2] = r.oz;
+    }
+    long long base = ray * arr_size;
+    int nh = march_ray<true>(bits, G, r.ox, r.oy, r.oz, r.dx, r.dy, r.dz, arr_size,
+                             [&](int j, const HitRecord& h) { store_hit(out, base + j, h); });
+    num_hits[ray] = nh;
+}
+
+// main.cu:154-174 on the device (the reference's own "TODO: make this a CUDA kernel", :153)
+__global__ void make_grid_kernel(int G, float* __restrict__ aabb)
+{
+    long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    long long n = (long long)G * G * G;
+    if (p >= n) return;
+    int z = (int)(p % G), y = (int)((p / G) % G), x = (int)(p / ((long long)G * G));
+    float L = 2.0f / (float)G;
+    float* a = aabb + 6 * p;
+    a[0] = rn_add(-1.0f, rn_mul((float)x, L));
+    a[1] = rn_add(-1.0f, rn_mul((float)y, L));
+    a[2] = rn_add(-1.0f, rn_mul((float)z, L));
+    a[3] = rn_add(a[0], L);
+    a[4] = rn_add(a[1], L);
+    a[5] = rn_add(a[2], L);
+}
+
+// ------------------------------------------------------------------------------------ host ABI
+static bool valid_res(int G) { return G >= 2 && G <= 1024 && (G & (G - 1)) == 0; }
+
+extern "C" int rtxnerf_grid_create(const uint32_t* occ_bits_host, int G, rtxnerf_grid** out)
+{
+    if (!occ_bits_host || !out) return RTXNERF_EINVAL;
+    if (!valid_res(G)) return RTXNERF_EGRID;
+    rtxnerf_grid* g = new (std::nothrow) rtxnerf_grid();
+    if (!g) return RTXNERF_ENOMEM;
+    g->G = G;
+    g->n_words = ((size_t)G * G * G + 31) / 32;
+    g->d_aabb = nullptr;
+    cudaError_t e = cudaMalloc(&g->d_bits, g->n_words * sizeof(uint32_t));
+    if (e != cudaSuccess) { delete g; return (int)e; }
+    e = cudaMemcpy(g->d_bits, occ_bits_host, g->n_words * sizeof(uint32_t), cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) { cudaFree(g->d_bits); delete g; return (int)e; }
+    *out = g;
+    return RTXNERF_OK;
+}
+
+extern "C" int rtxnerf_grid_create_from_aabbs(const float* aabb6_host, int n_prims, int G, rtxnerf_grid** out)
+{
+    if (!aabb6_host || !out || n_prims < 0) return RTXNERF_EINVAL;
+    if (!valid_res(G)) return RTXNERF_EGRID;
+    std::vector<uint32_t> bits(((size_t)G * G * G + 31) / 32, 0u);
+    const float L = 2.0f / (float)G;
+    for (int i = 0; i < n_prims; i++) {
+        const float* a = aabb6_host + 6 * (size_t)i;
+        int c[3];
+        for (int k = 0; k < 3; k++) {
+            c[k] = (int)lrintf((a[k] + 1.0f) / L);
+            if (c[k] < 0 || c[k] >= G) return RTXNERF_EINVAL;
+            if (a[k] != -1.0f + (float)c[k] * L || a[k + 3] != -1.0f + (float)c[k] * L + L) return RTXNERF_EINVAL;
+        }
+        size_t p = ((size_t)c[0] * G + c[1]) * G + c[2];
+        bits[p >> 5] |= 1u << (p & 31);
+    }
+    return rtxnerf_grid_create(bits.data(), G, out);
+}
+
+extern "C" int rtxnerf_grid_update(rtxnerf_grid* g, const uint32_t* occ_bits_host, void* stream)
+{
+    if (!g || !occ_bits_host) return RTXNERF_EINVAL;
+    RTX_CUDA_TRY(cudaMemcpyAsync(g->d_bits, occ_bits_host, g->n_words * sizeof(uint32_t), cudaMemcpyHostToDevice,
+                                 (cudaStream_t)stream));
+    return RTXNERF_OK;
+}
+
+extern "C" int rtxnerf_grid_destroy(rtxnerf_grid* g)
+{
+    if (!g) return RTXNERF_OK;
+    cudaFree(g->d_bits);
+    if (g->d_aabb) cudaFree(g->d_aabb);
+    delete g;
+    return RTXNERF_OK;
+}
+
+extern "C" int rtxnerf_grid_resolution(const rtxnerf_grid* g) { return g ? g->G : RTXNERF_EINVAL; }
+
+extern "C" int rtxnerf_grid_device_aabbs(rtxnerf_grid* g, float** d_aabb6_out)
+{
+    if (!g || !d_aabb6_out) return RTXNERF_EINVAL;
+    if (!g->d_aabb) {
+        long long n = (long long)g->G * g->G * g->G;
+        RTX_CUDA_TRY(cudaMalloc(&g->d_aabb, sizeof(float) * 6 * (size_t)n));
+        make_grid_kernel<<<(unsigned)((n + 255) / 256), 256>>>(g->G, g->d_aabb);
+        RTX_CUDA_TRY(cudaGetLastError());
+        RTX_CUDA_TRY(cudaDeviceSynchronize());
+    }
+    *d_aabb6_out = g->d_aabb;
+    return RTXNERF_OK;
+}
+
+extern "C" size_t rtxnerf_ray_march_workspace_bytes(long long n_rays)
+{
+    long long nb = (n_rays + MARCH_BLOCK - 1) / MARCH_BLOCK;
+    if (nb < 1) nb = 1;
+    return (size_t)nb * (sizeof(int) + sizeof(long long)) + 256;
+}
+
+extern "C" int rtxnerf_ray_march_csr(const rtxnerf_grid* grid, const rtxnerf_camera* cam, long long ray_begin,
+                                     long long n_rays, int max_hits, const rtxnerf_hits* hits, void* workspace,
+                                     size_t workspace_bytes, void* stream)
+{
+    if (!grid || !cam || !hits || !workspace || !cam->look_at) return RTXNERF_EINVAL;
+    if (!hits->num_hits || !hits->indices || !hits->view_dirs || !hits->start_points || !hits->end_points ||
+        !hits->total_hits)
+        return RTXNERF_EINVAL;
+    if (n_rays < 0 || ray_begin < 0 || max_hits < 1 || cam->width == 0 || cam->height == 0) return RTXNERF_EINVAL;
+    if (ray_begin + n_rays > (long long)cam->width * cam->height) return RTXNERF_EINVAL;
+    if (workspace_bytes < rtxnerf_ray_march_workspace_bytes(n_rays)) return RTXNERF_ECAPACITY;
+    cudaStream_t s = (cudaStream_t)stream;
+    if (n_rays == 0) {
+        RTX_CUDA_TRY(cudaMemsetAsync(hits->total_hits, 0, sizeof(long long), s));
+        return RTXNERF_OK;
+    }
+    long long nb = (n_rays + MARCH_BLOCK - 1) / MARCH_BLOCK;
+    // workspace: [block_offsets: nb x i64][block_sums: nb x i32]
+    long long* block_offsets = reinterpret_cast<long long*>(workspace);
+    int* block_sums = reinterpret_cast<int*>(block_offsets + nb);
+    CamArgs c{cam->look_at, cam->focal_length, cam->aspect_ratio, cam->width, cam->height};
+    march_count_kernel<<<(unsigned)nb, MARCH_BLOCK, 0, s>>>(grid->d_bits, grid->G, c, ray_begin, n_rays, max_hits,
+                                                          hits->num_hits, hits->view_dirs, hits->ray_origins,
+                                                          block_sums);
+    block_scan_kernel<<<1, 1024, 0, s>>>(block_sums, (int)nb, block_offsets, hits->total_hits);
+    FillOut fo{hits->t_start, hits->t_end, hits->start_points, hits->end_points, hits->hit_cells, hits->capacity};
+    march_fill_kernel<<<(unsigned)nb, MARCH_BLOCK, 0, s>>>(grid->d_bits, grid->G, c, ray_begin, n_rays, max_hits,
+                                                         hits->num_hits, block_offsets, hits->indices, fo);
+    return rtx_launch_status();
+}
+
+extern "C" int rtxnerf_ray_march_dense(const rtxnerf_params* p, void* stream)
+{
+    if (!p || !p->handle || !p->look_at || !p->num_hits || !p->start_points || !p->end_points) return RTXNERF_EINVAL;
+    if (p->intersection_arr_size < 1 || p->width == 0 || p->height == 0) return RTXNERF_EINVAL;
+    const rtxnerf_grid* grid = reinterpret_cast<const rtxnerf_grid*>((uintptr_t)p->handle);
+    long long n_rays = (long long)p->width * p->height;
+    CamArgs c{p->look_at, p->focal_length, p->aspect_ratio, p->width, p->height};
+    FillOut fo{p->t_start, p->t_end, p->start_points, p->end_points, nullptr, n_rays * p->intersection_arr_size};
+    march_dense_kernel<<<(unsigned)((n_rays + MARCH_BLOCK - 1) / MARCH_BLOCK), MARCH_BLOCK, 0, (cudaStream_t)stream>>>(
+        grid->d_bits, grid->G, c, n_rays, p->intersection_arr_size, p->num_hits, p->viewing_direction,
+        p->ray_origins, fo);
+    return rtx_launch_status();
+}

@@ -1,0 +1,92 @@
+"""The per-ray hot path as one pipeline over the C ABI: ray march -> sampler -> radiance ->
+compositing, in the reference's call order (main.cu:506-508 then :704-746), with every buffer
+allocated once (the reference re-mallocs per iteration, main.cu:683-694).
+
+The radiance stage is pluggable: the network (hash-grid + fused MLP, BASELINE configs 2-5) or
+the fixed per-cell table of BASELINE configs[0].
+"""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib, api
+
+
+class ViewRenderer:
+    """Renders views of W x H rays (or a contiguous ray range of them: the multi-GPU shard)."""
+
+    def __init__(self, grid, width, height, focal_length, aspect_ratio, samples_per_segment, max_hits,
+                 radiance, n_rays=None, ray_begin=0, capacity_hits=None, device="cuda", keep_t=False):
+        self.grid, self.W, self.H = grid, width, height
+        self.focal, self.aspect = float(focal_length), float(aspect_ratio)
+        self.S, self.max_hits = int(samples_per_segment), int(max_hits)
+        self.ray_begin = int(ray_begin)
+        self.R = int(n_rays if n_rays is not None else width * height - ray_begin)
+        self.cap = int(capacity_hits if capacity_hits is not None else self.R * self.max_hits)
+        self.radiance_stage = radiance
+        dev = torch.device(device)
+        self.hits = api.HitBuffers(self.R, self.cap, device=dev, want_t=keep_t, want_cells=radiance.needs_cells,
+                                   want_origins=False)
+        N = self.cap * self.S
+        self.N_cap = N
+        self.t_vals = torch.empty(N, dtype=torch.float32, device=dev)
+        self.samples = torch.empty((N, 5), dtype=torch.float32, device=dev)
+        self.radiance = torch.empty((N, 4), dtype=torch.float32, device=dev)
+        self.pixels = torch.empty((self.R, 3), dtype=torch.float32, device=dev)
+        self.pose_dev = torch.empty(16, dtype=torch.float32, device=dev)
+        self.pose_pinned = torch.empty(16, dtype=torch.float32).pin_memory()
+        self.pixels_pinned = torch.empty((self.R, 3), dtype=torch.float32).pin_memory()
+        self.launches_per_view = 3 + 1 + radiance.launches + 1
+
+    # --- stages (all asynchronous on the current stream) -------------------------------
+    def stage_march(self):
+        api.ray_march_csr(self.grid, self.pose_dev, self.focal, self.aspect, self.W, self.H, self.hits,
+                          self.max_hits, ray_begin=self.ray_begin, n_rays=self.R)
+
+    def stage_sampler(self):
+        h = self.hits
+        api.launchSampler(h.start_points, h.end_points, h.view_dirs, self.t_vals, self.samples, self.R,
+                          self.grid.G, h.num_hits, h.indices, api.SAMPLING_REGULAR, None, self.S)
+
+    def stage_radiance(self):
+        self.radiance_stage(self)
+
+    def stage_composite(self):
+        h = self.hits
+        api.launch_volrender_cuda(self.samples, self.radiance, h.num_hits, h.indices, self.t_vals, self.R, self.S,
+                                  self.pixels)
+
+    def render_device(self, pose_dev=None):
+        """Pose already on the device; returns the device pixel buffer."""
+        if pose_dev is not None:
+            self.pose_dev.copy_(pose_dev, non_blocking=True)
+        self.stage_march()
+        self.stage_sampler()
+        self.stage_radiance()
+        self.stage_composite()
+        return self.pixels
+
+    def render_host(self, pose_host):
+        """The user-facing call: host pose in, host pixels out (H2D + D2H inside)."""
+        self.pose_pinned.copy_(torch.as_tensor(np.asarray(pose_host, np.float32).reshape(16)))
+        self.pose_dev.copy_(self.pose_pinned, non_blocking=True)
+        self.render_device()
+        self.pixels_pinned.copy_(self.pixels, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return self.pixels_pinned
+
+    def total_hits(self):
+        return int(self.hits.total_hits.item())
+
+
+class CellRadiance:
+    """BASELINE configs[0]: fixed random density / RGB per grid cell."""
+    needs_cells = True
+    launches = 1
+
+    def __init__(self, cell_rgbs, device="cuda"):
+        self.cells = torch.as_tensor(np.ascontiguousarray(cell_rgbs, np.float32)).to(device)
+
+    def __call__(self, r):
+        api.cell_radiance(r.hits.hit_cells, r.hits.total_hits, r.cap, r.S, self.cells, r.radiance)
