@@ -164,6 +164,60 @@ int rtxnerf_cell_radiance(const int* d_hit_cells, const long long* d_total_hits,
                           long long capacity_hits, int samples_per_segment,
                           const float* d_cell_rgbs4, float* d_radiance, void* stream);
 
+/* ------------------------------------------------------------------------------------
+ * Network — replaces tiny-cuda-nn's encoding + FullyFusedMLP forward as called at
+ * main.cu:715-728 (network->forward + output slice + convertHalfToFloat).  tiny-cuda-nn
+ * @ d0522b4 is absent from the reference archive: the algorithms are restated from their
+ * published descriptions (PARITY UNPINNED).
+ * ---------------------------------------------------------------------------------- */
+#define RTXNERF_MAX_LEVELS 16
+
+/* Multiresolution hash encoding (instant-ngp) of xyz in [-1,1]^3.  Per-level geometry is
+ * explicit so that host oracle and kernel share it bit for bit:
+ *   pos = scale*x01 + 0.5 ; level l is dense (x + y*res + z*res^2) when res^3 <= size,
+ *   else hashed (x ^ y*2654435761 ^ z*805459861) mod size.  F = n_features = 2. */
+typedef struct rtxnerf_hashgrid {
+    const uint16_t* table;               /* device fp16 [sum(size)][2] */
+    int n_levels;                        /* 1..16 */
+    int n_features;                      /* 2 */
+    float scale[RTXNERF_MAX_LEVELS];
+    uint32_t res[RTXNERF_MAX_LEVELS];
+    uint32_t size[RTXNERF_MAX_LEVELS];   /* entries in the level */
+    uint32_t offset[RTXNERF_MAX_LEVELS]; /* first entry of the level */
+} rtxnerf_hashgrid;
+
+/* Bias-free MLP: fp16 weights row-major [out][in], layers concatenated
+ * [width][in_dim], (n_hidden-1) x [width][width], [16][width]; ReLU hidden, output padded
+ * to 16 (main.cu:715 padded_output_width), out_activation 0 = none, 1 = sigmoid (main.cu:63). */
+typedef struct rtxnerf_mlp {
+    const uint16_t* weights;             /* device fp16 */
+    int in_dim;                          /* 32 (= 16 levels x 2 features) */
+    int width;                           /* 64 */
+    int n_hidden;                        /* 2 */
+    int out_activation;
+} rtxnerf_mlp;
+
+enum { RTXNERF_IMPL_TCGEN05 = 0, RTXNERF_IMPL_SIMT = 1 };
+
+/* The number of rows processed is n = min(n_max, d_count ? *d_count * count_scale : n_max):
+ * d_count is the device hit total of the march, count_scale the samples per segment. */
+
+/* samples rows of `sample_stride` floats (x,y,z first) -> encoded fp16 [n][n_levels*2]. */
+int rtxnerf_hashgrid_encode(const rtxnerf_hashgrid* enc, const float* d_samples, int sample_stride,
+                            const long long* d_count, long long count_scale, long long n_max,
+                            uint16_t* d_encoded, void* stream);
+
+/* enc != NULL: input = fp32 sample rows [n][input_stride] (the sampler's [n][5] buffer,
+ * main.cu:716 GPUMatrix<float>(5,N)); enc == NULL: input = pre-encoded fp16 [n][in_dim].
+ * out16 (optional): fp16 [n][16] = GPUMatrix<half>(16,N) column-major (main.cu:720-721).
+ * radiance4 (optional): fp32 [n][4] = rows 0..3 converted to float (main.cu:723-728, the
+ * intended gather of Q3, fused into the epilogue).  impl selects the tcgen05 kernel (product)
+ * or the CUDA-core check kernel. */
+int rtxnerf_network_forward(const rtxnerf_hashgrid* enc, const rtxnerf_mlp* mlp, const void* d_input,
+                            int input_stride, const long long* d_count, long long count_scale,
+                            long long n_max, uint16_t* d_out16, float* d_radiance4, int impl,
+                            void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -39,6 +39,18 @@ class Hits(C.Structure):
                 ("total_hits", c_void_p), ("capacity", c_ll)]
 
 
+class HashGrid(C.Structure):
+    """rtxnerf_hashgrid (include/rtxnerf.h)."""
+    _fields_ = [("table", c_void_p), ("n_levels", c_int), ("n_features", c_int), ("scale", c_float * 16),
+                ("res", C.c_uint32 * 16), ("size", C.c_uint32 * 16), ("offset", C.c_uint32 * 16)]
+
+
+class Mlp(C.Structure):
+    """rtxnerf_mlp (include/rtxnerf.h)."""
+    _fields_ = [("weights", c_void_p), ("in_dim", c_int), ("width", c_int), ("n_hidden", c_int),
+                ("out_activation", c_int)]
+
+
 # symbol -> (restype, argtypes); this table is also what the CPU test checks against the header
 SIGNATURES = {
     "rtxnerf_abi_version": (c_int, []),
@@ -60,6 +72,10 @@ SIGNATURES = {
     "rtxnerf_launch_volrender_backward": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                                   c_int, c_int, c_void_p, c_void_p]),
     "rtxnerf_cell_radiance": (c_int, [c_void_p, c_void_p, c_ll, c_int, c_void_p, c_void_p, c_void_p]),
+    "rtxnerf_hashgrid_encode": (c_int, [C.POINTER(HashGrid), c_void_p, c_int, c_void_p, c_ll, c_ll, c_void_p,
+                                        c_void_p]),
+    "rtxnerf_network_forward": (c_int, [C.POINTER(HashGrid), C.POINTER(Mlp), c_void_p, c_int, c_void_p, c_ll, c_ll,
+                                        c_void_p, c_void_p, c_int, c_void_p]),
 }
 
 _lib = None

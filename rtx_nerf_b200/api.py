@@ -259,3 +259,66 @@ def cell_radiance(hit_cells, total_hits, capacity_hits, samples_per_segment, cel
                                                  int(samples_per_segment), _p(cell_rgbs), _p(radiance),
                                                  _stream_ptr(stream)), "cell_radiance")
     _lib.count_launches(1 if capacity_hits > 0 else 0)
+
+
+# ----------------------------------------------------------------------------- network
+IMPL_TCGEN05 = 0
+IMPL_SIMT = 1
+
+
+class Network:
+    """Encoding + fully fused MLP: the object the reference gets from tcnn::create_from_config
+    (main.cu:325) and drives with network->forward(stream, input, &output) (main.cu:721).
+    Configuration of BASELINE configs 2-5: 16-level hash grid (F=2) -> 2 x 64 ReLU -> 16 outputs,
+    sigmoid output activation (main.cu:63), fp16 parameters."""
+
+    n_input_dims = 5     # x, y, z, theta, phi (main.cu:322)
+    n_output_dims = 4    # r, g, b, sigma      (main.cu:323)
+
+    def __init__(self, levels, table_h, weights_h, in_dim=32, width=64, n_hidden=2, out_activation=1,
+                 device="cuda"):
+        self.levels = levels
+        self.table = torch.as_tensor(np.ascontiguousarray(table_h, np.float16)).to(device)
+        self.weights = torch.as_tensor(np.ascontiguousarray(weights_h, np.float16)).to(device)
+        self.in_dim, self.width, self.n_hidden, self.out_activation = in_dim, width, n_hidden, out_activation
+        hg = _lib.HashGrid()
+        hg.table = self.table.data_ptr()
+        hg.n_levels, hg.n_features = levels["n_levels"], levels["n_features"]
+        for l in range(levels["n_levels"]):
+            hg.scale[l] = float(levels["scale"][l])
+            hg.res[l] = int(levels["res"][l])
+            hg.size[l] = int(levels["size"][l])
+            hg.offset[l] = int(levels["offset"][l])
+        self._hg = hg
+        self._mlp = _lib.Mlp(self.weights.data_ptr(), in_dim, width, n_hidden, out_activation)
+
+    def padded_output_width(self):
+        return 16            # main.cu:715
+
+    def n_params(self):
+        return self.weights.numel() + self.table.numel()
+
+    def encode(self, samples, n=None, d_count=None, count_scale=1, encoded=None, stream=None):
+        n_max = samples.shape[0] if n is None else n
+        if encoded is None:
+            encoded = torch.empty((n_max, self.levels["n_levels"] * 2), dtype=torch.float16, device=samples.device)
+        _lib.check(_lib.load().rtxnerf_hashgrid_encode(C.byref(self._hg), _p(samples), samples.shape[1], _p(d_count),
+                                                       int(count_scale), int(n_max), _p(encoded),
+                                                       _stream_ptr(stream)), "hashgrid_encode")
+        _lib.count_launches(1 if n_max > 0 else 0)
+        return encoded
+
+    def forward(self, stream, input, output=None, radiance=None, n=None, d_count=None, count_scale=1,
+                impl=IMPL_TCGEN05, pre_encoded=False):
+        """input: fp32 [N][5] sample rows (GPUMatrix<float>(5,N)) or, with pre_encoded, fp16 [N][32].
+        output: fp16 [N][16] (GPUMatrix<half>(16,N)); radiance: fp32 [N][4] (rows 0..3 as float)."""
+        n_max = input.shape[0] if n is None else n
+        if output is None and radiance is None:
+            output = torch.empty((n_max, 16), dtype=torch.float16, device=input.device)
+        enc = None if pre_encoded else C.byref(self._hg)
+        _lib.check(_lib.load().rtxnerf_network_forward(enc, C.byref(self._mlp), _p(input), input.shape[1],
+                                                       _p(d_count), int(count_scale), int(n_max), _p(output),
+                                                       _p(radiance), int(impl), _stream_ptr(stream)),
+                   "network_forward")
+        _lib.count_launches(1 if n_max > 0 else 0)
+        return output if output is not None else radiance

@@ -1,0 +1,440 @@
+// network.cu — multiresolution hash encoding + fully fused MLP forward for sm_100a.
+//
+// Replaces tiny-cuda-nn's encoding + FullyFusedMLP forward as the reference calls it
+// (network->forward, main.cu:721; output slice + convertHalfToFloat, main.cu:723-728).
+// tcnn runs 16x16x16 wmma fragments (HMMA, sm_70 generation); here the three dense layers
+// 32->64->64->16 run on the 5th-gen tensor cores:
+//   * one CTA = 128 threads owns a tile of 128 samples = the M dimension of tcgen05.mma
+//   * weights (14 KB fp16) live in shared memory for the CTA's lifetime, in the K-major
+//     no-swizzle core-matrix layout the UMMA descriptors address
+//   * each thread encodes ITS sample (16 levels x 8 corner gathers, table L2-resident) and
+//     writes its row of the A operand straight into the UMMA layout
+//   * accumulators live in TMEM (128 lanes x 64 fp32 columns); epilogue = tcgen05.ld ->
+//     ReLU -> fp16 -> next layer's A operand in shared memory (activations never touch HBM)
+//   * last epilogue: sigmoid, fp16 round, and the fp32 (r,g,b,sigma) gather fused in, so the
+//     reference's separate half->float kernel (K7) disappears
+// Persistent grid; several CTAs per SM interleave gather latency with MMA/epilogue work.
+#include "common.cuh"
+#include "tcgen05.cuh"
+
+#define NET_TILE 128          // samples per tile = UMMA M
+#define NET_IN 32
+#define NET_W 64
+#define NET_OUT 16
+#define NET_TMEM_COLS 128     // D0: cols [0,64)  D1: [64,128)  D2: [0,16) (D0 is dead by then)
+
+struct Levels {
+    float scale[RTXNERF_MAX_LEVELS];
+    uint32_t res[RTXNERF_MAX_LEVELS];
+    uint32_t size[RTXNERF_MAX_LEVELS];
+    uint32_t offset[RTXNERF_MAX_LEVELS];
+    int n_levels;
+};
+
+// ---------------------------------------------------------------------------------------
+// One level of the hash encoding for one point: 8 corner gathers, trilinear weights.
+// Arithmetic order is fixed (and mirrored by the oracle) so the features are bit-defined.
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ __half2 encode_level(const __half2* __restrict__ table, float scale, uint32_t res,
+                                                uint32_t size, uint32_t offset, float x01, float y01, float z01)
+{
+    const float px = rn_fma(scale, x01, 0.5f), py = rn_fma(scale, y01, 0.5f), pz = rn_fma(scale, z01, 0.5f);
+    const float fx = floorf(px), fy = floorf(py), fz = floorf(pz);
+    const float wx = rn_sub(px, fx), wy = rn_sub(py, fy), wz = rn_sub(pz, fz);
+    const uint32_t gx = (uint32_t)(int)fx, gy = (uint32_t)(int)fy, gz = (uint32_t)(int)fz;
+    const bool dense = (uint64_t)res * res * res <= (uint64_t)size;
+    const __half2* lvl = table + offset;
+    __half2 v[8];
+#pragma unroll
+    for (int c = 0; c < 8; c++) {
+        const uint32_t qx = gx + (c & 1), qy = gy + ((c >> 1) & 1), qz = gz + ((c >> 2) & 1);
+        uint32_t idx;
+        if (dense) {
+            idx = qx + qy * res + qz * res * res;
+            idx = idx % size;
+        } else {
+            idx = (qx * 1u) ^ (qy * 2654435761u) ^ (qz * 805459861u);
+            idx = idx % size;
+        }
+        v[c] = __ldg(lvl + idx);
+    }
+    float a0 = 0.0f, a1 = 0.0f;
+#pragma unroll
+    for (int c = 0; c < 8; c++) {
+        float w = 1.0f;
+        w = rn_mul(w, (c & 1) ? wx : rn_sub(1.0f, wx));
+        w = rn_mul(w, (c & 2) ? wy : rn_sub(1.0f, wy));
+        w = rn_mul(w, (c & 4) ? wz : rn_sub(1.0f, wz));
+        const float2 f = __half22float2(v[c]);
+        a0 = rn_fma(w, f.x, a0);
+        a1 = rn_fma(w, f.y, a1);
+    }
+    return __floats2half2_rn(a0, a1);
+}
+
+__device__ __forceinline__ long long row_count(const long long* d_count, long long count_scale, long long n_max)
+{
+    if (!d_count) return n_max;
+    long long n = *d_count * count_scale;
+    return n < n_max ? n : n_max;
+}
+
+// encoding only (parity check of the features; also the producer for the SIMT check kernel)
+__global__ void __launch_bounds__(256)
+hashgrid_encode_kernel(Levels lv, const __half2* __restrict__ table, const float* __restrict__ samples, int stride,
+                       const long long* __restrict__ d_count, long long count_scale, long long n_max,
+                       __half2* __restrict__ encoded)
+{
+    const long long n = row_count(d_count, count_scale, n_max);
+    for (long long s = (long long)blockIdx.x * blockDim.x + threadIdx.x; s < n; s += (long long)gridDim.x * blockDim.x) {
+        const float* p = samples + s * stride;
+        const float x01 = rn_fma(p[0], 0.5f, 0.5f), y01 = rn_fma(p[1], 0.5f, 0.5f), z01 = rn_fma(p[2], 0.5f, 0.5f);
+        for (int l = 0; l < lv.n_levels; l++)
+            encoded[s * lv.n_levels + l] =
+                encode_level(table, lv.scale[l], lv.res[l], lv.size[l], lv.offset[l], x01, y01, z01);
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// UMMA operand tiles in shared memory: element (row r, col k) of a [rows x K] fp16 tile at
+//   (r>>3)*SBO + (k>>3)*128 + (r&7)*16 + (k&7)*2,   SBO = (K/8)*128, LBO = 128
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t tile_chunk_off(int r, int chunk, int K)
+{
+    return (uint32_t)((r >> 3) * (K * 16) + chunk * 128 + (r & 7) * 16);
+}
+
+// copy a row-major [rows][K] fp16 weight matrix from global into the UMMA layout
+__device__ __forceinline__ void load_weight_tile(uint8_t* smem_tile, const uint16_t* __restrict__ w, int rows, int K,
+                                                 int tid, int nthreads)
+{
+    const int chunks = K >> 3;
+    for (int i = tid; i < rows * chunks; i += nthreads) {
+        const int r = i / chunks, c = i - r * chunks;
+        const uint4 v = *reinterpret_cast<const uint4*>(w + (size_t)r * K + c * 8);
+        *reinterpret_cast<uint4*>(smem_tile + tile_chunk_off(r, c, K)) = v;
+    }
+}
+
+// one layer: D[128 x N] = A[128 x K] * W[N x K]^T, issued by a single thread
+template <int N, int K>
+__device__ __forceinline__ void issue_layer(uint32_t d_tmem, uint32_t a_saddr, uint32_t w_saddr, uint64_t* bar)
+{
+    constexpr uint32_t idesc = tc::idesc_f16_f32(NET_TILE, N);
+    constexpr uint32_t sbo = (K / 8) * 128;
+#pragma unroll
+    for (int ks = 0; ks < K / 16; ks++) {
+        const uint64_t ad = tc::smem_desc(a_saddr + ks * 256, 128, sbo);
+        const uint64_t bd = tc::smem_desc(w_saddr + ks * 256, 128, sbo);
+        tc::mma_f16_ss(d_tmem, ad, bd, idesc, ks > 0 ? 1u : 0u);
+    }
+    tc::mma_commit(bar);
+}
+
+// hidden-layer epilogue: TMEM row -> ReLU -> fp16 -> this thread's row of the next A tile
+__device__ __forceinline__ void relu_row_to_smem(uint32_t taddr, uint8_t* a_next, int row)
+{
+#pragma unroll
+    for (int q = 0; q < NET_W / 16; q++) {
+        uint32_t r[16];
+        tc::tmem_ld_x16(taddr + q * 16, r);
+        tc::tmem_ld_wait();
+        uint32_t pk[8];
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            const float a = fmaxf(__uint_as_float(r[2 * j]), 0.0f), b = fmaxf(__uint_as_float(r[2 * j + 1]), 0.0f);
+            const __half2 h = __floats2half2_rn(a, b);
+            pk[j] = *reinterpret_cast<const uint32_t*>(&h);
+        }
+        *reinterpret_cast<uint4*>(a_next + tile_chunk_off(row, 2 * q, NET_W)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+        *reinterpret_cast<uint4*>(a_next + tile_chunk_off(row, 2 * q + 1, NET_W)) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+    }
+}
+
+struct NetSmem {
+    // offsets into dynamic shared memory (all multiples of 128)
+    static constexpr int W0 = 0;                       // [64][32]  4 KB
+    static constexpr int W1 = W0 + NET_W * NET_IN * 2; // [64][64]  8 KB
+    static constexpr int W2 = W1 + NET_W * NET_W * 2;  // [16][64]  2 KB
+    static constexpr int A0 = W2 + NET_OUT * NET_W * 2;// [128][32] 8 KB
+    static constexpr int A1 = A0 + NET_TILE * NET_IN * 2;  // [128][64] 16 KB
+    static constexpr int A2 = A1 + NET_TILE * NET_W * 2;   // [128][64] 16 KB
+    static constexpr int BAR = A2 + NET_TILE * NET_W * 2;  // mbarrier (8 B) + tmem address (4 B)
+    static constexpr int BYTES = BAR + 16;
+};
+
+template <bool ENCODE>
+__global__ void __launch_bounds__(NET_TILE)
+network_forward_tc_kernel(Levels lv, const __half2* __restrict__ table, const uint16_t* __restrict__ weights,
+                          const void* __restrict__ input, int input_stride, int out_activation,
+                          const long long* __restrict__ d_count, long long count_scale, long long n_max,
+                          uint16_t* __restrict__ out16, float* __restrict__ radiance4)
+{
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint64_t* bar = reinterpret_cast<uint64_t*>(smem + NetSmem::BAR);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + NetSmem::BAR + 8);
+    const int tid = threadIdx.x, warp = tid >> 5;
+
+    load_weight_tile(smem + NetSmem::W0, weights, NET_W, NET_IN, tid, NET_TILE);
+    load_weight_tile(smem + NetSmem::W1, weights + NET_W * NET_IN, NET_W, NET_W, tid, NET_TILE);
+    load_weight_tile(smem + NetSmem::W2, weights + NET_W * NET_IN + NET_W * NET_W, NET_OUT, NET_W, tid, NET_TILE);
+    if (tid == 0) {
+        tc::mbar_init(bar, 1);
+        tc::fence_mbar_init();
+    }
+    if (warp == 0) tc::tmem_alloc<NET_TMEM_COLS>(tmem_slot);
+    tc::fence_proxy_async_smem();
+    tc::fence_before_thread_sync();
+    __syncthreads();
+    tc::fence_after_thread_sync();
+    const uint32_t tmem_base = *tmem_slot;
+    const uint32_t t_row = tmem_base + ((uint32_t)(warp * 32) << 16);   // this warp's 32 TMEM lanes
+    const uint32_t s_w0 = tc::smem_u32(smem + NetSmem::W0), s_w1 = tc::smem_u32(smem + NetSmem::W1),
+                   s_w2 = tc::smem_u32(smem + NetSmem::W2), s_a0 = tc::smem_u32(smem + NetSmem::A0),
+                   s_a1 = tc::smem_u32(smem + NetSmem::A1), s_a2 = tc::smem_u32(smem + NetSmem::A2);
+
+    const long long n = row_count(d_count, count_scale, n_max);
+    const long long n_tiles = (n + NET_TILE - 1) / NET_TILE;
+    uint32_t phase = 0;
+    for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const long long s = tile * NET_TILE + tid;
+        const bool valid = s < n;
+        // ---- A0: this thread's row of the layer-0 operand (4 chunks of 8 halves)
+        if (ENCODE) {
+            float x01 = 0.5f, y01 = 0.5f, z01 = 0.5f;
+            if (valid) {
+                const float* p = reinterpret_cast<const float*>(input) + s * input_stride;
+                x01 = rn_fma(p[0], 0.5f, 0.5f);
+                y01 = rn_fma(p[1], 0.5f, 0.5f);
+                z01 = rn_fma(p[2], 0.5f, 0.5f);
+            }
+#pragma unroll
+            for (int c = 0; c < NET_IN / 8; c++) {
+                uint32_t pk[4];
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const int l = c * 4 + j;
+                    __half2 f = __floats2half2_rn(0.0f, 0.0f);
+                    if (valid && l < lv.n_levels)
+                        f = encode_level(table, lv.scale[l], lv.res[l], lv.size[l], lv.offset[l], x01, y01, z01);
+                    pk[j] = *reinterpret_cast<const uint32_t*>(&f);
+                }
+                *reinterpret_cast<uint4*>(smem + NetSmem::A0 + tile_chunk_off(tid, c, NET_IN)) =
+                    make_uint4(pk[0], pk[1], pk[2], pk[3]);
+            }
+        } else {
+            const uint4* src = reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(input) + s * NET_IN);
+#pragma unroll
+            for (int c = 0; c < NET_IN / 8; c++) {
+                const uint4 v = valid ? __ldg(src + c) : make_uint4(0, 0, 0, 0);
+                *reinterpret_cast<uint4*>(smem + NetSmem::A0 + tile_chunk_off(tid, c, NET_IN)) = v;
+            }
+        }
+        tc::fence_proxy_async_smem();
+        tc::fence_before_thread_sync();
+        __syncthreads();
+        // ---- layer 0: D0 = A0 * W0^T
+        if (tid == 0) {
+            tc::fence_after_thread_sync();
+            issue_layer<NET_W, NET_IN>(tmem_base + 0, s_a0, s_w0, bar);
+        }
+        tc::mbar_wait(bar, phase);
+        phase ^= 1;
+        tc::fence_after_thread_sync();
+        relu_row_to_smem(t_row + 0, smem + NetSmem::A1, tid);
+        tc::fence_proxy_async_smem();
+        tc::fence_before_thread_sync();
+        __syncthreads();
+        // ---- layer 1: D1 = A1 * W1^T
+        if (tid == 0) {
+            tc::fence_after_thread_sync();
+            issue_layer<NET_W, NET_W>(tmem_base + 64, s_a1, s_w1, bar);
+        }
+        tc::mbar_wait(bar, phase);
+        phase ^= 1;
+        tc::fence_after_thread_sync();
+        relu_row_to_smem(t_row + 64, smem + NetSmem::A2, tid);
+        tc::fence_proxy_async_smem();
+        tc::fence_before_thread_sync();
+        __syncthreads();
+        // ---- output layer: D2 = A2 * W2^T (N = 16)
+        if (tid == 0) {
+            tc::fence_after_thread_sync();
+            issue_layer<NET_OUT, NET_W>(tmem_base + 0, s_a2, s_w2, bar);
+        }
+        tc::mbar_wait(bar, phase);
+        phase ^= 1;
+        tc::fence_after_thread_sync();
+        uint32_t r[16];
+        tc::tmem_ld_x16(t_row + 0, r);
+        tc::tmem_ld_wait();
+        if (valid) {
+            uint32_t pk[8];
+            float first4[4];
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                float a = __uint_as_float(r[2 * j]), b = __uint_as_float(r[2 * j + 1]);
+                if (out_activation == 1) {
+                    a = 1.0f / (1.0f + expf(-a));
+                    b = 1.0f / (1.0f + expf(-b));
+                }
+                const __half2 h = __floats2half2_rn(a, b);
+                pk[j] = *reinterpret_cast<const uint32_t*>(&h);
+                if (j < 2) {
+                    const float2 back = __half22float2(h);   // main.cu:723-728: radiance = float(half(out))
+                    first4[2 * j] = back.x;
+                    first4[2 * j + 1] = back.y;
+                }
+            }
+            if (out16) {
+                uint4* o = reinterpret_cast<uint4*>(out16 + s * NET_OUT);
+                o[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                o[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+            }
+            if (radiance4)
+                st_stream_f4(reinterpret_cast<float4*>(radiance4) + s,
+                             make_float4(first4[0], first4[1], first4[2], first4[3]));
+        }
+        // the next tile's MMAs overwrite D0/D1 and its encode overwrites A0: order TMEM reads first
+        tc::fence_before_thread_sync();
+        __syncthreads();
+    }
+    tc::fence_after_thread_sync();
+    if (warp == 0) tc::tmem_dealloc<NET_TMEM_COLS>(tmem_base);
+}
+
+// ---------------------------------------------------------------------------------------
+// CUDA-core check kernel (same numerics contract: fp16 weights/activations, fp32 accumulate).
+// Not the product path: selected only with impl = RTXNERF_IMPL_SIMT for A/B checks on the GPU.
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128)
+network_forward_simt_kernel(Levels lv, const __half2* __restrict__ table, const uint16_t* __restrict__ weights,
+                            const void* __restrict__ input, int input_stride, int encode, int out_activation,
+                            const long long* __restrict__ d_count, long long count_scale, long long n_max,
+                            uint16_t* __restrict__ out16, float* __restrict__ radiance4)
+{
+    __shared__ __half w[NET_W * NET_IN + NET_W * NET_W + NET_OUT * NET_W];
+    for (int i = threadIdx.x; i < NET_W * NET_IN + NET_W * NET_W + NET_OUT * NET_W; i += blockDim.x)
+        w[i] = reinterpret_cast<const __half*>(weights)[i];
+    __syncthreads();
+    const long long n = row_count(d_count, count_scale, n_max);
+    for (long long s = (long long)blockIdx.x * blockDim.x + threadIdx.x; s < n; s += (long long)gridDim.x * blockDim.x) {
+        float a[NET_W], b[NET_W];
+        if (encode) {
+            const float* p = reinterpret_cast<const float*>(input) + s * input_stride;
+            const float x01 = rn_fma(p[0], 0.5f, 0.5f), y01 = rn_fma(p[1], 0.5f, 0.5f), z01 = rn_fma(p[2], 0.5f, 0.5f);
+            for (int l = 0; l < NET_IN / 2; l++) {
+                float2 f = make_float2(0.f, 0.f);
+                if (l < lv.n_levels)
+                    f = __half22float2(encode_level(table, lv.scale[l], lv.res[l], lv.size[l], lv.offset[l], x01, y01, z01));
+                a[2 * l] = f.x;
+                a[2 * l + 1] = f.y;
+            }
+        } else {
+            const __half* src = reinterpret_cast<const __half*>(input) + s * NET_IN;
+            for (int k = 0; k < NET_IN; k++) a[k] = __half2float(src[k]);
+        }
+        const __half* wl = w;
+        for (int r = 0; r < NET_W; r++) {
+            float acc = 0.f;
+            for (int k = 0; k < NET_IN; k++) acc = fmaf(__half2float(wl[r * NET_IN + k]), a[k], acc);
+            b[r] = __half2float(__float2half_rn(fmaxf(acc, 0.f)));
+        }
+        wl += NET_W * NET_IN;
+        for (int r = 0; r < NET_W; r++) {
+            float acc = 0.f;
+            for (int k = 0; k < NET_W; k++) acc = fmaf(__half2float(wl[r * NET_W + k]), b[k], acc);
+            a[r] = __half2float(__float2half_rn(fmaxf(acc, 0.f)));
+        }
+        wl += NET_W * NET_W;
+        for (int r = 0; r < NET_OUT; r++) {
+            float acc = 0.f;
+            for (int k = 0; k < NET_W; k++) acc = fmaf(__half2float(wl[r * NET_W + k]), a[k], acc);
+            if (out_activation == 1) acc = 1.0f / (1.0f + expf(-acc));
+            const __half h = __float2half_rn(acc);
+            if (out16) reinterpret_cast<__half*>(out16)[s * NET_OUT + r] = h;
+            if (radiance4 && r < 4) radiance4[s * 4 + r] = __half2float(h);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------ host ABI
+static int levels_from(const rtxnerf_hashgrid* enc, Levels* lv)
+{
+    if (!enc->table || enc->n_levels < 1 || enc->n_levels > RTXNERF_MAX_LEVELS || enc->n_features != 2)
+        return RTXNERF_ECONFIG;
+    lv->n_levels = enc->n_levels;
+    for (int l = 0; l < RTXNERF_MAX_LEVELS; l++) {
+        const bool on = l < enc->n_levels;
+        lv->scale[l] = on ? enc->scale[l] : 0.f;
+        lv->res[l] = on ? enc->res[l] : 1u;
+        lv->size[l] = on ? enc->size[l] : 1u;
+        lv->offset[l] = on ? enc->offset[l] : 0u;
+        if (on && (enc->size[l] == 0 || enc->res[l] == 0)) return RTXNERF_ECONFIG;
+    }
+    return RTXNERF_OK;
+}
+
+extern "C" int rtxnerf_hashgrid_encode(const rtxnerf_hashgrid* enc, const float* d_samples, int sample_stride,
+                                       const long long* d_count, long long count_scale, long long n_max,
+                                       uint16_t* d_encoded, void* stream)
+{
+    if (!enc || !d_samples || !d_encoded || sample_stride < 3 || n_max < 0) return RTXNERF_EINVAL;
+    Levels lv;
+    int rc = levels_from(enc, &lv);
+    if (rc) return rc;
+    if (n_max == 0) return RTXNERF_OK;
+    long long blocks = (n_max + 255) / 256;
+    if (blocks > RTX_NUM_SMS * 32) blocks = RTX_NUM_SMS * 32;
+    hashgrid_encode_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(
+        lv, reinterpret_cast<const __half2*>(enc->table), d_samples, sample_stride, d_count, count_scale, n_max,
+        reinterpret_cast<__half2*>(d_encoded));
+    return rtx_launch_status();
+}
+
+extern "C" int rtxnerf_network_forward(const rtxnerf_hashgrid* enc, const rtxnerf_mlp* mlp, const void* d_input,
+                                       int input_stride, const long long* d_count, long long count_scale,
+                                       long long n_max, uint16_t* d_out16, float* d_radiance4, int impl, void* stream)
+{
+    if (!mlp || !mlp->weights || !d_input || n_max < 0 || (!d_out16 && !d_radiance4)) return RTXNERF_EINVAL;
+    if (mlp->in_dim != NET_IN || mlp->width != NET_W || mlp->n_hidden != 2) return RTXNERF_ECONFIG;
+    if (mlp->out_activation != 0 && mlp->out_activation != 1) return RTXNERF_ECONFIG;
+    Levels lv = {};
+    if (enc) {
+        if (input_stride < 3) return RTXNERF_EINVAL;
+        int rc = levels_from(enc, &lv);
+        if (rc) return rc;
+        if (enc->n_levels * 2 > NET_IN) return RTXNERF_ECONFIG;
+    }
+    if (n_max == 0) return RTXNERF_OK;
+    const __half2* table = enc ? reinterpret_cast<const __half2*>(enc->table) : nullptr;
+    cudaStream_t s = (cudaStream_t)stream;
+    if (impl == RTXNERF_IMPL_SIMT) {
+        long long blocks = (n_max + 127) / 128;
+        if (blocks > RTX_NUM_SMS * 16) blocks = RTX_NUM_SMS * 16;
+        network_forward_simt_kernel<<<(unsigned)blocks, 128, 0, s>>>(lv, table, mlp->weights, d_input, input_stride,
+                                                                   enc ? 1 : 0, mlp->out_activation, d_count,
+                                                                   count_scale, n_max, d_out16, d_radiance4);
+        return rtx_launch_status();
+    }
+    if (impl != RTXNERF_IMPL_TCGEN05) return RTXNERF_EINVAL;
+    static bool attr_set = false;
+    if (!attr_set) {
+        RTX_CUDA_TRY(cudaFuncSetAttribute(network_forward_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          NetSmem::BYTES));
+        RTX_CUDA_TRY(cudaFuncSetAttribute(network_forward_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          NetSmem::BYTES));
+        attr_set = true;
+    }
+    long long tiles = (n_max + NET_TILE - 1) / NET_TILE;
+    long long blocks = tiles < (long long)RTX_NUM_SMS * 4 ? tiles : (long long)RTX_NUM_SMS * 4;   // 4 CTAs / SM
+    if (enc)
+        network_forward_tc_kernel<true><<<(unsigned)blocks, NET_TILE, NetSmem::BYTES, s>>>(
+            lv, table, mlp->weights, d_input, input_stride, mlp->out_activation, d_count, count_scale, n_max, d_out16,
+            d_radiance4);
+    else
+        network_forward_tc_kernel<false><<<(unsigned)blocks, NET_TILE, NetSmem::BYTES, s>>>(
+            lv, table, mlp->weights, d_input, input_stride, mlp->out_activation, d_count, count_scale, n_max, d_out16,
+            d_radiance4);
+    return rtx_launch_status();
+}

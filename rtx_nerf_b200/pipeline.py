@@ -90,3 +90,17 @@ class CellRadiance:
 
     def __call__(self, r):
         api.cell_radiance(r.hits.hit_cells, r.hits.total_hits, r.cap, r.S, self.cells, r.radiance)
+
+
+class NetworkRadiance:
+    """BASELINE configs 2-5: hash-grid encoding + fused MLP (tcgen05) evaluated on the sampler's
+    [N][5] buffer, fp32 (r,g,b,sigma) written straight into the compositing input."""
+    needs_cells = False
+    launches = 1
+
+    def __init__(self, network, impl=api.IMPL_TCGEN05):
+        self.net, self.impl = network, impl
+
+    def __call__(self, r):
+        self.net.forward(None, r.samples, radiance=r.radiance, n=r.N_cap, d_count=r.hits.total_hits,
+                         count_scale=r.S, impl=self.impl)

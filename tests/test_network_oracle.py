@@ -1,0 +1,61 @@
+"""CPU tests of the encoding / MLP oracle (PARITY UNPINNED: tiny-cuda-nn is absent from the
+reference archive, so these pin the restatement to the published algorithm's properties and to
+an independent numpy evaluation, not to the reference)."""
+import numpy as np
+
+from rtx_nerf_b200 import synth
+
+
+def test_level_geometry_python_equals_c(orc):
+    lv = synth.hashgrid_levels()
+    sc, rs, sz = orc.hashgrid_geometry(16, 2, 19, 16, lv["per_level_scale"])
+    assert np.array_equal(sc, lv["scale"]) and np.array_equal(rs, lv["res"]) and np.array_equal(sz, lv["size"])
+    off, total = orc.hashgrid_offsets(16, 2, 19, 16, lv["per_level_scale"])
+    assert np.array_equal(off, lv["offset"]) and total == lv["n_entries"]
+    assert lv["res"][0] == 16 and lv["res"][-1] == 2048          # N_min .. N_max of instant-ngp
+    assert lv["size"].max() == 1 << 19
+
+
+def test_encode_interpolates_dense_level(orc):
+    """On a dense level, a sample exactly on a grid vertex returns that vertex's entry."""
+    lv = synth.hashgrid_levels(n_levels=2, log2_hashmap_size=19, base_resolution=16)
+    rng = np.random.default_rng(0)
+    table = rng.uniform(-1, 1, lv["n_entries"] * 2).astype(np.float16)
+    res, scale = int(lv["res"][0]), float(lv["scale"][0])
+    g = np.array([3, 5, 7])
+    x01 = (g - 0.5 + 1e-4) / scale * 0 + (g + 0.0) / scale - 0.5 / scale     # pos = scale*x + 0.5 = g exactly-ish
+    s = np.zeros((1, 5), np.float32)
+    s[0, :3] = x01 * 2 - 1
+    enc = orc.hashgrid_encode(lv, table, s).astype(np.float32)[0]
+    idx = g[0] + g[1] * res + g[2] * res * res
+    want = table.reshape(-1, 2)[idx].astype(np.float32)
+    np.testing.assert_allclose(enc[:2], want, atol=2e-2)
+
+
+def test_encode_continuity_and_range(orc):
+    lv = synth.hashgrid_levels()
+    rng = np.random.default_rng(1)
+    table = rng.uniform(-1, 1, lv["n_entries"] * 2).astype(np.float16)
+    s = np.zeros((4096, 5), np.float32)
+    s[:, :3] = rng.uniform(-1, 1, (4096, 3))
+    e = orc.hashgrid_encode(lv, table, s).astype(np.float32)
+    assert e.shape == (4096, 32) and np.all(np.abs(e) <= 1.0 + 1e-3)
+    s2 = s.copy()
+    s2[:, :3] += 1e-6
+    e2 = orc.hashgrid_encode(lv, table, s2).astype(np.float32)
+    assert np.abs(e - e2).max() < 0.02          # trilinear interpolation is continuous
+
+
+def test_mlp_oracle_vs_numpy(orc):
+    rng = np.random.default_rng(2)
+    w = synth.mlp_weights(seed=3)
+    x = rng.uniform(-1, 1, (512, 32)).astype(np.float16)
+    out16, rad = orc.mlp_forward(w, 32, 64, 2, 1, x)
+    wf = w.astype(np.float64)
+    W0, W1, W2 = wf[:2048].reshape(64, 32), wf[2048:6144].reshape(64, 64), wf[6144:].reshape(16, 64)
+    h = np.maximum(x.astype(np.float64) @ W0.T, 0).astype(np.float32).astype(np.float16).astype(np.float64)
+    h = np.maximum(h @ W1.T, 0).astype(np.float32).astype(np.float16).astype(np.float64)
+    o = 1.0 / (1.0 + np.exp(-(h @ W2.T)))
+    np.testing.assert_allclose(out16.astype(np.float64), o, atol=1e-3)
+    assert np.array_equal(rad, out16[:, :4].astype(np.float32))
+    assert w.size == 7168                        # SURVEY: 7 168 MLP parameters
