@@ -1,0 +1,297 @@
+#!/usr/bin/env python3
+"""bench.py — the driver's benchmark contract for the rtx_nerf per-ray hot path on B200.
+
+  python bench.py --gpus N --steps K --warmup W            (our arm; torchrun for N > 1)
+  python bench.py --impl reference --gpus N --steps K --warmup W
+
+One "step" = one pass of the hot path over one 800x800 view (BASELINE.json configs[1]):
+ray march over the 128^3 lego-shaped occupancy grid -> sampler (S = 4 samples per hit cell,
+H_max = 16 hit cells: "64 samples/ray") -> hash-grid encoding + 2x64 fused MLP -> alpha
+compositing.  Every rank renders its own view each step (views shard across GPUs with no
+data-path collective): weak scaling, value = total rays of all ranks / time.
+Synthetic data (seeded poses, lego-shaped grid, random-init hash table and MLP weights).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+WORKLOAD = dict(workload="configs[1]: one 800x800 view per step per GPU, 128^3 lego-shaped grid, "
+                         "S=4 samples/hit x H_max=16 hits (64 samples/ray), 16-level hash-grid + 2x64 fused MLP",
+                width=800, height=800, grid=128, samples_per_hit=4, max_hits=16,
+                network="hashgrid L16 F2 T2^19 Nmin16 Nmax2048 -> 64 -> 64 -> 16 (sigmoid), fp16",
+                parallelism="views sharded across ranks, no collective",
+                l2="per-step sample/radiance buffers (1.6 GB) exceed L2; hash table and bitfield are L2-resident by design")
+FLOP_PER_SAMPLE = 14336          # 2*(32*64 + 64*64 + 64*16)
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return dict(hbm=d["hbm_gbs"], tf=d["bf16_tflops"], tf_sustained=d.get("bf16_tflops_sustained"), src="measured")
+    return dict(hbm=6650.0, tf=1590.0, tf_sustained=1400.0, src="fallback")
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.stop_flag = index, [], False
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                f = [x.strip() for x in out.strip().split(",")]
+                if len(f) >= 6:
+                    self.rows.append(f)
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def summary(self):
+        self.stop_flag = True
+        if not self.rows:
+            return dict(sm_mhz=None, sm_max_mhz=None, reasons=["unsampled"])
+        sm = sorted(float(r[0]) for r in self.rows)
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(r[2 + i].lower().startswith("active") for r in self.rows)]
+        return dict(sm_mhz=sm[len(sm) // 2], sm_max_mhz=float(self.rows[0][1]), reasons=reasons, samples=len(sm))
+
+
+def scene():
+    from rtx_nerf_b200 import synth
+    G = WORKLOAD["grid"]
+    occ = synth.occupancy_lego(G, seed=0)
+    levels = synth.hashgrid_levels()
+    table = synth.hashgrid_table(levels, seed=1)
+    weights = synth.mlp_weights(seed=2)
+    return occ, levels, table, weights
+
+
+# ------------------------------------------------------------------------------------------- CPU arm
+def cpu_path(sample_rays, poses, nthreads, repeats=1):
+    """The hot path on host cores: oracle restatement (march via the exact DDA sweep, hash-grid +
+    MLP), with the reference's own host-compiled sampler / vol_render when oracle/_ref is present.
+    Returns (rays_per_s, samples_per_s, description)."""
+    from oracle import oracle as orc
+    from rtx_nerf_b200 import synth
+    occ, levels, table, weights = scene()
+    W, H, G, S, HM = WORKLOAD["width"], WORKLOAD["height"], WORKLOAD["grid"], WORKLOAD["samples_per_hit"], WORKLOAD["max_hits"]
+    focal = synth.focal_length()
+    have_ref = orc.ref_host() is not None
+    t_total, rays, samples = 0.0, 0, 0
+    for i in range(repeats):
+        pose = poses[i % len(poses)]
+        t0 = time.perf_counter()
+        m = orc.ray_march_dda(pose, focal, W / H, W, H, occ, G, max_hits=HM, csr=True, rays=(0, sample_rays),
+                              nthreads=nthreads)
+        nh, idx = m.num_hits[:sample_rays], m.indices[:sample_rays]
+        s, t = orc.sampler(m.start_points, m.end_points, m.view_dirs[:sample_rays], nh, idx, S, 0, nthreads=nthreads)
+        enc = orc.hashgrid_encode(levels, table, s, nthreads=nthreads)
+        _, rad = orc.mlp_forward(weights, 32, 64, 2, 1, enc, nthreads=nthreads)
+        if have_ref and S == 32:
+            orc.ref_volrender(rad, nh, idx, t, S)
+        else:
+            orc.volrender(rad, nh, idx, t, S, nthreads=nthreads)
+        t_total += time.perf_counter() - t0
+        rays += sample_rays
+        samples += s.shape[0]
+    return rays / t_total, samples / t_total, "first %d rays of an 800x800 view x %d" % (sample_rays, repeats)
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    from rtx_nerf_b200 import synth
+    nthreads = os.cpu_count() or 1
+    poses = synth.poses(args.steps + args.warmup + 1, seed=123)
+    sample = 16000
+    for _ in range(max(1, min(args.warmup, 2))):
+        cpu_path(2000, poses, nthreads)
+    t_steps = []
+    rays_s, samp_s = [], []
+    for k in range(args.steps):
+        t0 = time.perf_counter()
+        r, s, desc = cpu_path(sample, poses[k + 1:], nthreads)
+        t_steps.append(time.perf_counter() - t0)
+        rays_s.append(r)
+        samp_s.append(s)
+    v = float(np.mean(rays_s))
+    line = dict(metric="rays/s", value=v, unit="rays/s", n_gpus=args.gpus, steps=args.steps, warmup=args.warmup,
+                ms_per_step=1e3 * float(np.mean(t_steps)), higher_is_better=True, scaling="weak", vs_baseline=None,
+                dtype="f32", data="synthetic", impl="reference", config=WORKLOAD, samples_per_s=float(np.mean(samp_s)),
+                cpu_baseline=dict(value=v, unit="rays/s", cores=nthreads, kind="port",
+                                  sample="each step = first %d rays of one 800x800 view (CPU oracle: exact-DDA march, "
+                                         "sampler, hash-grid + MLP, compositing); OptiX / tiny-cuda-nn are unavailable "
+                                         "on this box so the reference's own march/MLP cannot run" % sample),
+                e2e=dict(value=v, unit="rays/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0), gpu_launches=0)
+    print(json.dumps(line))
+    return 0
+
+
+# ------------------------------------------------------------------------------------------- GPU arm
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from rtx_nerf_b200 import _lib, api, pipeline, synth
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    assert torch.cuda.is_available(), "bench.py needs a GPU (no CPU fallback)"
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    _lib.load()
+    pk = peaks()
+
+    occ, levels, table, weights = scene()
+    W, H, G, S, HM = WORKLOAD["width"], WORKLOAD["height"], WORKLOAD["grid"], WORKLOAD["samples_per_hit"], WORKLOAD["max_hits"]
+    focal = synth.focal_length()
+    grid = api.OccupancyGrid.from_occupancy(occ, G)
+    net = api.Network(levels, table, weights)
+    r = pipeline.ViewRenderer(grid, W, H, focal, W / H, S, HM, pipeline.NetworkRadiance(net))
+    # every rank renders a different view each step (views round-robin across ranks)
+    n_views = args.steps + args.warmup
+    poses = synth.poses(n_views * world + 1, seed=123)
+    my_poses = [poses[1 + k * world + rank] for k in range(n_views)]
+    poses_dev = [torch.as_tensor(p.reshape(16)).cuda() for p in my_poses]
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    stage_names = ["march", "sampler", "network", "composite"]
+    stage_fns = [r.stage_march, r.stage_sampler, r.stage_radiance, r.stage_composite]
+
+    # ---- warm-up
+    for k in range(args.warmup):
+        r.render_device(poses_dev[k])
+    barrier()
+
+    # ---- timed: K steps, inputs (pose) already resident in HBM, CUDA events on the launch stream
+    clocks = ClockSampler(local) if rank == 0 else None
+    if clocks:
+        clocks.start()
+    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(len(stage_fns) + 1)] for _ in range(args.steps)]
+    launches0 = _lib.launch_count
+    hits_total = torch.zeros(1, dtype=torch.int64, device="cuda")
+    barrier()
+    t_start = torch.cuda.Event(enable_timing=True)
+    t_end = torch.cuda.Event(enable_timing=True)
+    t_start.record()
+    for k in range(args.steps):
+        r.pose_dev.copy_(poses_dev[args.warmup + k], non_blocking=True)
+        ev[k][0].record()
+        for i, fn in enumerate(stage_fns):
+            fn()
+            ev[k][i + 1].record()
+        hits_total += r.hits.total_hits
+    t_end.record()
+    barrier()
+    launches = _lib.launch_count - launches0
+    ms_total = t_start.elapsed_time(t_end)
+    stage_ms = [float(np.mean([ev[k][i].elapsed_time(ev[k][i + 1]) for k in range(args.steps)])) for i in range(len(stage_fns))]
+    hits = int(hits_total.item())
+
+    # ---- e2e: the user's call, host pose in / host pixels out every step
+    barrier()
+    t0 = time.perf_counter()
+    for k in range(args.steps):
+        r.render_host(my_poses[args.warmup + k])
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    clock_summary = clocks.summary() if clocks else None
+
+    # ---- max over ranks
+    vals = torch.tensor([ms_total, e2e_s * 1e3, float(hits)] + stage_ms, dtype=torch.float64, device="cuda")
+    if world > 1:
+        mx = vals.clone()
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        sm = vals.clone()
+        dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+        ms_total, e2e_ms = float(mx[0]), float(mx[1])
+        hits_all = float(sm[2])
+        stage_ms = [float(x) for x in mx[3:]]
+    else:
+        e2e_ms, hits_all = e2e_s * 1e3, float(hits)
+
+    if rank == 0:
+        R = W * H
+        rays_all = R * args.steps * world
+        samples_all = hits_all * S
+        value = rays_all / (ms_total * 1e-3)
+        # per-launch algorithmic work of this rank's kernels, per step
+        Hh = hits / args.steps
+        Ns = Hh * S
+        byts = dict(march=28 * R + 32 * Hh + G ** 3 / 8 + 64, sampler=16 * R + 24 * Hh + 24 * Ns,
+                    composite=20 * Ns + 8 * R + 12 * R)
+        stages = {}
+        for nme, ms in zip(stage_names, stage_ms):
+            if nme == "network":
+                tf = FLOP_PER_SAMPLE * Ns / (ms * 1e-3) / 1e12
+                stages[nme] = dict(ms=ms, bound="tensor", achieved=tf, peak=pk["tf"], unit="TFLOP/s", frac=tf / pk["tf"],
+                                   samples_per_s=Ns / (ms * 1e-3))
+            else:
+                gb = byts[nme] / (ms * 1e-3) / 1e9
+                stages[nme] = dict(ms=ms, bound="hbm", achieved=gb, peak=pk["hbm"], unit="GB/s", frac=gb / pk["hbm"])
+        dom = max(stages, key=lambda k: stages[k]["ms"])
+        d = stages[dom]
+        roofline = dict(kernel=dom, bound=d["bound"], achieved=d["achieved"], peak=d["peak"], unit=d["unit"],
+                        frac=d["frac"], traffic=None, peak_source=pk["src"],
+                        note="achieved = algorithmic work per launch (SURVEY 8d) / mean CUDA-event duration of that "
+                             "stage inside the timed region; kernel share of the step = %.2f" % (d["ms"] / sum(stage_ms)))
+        line = dict(metric="rays/s", value=value, unit="rays/s", n_gpus=world, steps=args.steps, warmup=args.warmup,
+                    ms_per_step=ms_total / args.steps, higher_is_better=True, scaling="weak", vs_baseline=None,
+                    dtype="f16 tensor-core MLP (fp32 accumulate), f32 march/sampler/compositing", data="synthetic",
+                    config=WORKLOAD, samples_per_s=samples_all / (ms_total * 1e-3),
+                    rays_per_step_per_gpu=R, samples_per_step_per_gpu=Ns,
+                    e2e=dict(value=rays_all / (e2e_ms * 1e-3), unit="rays/s", h2d_bytes_per_step=64,
+                             d2h_bytes_per_step=R * 12, ms_per_step=e2e_ms / args.steps),
+                    gpu_launches=launches, roofline=roofline, stages=stages, clocks=clock_summary)
+        if world == 1 and not args.no_cpu:
+            nthreads = os.cpu_count() or 1
+            cpu_path(1000, my_poses, nthreads)
+            rs, ss, desc = cpu_path(16000, my_poses, nthreads)
+            line["cpu_baseline"] = dict(value=rs, unit="rays/s", cores=nthreads, kind="port", samples_per_s=ss,
+                                        sample=desc + " (CPU oracle, all host threads)")
+        print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())
