@@ -218,6 +218,16 @@ int rtxnerf_network_forward(const rtxnerf_hashgrid* enc, const rtxnerf_mlp* mlp,
                             long long n_max, uint16_t* d_out16, float* d_radiance4, int impl,
                             void* stream);
 
+/* Ray-coherent schedule of the same function over the sampler's CSR sample buffer
+ * (sample (j,i) of ray x at row (indices[x]+j)*S+i, sampler/sampler.cu:60-64): a warp covers 32
+ * neighbouring rays at one sample slot, so its hash-table gathers coalesce.  Results are
+ * identical to rtxnerf_network_forward on the same rows; rows not covered by
+ * (num_hits, indices) are not written.  This is what the render pipeline calls. */
+int rtxnerf_network_forward_rays(const rtxnerf_hashgrid* enc, const rtxnerf_mlp* mlp,
+                                 const float* d_samples, int sample_stride, const int* d_num_hits,
+                                 const int* d_indices, int n_rays, int samples_per_segment,
+                                 uint16_t* d_out16, float* d_radiance4, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -76,6 +76,8 @@ SIGNATURES = {
                                         c_void_p]),
     "rtxnerf_network_forward": (c_int, [C.POINTER(HashGrid), C.POINTER(Mlp), c_void_p, c_int, c_void_p, c_ll, c_ll,
                                         c_void_p, c_void_p, c_int, c_void_p]),
+    "rtxnerf_network_forward_rays": (c_int, [C.POINTER(HashGrid), C.POINTER(Mlp), c_void_p, c_int, c_void_p,
+                                             c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p]),
 }
 
 _lib = None

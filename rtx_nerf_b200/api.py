@@ -322,3 +322,17 @@ class Network:
                    "network_forward")
         _lib.count_launches(1 if n_max > 0 else 0)
         return output if output is not None else radiance
+
+    def forward_rays(self, stream, samples, num_hits, indices, n_rays, samples_per_segment, output=None,
+                     radiance=None):
+        """Ray-coherent schedule of forward() over the sampler's CSR sample buffer: same rows,
+        same results, gathers coalesced across neighbouring rays (network_rays.cu)."""
+        if output is None and radiance is None:
+            raise ValueError("forward_rays needs an output and/or radiance buffer")
+        _lib.check(_lib.load().rtxnerf_network_forward_rays(C.byref(self._hg), C.byref(self._mlp), _p(samples),
+                                                            samples.shape[1], _p(num_hits), _p(indices),
+                                                            int(n_rays), int(samples_per_segment), _p(output),
+                                                            _p(radiance), _stream_ptr(stream)),
+                   "network_forward_rays")
+        _lib.count_launches(1 if n_rays > 0 else 0)
+        return output if output is not None else radiance

@@ -1,0 +1,188 @@
+// hashgrid.cuh — multiresolution hash encoding (instant-ngp) shared by the forward and
+// backward network kernels.  tiny-cuda-nn (the reference's encoder, main.cu:35-69,721) is
+// absent from the reference archive; the published algorithm is restated here and in
+// oracle/rtxnerf_oracle.c with one fixed arithmetic order so the features are bit-defined.
+//
+// Cost model (ncu, profiles/r01_a_*): the encoding, not the MLP, bounds the network stage —
+// 128 gathers per sample against ~14 kFLOP of tensor work.  What is paid for is L1TEX
+// wavefronts (distinct 128-byte lines per load instruction) and issue slots, so:
+//   * the two x-neighbours of a corner pair are fetched with ONE 8-byte load whenever they
+//     share an aligned pair of entries (always for even gx on hashed levels: idx ^ 1; for
+//     even idx on dense levels), which removes ~1/3 of the load instructions;
+//   * index arithmetic is 32-bit, hashed levels of power-of-two size use a mask, dense
+//     levels take the modulo only on the (rare) wrap.
+#pragma once
+#include "common.cuh"
+
+struct Levels {
+    float scale[RTXNERF_MAX_LEVELS];
+    uint32_t res[RTXNERF_MAX_LEVELS];
+    uint32_t size[RTXNERF_MAX_LEVELS];
+    uint32_t offset[RTXNERF_MAX_LEVELS];
+    uint32_t mode[RTXNERF_MAX_LEVELS];   // 0 dense, 1 hashed (size = 2^k), 2 hashed (any size)
+    int n_levels;
+};
+
+#define HG_PRIME_Y 2654435761u
+#define HG_PRIME_Z 805459861u
+
+struct LevelPoint {
+    uint32_t idx[8];   // entry index of corner c = (cx) | (cy << 1) | (cz << 2) within the level
+    float w[8];        // trilinear weight of corner c
+};
+
+// Corner indices and weights of one level for one point (x01,y01,z01 in [0,1]).
+__device__ __forceinline__ void level_point(const Levels& lv, int l, float x01, float y01, float z01, LevelPoint& p)
+{
+    const float scale = lv.scale[l];
+    const uint32_t res = lv.res[l], size = lv.size[l], mode = lv.mode[l];
+    const float px = rn_fma(scale, x01, 0.5f), py = rn_fma(scale, y01, 0.5f), pz = rn_fma(scale, z01, 0.5f);
+    const float fx = floorf(px), fy = floorf(py), fz = floorf(pz);
+    const float wx = rn_sub(px, fx), wy = rn_sub(py, fy), wz = rn_sub(pz, fz);
+    const uint32_t gx = (uint32_t)(int)fx, gy = (uint32_t)(int)fy, gz = (uint32_t)(int)fz;
+    if (mode == 0) {
+        const uint32_t s2 = res * res;
+        const uint32_t base = gx + gy * res + gz * s2;
+        const bool wraps = base + 1u + res + s2 >= size;   // only on the far faces of the grid
+#pragma unroll
+        for (int c = 0; c < 8; c++) {
+            uint32_t i = base + (c & 1) + ((c & 2) ? res : 0u) + ((c & 4) ? s2 : 0u);
+            if (wraps) i %= size;
+            p.idx[c] = i;
+        }
+    } else {
+        const uint32_t hx0 = gx, hx1 = gx + 1u;
+        const uint32_t hy0 = gy * HG_PRIME_Y, hy1 = hy0 + HG_PRIME_Y;
+        const uint32_t hz0 = gz * HG_PRIME_Z, hz1 = hz0 + HG_PRIME_Z;
+        const uint32_t mask = size - 1u;
+#pragma unroll
+        for (int c = 0; c < 8; c++) {
+            const uint32_t h = ((c & 1) ? hx1 : hx0) ^ ((c & 2) ? hy1 : hy0) ^ ((c & 4) ? hz1 : hz0);
+            p.idx[c] = (mode == 1) ? (h & mask) : (h % size);
+        }
+    }
+    // w_c = ((1*wx_c)*wy_c)*wz_c in this order (1*x is exact)
+    const float ux = rn_sub(1.0f, wx), uy = rn_sub(1.0f, wy), uz = rn_sub(1.0f, wz);
+    const float w00 = rn_mul(ux, uy), w10 = rn_mul(wx, uy), w01 = rn_mul(ux, wy), w11 = rn_mul(wx, wy);
+    p.w[0] = rn_mul(w00, uz); p.w[1] = rn_mul(w10, uz); p.w[2] = rn_mul(w01, uz); p.w[3] = rn_mul(w11, uz);
+    p.w[4] = rn_mul(w00, wz); p.w[5] = rn_mul(w10, wz); p.w[6] = rn_mul(w01, wz); p.w[7] = rn_mul(w11, wz);
+}
+
+__device__ __forceinline__ uint2 ldg_u2(const void* p)
+{
+    uint2 v;
+    asm volatile("ld.global.nc.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ uint32_t ldg_u1(const void* p)
+{
+    uint32_t v;
+    asm volatile("ld.global.nc.u32 %0, [%1];" : "=r"(v) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ float2 h2_bits_to_f2(uint32_t b)
+{
+    return __half22float2(*reinterpret_cast<const __half2*>(&b));
+}
+
+// Features of one level: 8 corner gathers (x-pairs merged), fp32 trilinear blend in corner
+// order 0..7, one rounding to fp16 at the end.  `table` must be 8-byte aligned and the level
+// offset even (checked on the host).
+__device__ __forceinline__ __half2 encode_level(const __half2* __restrict__ table, const Levels& lv, int l,
+                                                float x01, float y01, float z01)
+{
+    LevelPoint p;
+    level_point(lv, l, x01, y01, z01, p);
+    const uint32_t* lvl = reinterpret_cast<const uint32_t*>(table) + lv.offset[l];
+    uint32_t v[8];
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+        const uint32_t i0 = p.idx[2 * q], i1 = p.idx[2 * q + 1];
+        const uint2 e = ldg_u2(lvl + (i0 & ~1u));
+        const bool odd = i0 & 1u;
+        v[2 * q] = odd ? e.y : e.x;
+        uint32_t other = odd ? e.x : e.y;
+        if ((i0 ^ i1) != 1u) other = ldg_u1(lvl + i1);
+        v[2 * q + 1] = other;
+    }
+    float a0 = 0.0f, a1 = 0.0f;
+#pragma unroll
+    for (int c = 0; c < 8; c++) {
+        const float2 f = h2_bits_to_f2(v[c]);
+        a0 = rn_fma(p.w[c], f.x, a0);
+        a1 = rn_fma(p.w[c], f.y, a1);
+    }
+    return __floats2half2_rn(a0, a1);
+}
+
+__device__ __forceinline__ long long row_count(const long long* d_count, long long count_scale, long long n_max)
+{
+    if (!d_count) return n_max;
+    long long n = *d_count * count_scale;
+    return n < n_max ? n : n_max;
+}
+
+// host side: validate + derive the per-level mode
+static inline int levels_from(const rtxnerf_hashgrid* enc, Levels* lv)
+{
+    if (!enc->table || enc->n_levels < 1 || enc->n_levels > RTXNERF_MAX_LEVELS || enc->n_features != 2)
+        return RTXNERF_ECONFIG;
+    if (((uintptr_t)enc->table & 7u) != 0) return RTXNERF_ECONFIG;
+    lv->n_levels = enc->n_levels;
+    for (int l = 0; l < RTXNERF_MAX_LEVELS; l++) {
+        const bool on = l < enc->n_levels;
+        lv->scale[l] = on ? enc->scale[l] : 0.f;
+        lv->res[l] = on ? enc->res[l] : 1u;
+        lv->size[l] = on ? enc->size[l] : 2u;
+        lv->offset[l] = on ? enc->offset[l] : 0u;
+        lv->mode[l] = 0;
+        if (!on) continue;
+        const uint32_t size = enc->size[l], res = enc->res[l];
+        // sizes are even so an aligned pair never straddles the end of a level
+        if (size < 2 || (size & 1u) || res == 0 || (enc->offset[l] & 1u)) return RTXNERF_ECONFIG;
+        const bool dense = (uint64_t)res * res * res <= (uint64_t)size;
+        lv->mode[l] = dense ? 0u : (((size & (size - 1u)) == 0 && size >= 4u) ? 1u : 2u);
+    }
+    return RTXNERF_OK;
+}
+
+// Branch-free fast path of encode_level for a hashed level of power-of-two size >= 4
+// (mode 1): identical arithmetic and corner order, so identical bits.  On such a level the
+// x-neighbour shares the aligned entry pair exactly when gx is even ((gx+1)^gx == 1).
+__device__ __forceinline__ __half2 encode_level_hashed(const uint32_t* __restrict__ table32, float scale,
+                                                       uint32_t mask, uint32_t offset, float x01, float y01,
+                                                       float z01)
+{
+    const float px = rn_fma(scale, x01, 0.5f), py = rn_fma(scale, y01, 0.5f), pz = rn_fma(scale, z01, 0.5f);
+    const float fx = floorf(px), fy = floorf(py), fz = floorf(pz);
+    const float wx = rn_sub(px, fx), wy = rn_sub(py, fy), wz = rn_sub(pz, fz);
+    const uint32_t gx = (uint32_t)(int)fx, gy = (uint32_t)(int)fy, gz = (uint32_t)(int)fz;
+    const uint32_t hy0 = gy * HG_PRIME_Y, hy1 = hy0 + HG_PRIME_Y;
+    const uint32_t hz0 = gz * HG_PRIME_Z, hz1 = hz0 + HG_PRIME_Z;
+    const uint32_t yz[4] = {hy0 ^ hz0, hy1 ^ hz0, hy0 ^ hz1, hy1 ^ hz1};
+    const uint32_t* lvl = table32 + offset;
+    const bool gx_odd = gx & 1u;
+    uint32_t v[8];
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+        const uint32_t i0 = (gx ^ yz[q]) & mask;
+        const uint2 e = __ldg(reinterpret_cast<const uint2*>(lvl + (i0 & ~1u)));
+        const bool odd = i0 & 1u;
+        v[2 * q] = odd ? e.y : e.x;
+        uint32_t other = odd ? e.x : e.y;
+        if (gx_odd) other = __ldg(lvl + (((gx + 1u) ^ yz[q]) & mask));
+        v[2 * q + 1] = other;
+    }
+    const float ux = rn_sub(1.0f, wx), uy = rn_sub(1.0f, wy), uz = rn_sub(1.0f, wz);
+    const float w00 = rn_mul(ux, uy), w10 = rn_mul(wx, uy), w01 = rn_mul(ux, wy), w11 = rn_mul(wx, wy);
+    const float w[8] = {rn_mul(w00, uz), rn_mul(w10, uz), rn_mul(w01, uz), rn_mul(w11, uz),
+                        rn_mul(w00, wz), rn_mul(w10, wz), rn_mul(w01, wz), rn_mul(w11, wz)};
+    float a0 = 0.0f, a1 = 0.0f;
+#pragma unroll
+    for (int c = 0; c < 8; c++) {
+        const float2 f = h2_bits_to_f2(v[c]);
+        a0 = rn_fma(w[c], f.x, a0);
+        a1 = rn_fma(w[c], f.y, a1);
+    }
+    return __floats2half2_rn(a0, a1);
+}

@@ -15,69 +15,8 @@
 //     reference's separate half->float kernel (K7) disappears
 // Persistent grid; several CTAs per SM interleave gather latency with MMA/epilogue work.
 #include "common.cuh"
-#include "tcgen05.cuh"
-
-#define NET_TILE 128          // samples per tile = UMMA M
-#define NET_IN 32
-#define NET_W 64
-#define NET_OUT 16
-#define NET_TMEM_COLS 128     // D0: cols [0,64)  D1: [64,128)  D2: [0,16) (D0 is dead by then)
-
-struct Levels {
-    float scale[RTXNERF_MAX_LEVELS];
-    uint32_t res[RTXNERF_MAX_LEVELS];
-    uint32_t size[RTXNERF_MAX_LEVELS];
-    uint32_t offset[RTXNERF_MAX_LEVELS];
-    int n_levels;
-};
-
-// ---------------------------------------------------------------------------------------
-// One level of the hash encoding for one point: 8 corner gathers, trilinear weights.
-// Arithmetic order is fixed (and mirrored by the oracle) so the features are bit-defined.
-// ---------------------------------------------------------------------------------------
-__device__ __forceinline__ __half2 encode_level(const __half2* __restrict__ table, float scale, uint32_t res,
-                                                uint32_t size, uint32_t offset, float x01, float y01, float z01)
-{
-    const float px = rn_fma(scale, x01, 0.5f), py = rn_fma(scale, y01, 0.5f), pz = rn_fma(scale, z01, 0.5f);
-    const float fx = floorf(px), fy = floorf(py), fz = floorf(pz);
-    const float wx = rn_sub(px, fx), wy = rn_sub(py, fy), wz = rn_sub(pz, fz);
-    const uint32_t gx = (uint32_t)(int)fx, gy = (uint32_t)(int)fy, gz = (uint32_t)(int)fz;
-    const bool dense = (uint64_t)res * res * res <= (uint64_t)size;
-    const __half2* lvl = table + offset;
-    __half2 v[8];
-#pragma unroll
-    for (int c = 0; c < 8; c++) {
-        const uint32_t qx = gx + (c & 1), qy = gy + ((c >> 1) & 1), qz = gz + ((c >> 2) & 1);
-        uint32_t idx;
-        if (dense) {
-            idx = qx + qy * res + qz * res * res;
-            idx = idx % size;
-        } else {
-            idx = (qx * 1u) ^ (qy * 2654435761u) ^ (qz * 805459861u);
-            idx = idx % size;
-        }
-        v[c] = __ldg(lvl + idx);
-    }
-    float a0 = 0.0f, a1 = 0.0f;
-#pragma unroll
-    for (int c = 0; c < 8; c++) {
-        float w = 1.0f;
-        w = rn_mul(w, (c & 1) ? wx : rn_sub(1.0f, wx));
-        w = rn_mul(w, (c & 2) ? wy : rn_sub(1.0f, wy));
-        w = rn_mul(w, (c & 4) ? wz : rn_sub(1.0f, wz));
-        const float2 f = __half22float2(v[c]);
-        a0 = rn_fma(w, f.x, a0);
-        a1 = rn_fma(w, f.y, a1);
-    }
-    return __floats2half2_rn(a0, a1);
-}
-
-__device__ __forceinline__ long long row_count(const long long* d_count, long long count_scale, long long n_max)
-{
-    if (!d_count) return n_max;
-    long long n = *d_count * count_scale;
-    return n < n_max ? n : n_max;
-}
+#include "hashgrid.cuh"
+#include "mlp_tile.cuh"
 
 // encoding only (parity check of the features; also the producer for the SIMT check kernel)
 __global__ void __launch_bounds__(256)
@@ -91,77 +30,23 @@ hashgrid_encode_kernel(Levels lv, const __half2* __restrict__ table, const float
         const float x01 = rn_fma(p[0], 0.5f, 0.5f), y01 = rn_fma(p[1], 0.5f, 0.5f), z01 = rn_fma(p[2], 0.5f, 0.5f);
         for (int l = 0; l < lv.n_levels; l++)
             encoded[s * lv.n_levels + l] =
-                encode_level(table, lv.scale[l], lv.res[l], lv.size[l], lv.offset[l], x01, y01, z01);
-    }
-}
-
-// ---------------------------------------------------------------------------------------
-// UMMA operand tiles in shared memory: element (row r, col k) of a [rows x K] fp16 tile at
-//   (r>>3)*SBO + (k>>3)*128 + (r&7)*16 + (k&7)*2,   SBO = (K/8)*128, LBO = 128
-// ---------------------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t tile_chunk_off(int r, int chunk, int K)
-{
-    return (uint32_t)((r >> 3) * (K * 16) + chunk * 128 + (r & 7) * 16);
-}
-
-// copy a row-major [rows][K] fp16 weight matrix from global into the UMMA layout
-__device__ __forceinline__ void load_weight_tile(uint8_t* smem_tile, const uint16_t* __restrict__ w, int rows, int K,
-                                                 int tid, int nthreads)
-{
-    const int chunks = K >> 3;
-    for (int i = tid; i < rows * chunks; i += nthreads) {
-        const int r = i / chunks, c = i - r * chunks;
-        const uint4 v = *reinterpret_cast<const uint4*>(w + (size_t)r * K + c * 8);
-        *reinterpret_cast<uint4*>(smem_tile + tile_chunk_off(r, c, K)) = v;
-    }
-}
-
-// one layer: D[128 x N] = A[128 x K] * W[N x K]^T, issued by a single thread
-template <int N, int K>
-__device__ __forceinline__ void issue_layer(uint32_t d_tmem, uint32_t a_saddr, uint32_t w_saddr, uint64_t* bar)
-{
-    constexpr uint32_t idesc = tc::idesc_f16_f32(NET_TILE, N);
-    constexpr uint32_t sbo = (K / 8) * 128;
-#pragma unroll
-    for (int ks = 0; ks < K / 16; ks++) {
-        const uint64_t ad = tc::smem_desc(a_saddr + ks * 256, 128, sbo);
-        const uint64_t bd = tc::smem_desc(w_saddr + ks * 256, 128, sbo);
-        tc::mma_f16_ss(d_tmem, ad, bd, idesc, ks > 0 ? 1u : 0u);
-    }
-    tc::mma_commit(bar);
-}
-
-// hidden-layer epilogue: TMEM row -> ReLU -> fp16 -> this thread's row of the next A tile
-__device__ __forceinline__ void relu_row_to_smem(uint32_t taddr, uint8_t* a_next, int row)
-{
-#pragma unroll
-    for (int q = 0; q < NET_W / 16; q++) {
-        uint32_t r[16];
-        tc::tmem_ld_x16(taddr + q * 16, r);
-        tc::tmem_ld_wait();
-        uint32_t pk[8];
-#pragma unroll
-        for (int j = 0; j < 8; j++) {
-            const float a = fmaxf(__uint_as_float(r[2 * j]), 0.0f), b = fmaxf(__uint_as_float(r[2 * j + 1]), 0.0f);
-            const __half2 h = __floats2half2_rn(a, b);
-            pk[j] = *reinterpret_cast<const uint32_t*>(&h);
-        }
-        *reinterpret_cast<uint4*>(a_next + tile_chunk_off(row, 2 * q, NET_W)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-        *reinterpret_cast<uint4*>(a_next + tile_chunk_off(row, 2 * q + 1, NET_W)) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+                encode_level(table, lv, l, x01, y01, z01);
     }
 }
 
 struct NetSmem {
-    // offsets into dynamic shared memory (all multiples of 128)
+    // offsets into dynamic shared memory (all multiples of 128).  One activation tile: the A
+    // operand of layer k+1 overwrites that of layer k, which is safe because every thread has
+    // waited on the MMA-complete barrier of layer k before it writes.  30 KB per CTA -> 7 CTAs
+    // per SM, 7 x 64 = 448 of the 512 TMEM columns.
     static constexpr int W0 = 0;                       // [64][32]  4 KB
     static constexpr int W1 = W0 + NET_W * NET_IN * 2; // [64][64]  8 KB
     static constexpr int W2 = W1 + NET_W * NET_W * 2;  // [16][64]  2 KB
-    static constexpr int A0 = W2 + NET_OUT * NET_W * 2;// [128][32] 8 KB
-    static constexpr int A1 = A0 + NET_TILE * NET_IN * 2;  // [128][64] 16 KB
-    static constexpr int A2 = A1 + NET_TILE * NET_W * 2;   // [128][64] 16 KB
-    static constexpr int BAR = A2 + NET_TILE * NET_W * 2;  // mbarrier (8 B) + tmem address (4 B)
+    static constexpr int ACT = W2 + NET_OUT * NET_W * 2;   // [128][32] then [128][64] twice, 16 KB
+    static constexpr int BAR = ACT + NET_TILE * NET_W * 2; // mbarrier (8 B) + tmem address (4 B)
     static constexpr int BYTES = BAR + 16;
 };
+#define NET_CTAS_PER_SM 7
 
 template <bool ENCODE>
 __global__ void __launch_bounds__(NET_TILE)
@@ -190,8 +75,8 @@ network_forward_tc_kernel(Levels lv, const __half2* __restrict__ table, const ui
     const uint32_t tmem_base = *tmem_slot;
     const uint32_t t_row = tmem_base + ((uint32_t)(warp * 32) << 16);   // this warp's 32 TMEM lanes
     const uint32_t s_w0 = tc::smem_u32(smem + NetSmem::W0), s_w1 = tc::smem_u32(smem + NetSmem::W1),
-                   s_w2 = tc::smem_u32(smem + NetSmem::W2), s_a0 = tc::smem_u32(smem + NetSmem::A0),
-                   s_a1 = tc::smem_u32(smem + NetSmem::A1), s_a2 = tc::smem_u32(smem + NetSmem::A2);
+                   s_w2 = tc::smem_u32(smem + NetSmem::W2), s_act = tc::smem_u32(smem + NetSmem::ACT);
+    uint8_t* act = smem + NetSmem::ACT;
 
     const long long n = row_count(d_count, count_scale, n_max);
     const long long n_tiles = (n + NET_TILE - 1) / NET_TILE;
@@ -199,80 +84,78 @@ network_forward_tc_kernel(Levels lv, const __half2* __restrict__ table, const ui
     for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         const long long s = tile * NET_TILE + tid;
         const bool valid = s < n;
-        // ---- A0: this thread's row of the layer-0 operand (4 chunks of 8 halves)
+        // ---- A0: this thread's row of the layer-0 operand.  The previous tile's last MMA has
+        // completed (every thread waited on its barrier), so the tile may be overwritten.
         if (ENCODE) {
             float x01 = 0.5f, y01 = 0.5f, z01 = 0.5f;
             if (valid) {
                 const float* p = reinterpret_cast<const float*>(input) + s * input_stride;
-                x01 = rn_fma(p[0], 0.5f, 0.5f);
-                y01 = rn_fma(p[1], 0.5f, 0.5f);
-                z01 = rn_fma(p[2], 0.5f, 0.5f);
+                x01 = rn_fma(ld_stream_f1(p), 0.5f, 0.5f);
+                y01 = rn_fma(ld_stream_f1(p + 1), 0.5f, 0.5f);
+                z01 = rn_fma(ld_stream_f1(p + 2), 0.5f, 0.5f);
             }
-#pragma unroll
-            for (int c = 0; c < NET_IN / 8; c++) {
-                uint32_t pk[4];
-#pragma unroll
-                for (int j = 0; j < 4; j++) {
-                    const int l = c * 4 + j;
-                    __half2 f = __floats2half2_rn(0.0f, 0.0f);
-                    if (valid && l < lv.n_levels)
-                        f = encode_level(table, lv.scale[l], lv.res[l], lv.size[l], lv.offset[l], x01, y01, z01);
-                    pk[j] = *reinterpret_cast<const uint32_t*>(&f);
-                }
-                *reinterpret_cast<uint4*>(smem + NetSmem::A0 + tile_chunk_off(tid, c, NET_IN)) =
-                    make_uint4(pk[0], pk[1], pk[2], pk[3]);
+            // rolled over levels: per-level parameters come from the constant bank, the body
+            // stays small enough for the instruction cache, 8 gathers are in flight per thread
+            // and the other CTAs of the SM hide their latency
+#pragma unroll 1
+            for (int l = 0; l < NET_IN / 2; l++) {
+                __half2 f = __floats2half2_rn(0.0f, 0.0f);
+                if (l < lv.n_levels) f = encode_level(table, lv, l, x01, y01, z01);
+                *reinterpret_cast<__half2*>(act + tile_chunk_off(tid, l >> 2, NET_IN) + (l & 3) * 4) = f;
             }
         } else {
             const uint4* src = reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(input) + s * NET_IN);
 #pragma unroll
             for (int c = 0; c < NET_IN / 8; c++) {
                 const uint4 v = valid ? __ldg(src + c) : make_uint4(0, 0, 0, 0);
-                *reinterpret_cast<uint4*>(smem + NetSmem::A0 + tile_chunk_off(tid, c, NET_IN)) = v;
+                *reinterpret_cast<uint4*>(act + tile_chunk_off(tid, c, NET_IN)) = v;
             }
         }
         tc::fence_proxy_async_smem();
-        tc::fence_before_thread_sync();
+        tc::fence_before_thread_sync();   // also orders the previous tile's tcgen05.ld before the next MMA
         __syncthreads();
-        // ---- layer 0: D0 = A0 * W0^T
+        // ---- layer 0: D = A0 * W0^T
         if (tid == 0) {
             tc::fence_after_thread_sync();
-            issue_layer<NET_W, NET_IN>(tmem_base + 0, s_a0, s_w0, bar);
+            issue_layer<NET_W, NET_IN>(tmem_base, s_act, s_w0, bar);
         }
         tc::mbar_wait(bar, phase);
         phase ^= 1;
         tc::fence_after_thread_sync();
-        relu_row_to_smem(t_row + 0, smem + NetSmem::A1, tid);
+        relu_row_to_smem(t_row, act, tid);
         tc::fence_proxy_async_smem();
         tc::fence_before_thread_sync();
         __syncthreads();
-        // ---- layer 1: D1 = A1 * W1^T
+        // ---- layer 1: D = A1 * W1^T
         if (tid == 0) {
             tc::fence_after_thread_sync();
-            issue_layer<NET_W, NET_W>(tmem_base + 64, s_a1, s_w1, bar);
+            issue_layer<NET_W, NET_W>(tmem_base, s_act, s_w1, bar);
         }
         tc::mbar_wait(bar, phase);
         phase ^= 1;
         tc::fence_after_thread_sync();
-        relu_row_to_smem(t_row + 64, smem + NetSmem::A2, tid);
+        relu_row_to_smem(t_row, act, tid);
         tc::fence_proxy_async_smem();
         tc::fence_before_thread_sync();
         __syncthreads();
-        // ---- output layer: D2 = A2 * W2^T (N = 16)
+        // ---- output layer: D[:, 0:16] = A2 * W2^T
         if (tid == 0) {
             tc::fence_after_thread_sync();
-            issue_layer<NET_OUT, NET_W>(tmem_base + 0, s_a2, s_w2, bar);
+            issue_layer<NET_OUT, NET_W>(tmem_base, s_act, s_w2, bar);
         }
         tc::mbar_wait(bar, phase);
         phase ^= 1;
         tc::fence_after_thread_sync();
         uint32_t r[16];
-        tc::tmem_ld_x16(t_row + 0, r);
+        tc::tmem_ld_x16(t_row, r);
         tc::tmem_ld_wait();
         if (valid) {
             uint32_t pk[8];
             float first4[4];
+            const int n_pairs = out16 ? 8 : 2;     // only (r,g,b,sigma) are needed without out16
 #pragma unroll
             for (int j = 0; j < 8; j++) {
+                if (j >= n_pairs) break;
                 float a = __uint_as_float(r[2 * j]), b = __uint_as_float(r[2 * j + 1]);
                 if (out_activation == 1) {
                     a = 1.0f / (1.0f + expf(-a));
@@ -295,10 +178,9 @@ network_forward_tc_kernel(Levels lv, const __half2* __restrict__ table, const ui
                 st_stream_f4(reinterpret_cast<float4*>(radiance4) + s,
                              make_float4(first4[0], first4[1], first4[2], first4[3]));
         }
-        // the next tile's MMAs overwrite D0/D1 and its encode overwrites A0: order TMEM reads first
-        tc::fence_before_thread_sync();
-        __syncthreads();
     }
+    tc::fence_before_thread_sync();
+    __syncthreads();
     tc::fence_after_thread_sync();
     if (warp == 0) tc::tmem_dealloc<NET_TMEM_COLS>(tmem_base);
 }
@@ -326,7 +208,7 @@ network_forward_simt_kernel(Levels lv, const __half2* __restrict__ table, const 
             for (int l = 0; l < NET_IN / 2; l++) {
                 float2 f = make_float2(0.f, 0.f);
                 if (l < lv.n_levels)
-                    f = __half22float2(encode_level(table, lv.scale[l], lv.res[l], lv.size[l], lv.offset[l], x01, y01, z01));
+                    f = __half22float2(encode_level(table, lv, l, x01, y01, z01));
                 a[2 * l] = f.x;
                 a[2 * l + 1] = f.y;
             }
@@ -359,22 +241,6 @@ network_forward_simt_kernel(Levels lv, const __half2* __restrict__ table, const 
 }
 
 // ------------------------------------------------------------------------------------ host ABI
-static int levels_from(const rtxnerf_hashgrid* enc, Levels* lv)
-{
-    if (!enc->table || enc->n_levels < 1 || enc->n_levels > RTXNERF_MAX_LEVELS || enc->n_features != 2)
-        return RTXNERF_ECONFIG;
-    lv->n_levels = enc->n_levels;
-    for (int l = 0; l < RTXNERF_MAX_LEVELS; l++) {
-        const bool on = l < enc->n_levels;
-        lv->scale[l] = on ? enc->scale[l] : 0.f;
-        lv->res[l] = on ? enc->res[l] : 1u;
-        lv->size[l] = on ? enc->size[l] : 1u;
-        lv->offset[l] = on ? enc->offset[l] : 0u;
-        if (on && (enc->size[l] == 0 || enc->res[l] == 0)) return RTXNERF_ECONFIG;
-    }
-    return RTXNERF_OK;
-}
-
 extern "C" int rtxnerf_hashgrid_encode(const rtxnerf_hashgrid* enc, const float* d_samples, int sample_stride,
                                        const long long* d_count, long long count_scale, long long n_max,
                                        uint16_t* d_encoded, void* stream)
@@ -427,7 +293,8 @@ extern "C" int rtxnerf_network_forward(const rtxnerf_hashgrid* enc, const rtxner
         attr_set = true;
     }
     long long tiles = (n_max + NET_TILE - 1) / NET_TILE;
-    long long blocks = tiles < (long long)RTX_NUM_SMS * 4 ? tiles : (long long)RTX_NUM_SMS * 4;   // 4 CTAs / SM
+    const long long resident = (long long)RTX_NUM_SMS * NET_CTAS_PER_SM;
+    long long blocks = tiles < resident ? tiles : resident;
     if (enc)
         network_forward_tc_kernel<true><<<(unsigned)blocks, NET_TILE, NetSmem::BYTES, s>>>(
             lv, table, mlp->weights, d_input, input_stride, mlp->out_activation, d_count, count_scale, n_max, d_out16,

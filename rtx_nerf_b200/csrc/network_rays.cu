@@ -1,0 +1,218 @@
+// network_rays.cu — ray-coherent hash encoding + fused MLP forward for sm_100a.
+//
+// Same function as network.cu's flat kernel (tiny-cuda-nn encoding + FullyFusedMLP forward as
+// called at main.cu:715-728) over the sampler's CSR sample buffer, but scheduled by RAY:
+//
+//   * a warp-group (4 warps) owns 32 consecutive rays (adjacent pixels of an image row);
+//     lane = ray, warp k = sample slot q0+k along the ray.  One gather instruction therefore
+//     touches the 32 neighbouring rays at the SAME depth, whose corners fall into the same or
+//     adjacent cells on almost every level: the number of distinct 128-byte lines per load
+//     (the L1TEX wavefronts that bound the flat kernel, profiles/r01_b_*) drops from up to 32
+//     to a handful, and the four warps walk consecutive samples so coarse levels hit L1.
+//   * the 16 feature pairs of a row stay in registers while they are gathered; the CTA's single
+//     16 KB activation tile and 64 TMEM columns are taken only for the ~1.5k cycles of the three
+//     tcgen05 layers (a shared-memory mutex between the CTA's 4 warp-groups).  30 KB of shared
+//     memory per 512 threads leaves ~160 KB of the SM's L1 to the hash table.
+//   * weights stay resident in shared memory (UMMA K-major layout) for the CTA's lifetime.
+#include "common.cuh"
+#include "hashgrid.cuh"
+#include "mlp_tile.cuh"
+
+#define NETR_WGS 4
+#define NETR_THREADS (NETR_WGS * NET_TILE)
+
+struct NetRSmem {
+    static constexpr int W0 = 0;
+    static constexpr int W1 = W0 + NET_W * NET_IN * 2;
+    static constexpr int W2 = W1 + NET_W * NET_W * 2;
+    static constexpr int ACT = W2 + NET_OUT * NET_W * 2;
+    static constexpr int BAR = ACT + NET_TILE * NET_W * 2;   // NETR_WGS mbarriers, tmem slot, lock
+    static constexpr int BYTES = BAR + 8 * NETR_WGS + 16;
+};
+
+__device__ __forceinline__ void wg_barrier(int wg)
+{
+    asm volatile("bar.sync %0, %1;" ::"r"(wg + 1), "n"(NET_TILE) : "memory");
+}
+
+// two levels at a time when both are hashed power-of-two levels (the expensive ones): the
+// body is branch-free so the 8-12 gathers of both levels are in flight together
+__device__ __forceinline__ void encode_pair(const Levels& lv, const uint32_t* __restrict__ table32, int l,
+                                            float x01, float y01, float z01, uint32_t& f0, uint32_t& f1)
+{
+    __half2 h0 = __floats2half2_rn(0.f, 0.f), h1 = h0;
+    if (l + 1 < lv.n_levels && lv.mode[l] == 1u && lv.mode[l + 1] == 1u) {
+        h0 = encode_level_hashed(table32, lv.scale[l], lv.size[l] - 1u, lv.offset[l], x01, y01, z01);
+        h1 = encode_level_hashed(table32, lv.scale[l + 1], lv.size[l + 1] - 1u, lv.offset[l + 1], x01, y01, z01);
+    } else {
+        if (l < lv.n_levels) h0 = encode_level(reinterpret_cast<const __half2*>(table32), lv, l, x01, y01, z01);
+        if (l + 1 < lv.n_levels)
+            h1 = encode_level(reinterpret_cast<const __half2*>(table32), lv, l + 1, x01, y01, z01);
+    }
+    f0 = *reinterpret_cast<const uint32_t*>(&h0);
+    f1 = *reinterpret_cast<const uint32_t*>(&h1);
+}
+
+template <int MIN_CTAS>
+__global__ void __launch_bounds__(NETR_THREADS, MIN_CTAS)
+network_forward_rays_kernel(Levels lv, const uint32_t* __restrict__ table32, const uint16_t* __restrict__ weights,
+                            const float* __restrict__ samples, int stride, int out_activation,
+                            const int* __restrict__ num_hits, const int* __restrict__ indices, int n_rays, int S,
+                            uint16_t* __restrict__ out16, float* __restrict__ radiance4)
+{
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + NetRSmem::BAR);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + NetRSmem::BAR + 8 * NETR_WGS);
+    int* lock = reinterpret_cast<int*>(smem + NetRSmem::BAR + 8 * NETR_WGS + 4);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int wg = tid >> 7, wt = tid & (NET_TILE - 1), wk = warp & 3;
+
+    load_weight_tile(smem + NetRSmem::W0, weights, NET_W, NET_IN, tid, NETR_THREADS);
+    load_weight_tile(smem + NetRSmem::W1, weights + NET_W * NET_IN, NET_W, NET_W, tid, NETR_THREADS);
+    load_weight_tile(smem + NetRSmem::W2, weights + NET_W * NET_IN + NET_W * NET_W, NET_OUT, NET_W, tid, NETR_THREADS);
+    if (tid == 0) {
+        for (int i = 0; i < NETR_WGS; i++) tc::mbar_init(bars + i, 1);
+        *lock = 0;
+        tc::fence_mbar_init();
+    }
+    if (warp == 0) tc::tmem_alloc<NET_TMEM_COLS>(tmem_slot);
+    tc::fence_proxy_async_smem();
+    tc::fence_before_thread_sync();
+    __syncthreads();
+    tc::fence_after_thread_sync();
+    const uint32_t tmem_base = *tmem_slot;
+    const uint32_t t_row = tmem_base + ((uint32_t)(wk * 32) << 16);   // TMEM lanes of this warp's quarter
+    const uint32_t s_w0 = tc::smem_u32(smem + NetRSmem::W0), s_w1 = tc::smem_u32(smem + NetRSmem::W1),
+                   s_w2 = tc::smem_u32(smem + NetRSmem::W2), s_act = tc::smem_u32(smem + NetRSmem::ACT);
+    uint8_t* act = smem + NetRSmem::ACT;
+    uint64_t* bar = bars + wg;
+    uint32_t phase = 0;
+
+    const int n_groups = (n_rays + 31) >> 5;
+    for (int g = blockIdx.x * NETR_WGS + wg; g < n_groups; g += gridDim.x * NETR_WGS) {
+        const int ray = g * 32 + lane;
+        int ns = 0;
+        long long base = 0;
+        if (ray < n_rays) {
+            ns = num_hits[ray] * S;
+            base = (long long)indices[ray] * S;
+        }
+        int maxn = ns;
+#pragma unroll
+        for (int o = 16; o; o >>= 1) maxn = max(maxn, __shfl_xor_sync(0xffffffffu, maxn, o));
+
+        for (int q0 = 0; q0 < maxn; q0 += 4) {
+            const int q = q0 + wk;
+            const bool valid = q < ns;
+            const long long s = base + q;
+            // ---- gather: this row's 16 feature pairs, in registers
+            uint32_t pk[NET_IN / 2];
+#pragma unroll
+            for (int i = 0; i < NET_IN / 2; i++) pk[i] = 0u;
+            if (valid) {
+                const float* p = samples + s * stride;
+                const float x01 = rn_fma(ld_stream_f1(p), 0.5f, 0.5f);
+                const float y01 = rn_fma(ld_stream_f1(p + 1), 0.5f, 0.5f);
+                const float z01 = rn_fma(ld_stream_f1(p + 2), 0.5f, 0.5f);
+#pragma unroll 1
+                for (int c = 0; c < NET_IN / 4; c++) {
+                    uint32_t f0, f1;
+                    encode_pair(lv, table32, 2 * c, x01, y01, z01, f0, f1);
+#pragma unroll
+                    for (int i = 0; i < NET_IN / 4; i++)
+                        if (i == c) {
+                            pk[2 * i] = f0;
+                            pk[2 * i + 1] = f1;
+                        }
+                }
+            }
+            // ---- the three layers, holding the CTA's activation tile and TMEM columns
+            if (wt == 0) {
+                while (atomicCAS(lock, 0, 1) != 0) __nanosleep(64);
+                __threadfence_block();
+            }
+            wg_barrier(wg);
+#pragma unroll
+            for (int c = 0; c < NET_IN / 8; c++)
+                *reinterpret_cast<uint4*>(act + tile_chunk_off(wt, c, NET_IN)) =
+                    make_uint4(pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
+            tc::fence_proxy_async_smem();
+            tc::fence_before_thread_sync();
+            wg_barrier(wg);
+            if (wt == 0) {
+                tc::fence_after_thread_sync();
+                issue_layer<NET_W, NET_IN>(tmem_base, s_act, s_w0, bar);
+            }
+            tc::mbar_wait(bar, phase);
+            phase ^= 1;
+            tc::fence_after_thread_sync();
+            relu_row_to_smem(t_row, act, wt);
+            tc::fence_proxy_async_smem();
+            tc::fence_before_thread_sync();
+            wg_barrier(wg);
+            if (wt == 0) {
+                tc::fence_after_thread_sync();
+                issue_layer<NET_W, NET_W>(tmem_base, s_act, s_w1, bar);
+            }
+            tc::mbar_wait(bar, phase);
+            phase ^= 1;
+            tc::fence_after_thread_sync();
+            relu_row_to_smem(t_row, act, wt);
+            tc::fence_proxy_async_smem();
+            tc::fence_before_thread_sync();
+            wg_barrier(wg);
+            if (wt == 0) {
+                tc::fence_after_thread_sync();
+                issue_layer<NET_OUT, NET_W>(tmem_base, s_act, s_w2, bar);
+            }
+            tc::mbar_wait(bar, phase);
+            phase ^= 1;
+            tc::fence_after_thread_sync();
+            uint32_t r[16];
+            output_row_load(t_row, r);
+            tc::fence_before_thread_sync();
+            wg_barrier(wg);                      // every row of the accumulator has been read
+            if (wt == 0) {
+                __threadfence_block();
+                atomicExch(lock, 0);
+            }
+            if (valid) output_row_store(r, out_activation, s, out16, radiance4);
+        }
+    }
+    tc::fence_before_thread_sync();
+    __syncthreads();
+    tc::fence_after_thread_sync();
+    if (warp == 0) tc::tmem_dealloc<NET_TMEM_COLS>(tmem_base);
+}
+
+extern "C" int rtxnerf_network_forward_rays(const rtxnerf_hashgrid* enc, const rtxnerf_mlp* mlp,
+                                            const float* d_samples, int sample_stride, const int* d_num_hits,
+                                            const int* d_indices, int n_rays, int samples_per_segment,
+                                            uint16_t* d_out16, float* d_radiance4, void* stream)
+{
+    if (!enc || !mlp || !mlp->weights || !d_samples || !d_num_hits || !d_indices || (!d_out16 && !d_radiance4))
+        return RTXNERF_EINVAL;
+    if (n_rays < 0 || samples_per_segment < 1 || sample_stride < 3) return RTXNERF_EINVAL;
+    if (mlp->in_dim != NET_IN || mlp->width != NET_W || mlp->n_hidden != 2) return RTXNERF_ECONFIG;
+    if (mlp->out_activation != 0 && mlp->out_activation != 1) return RTXNERF_ECONFIG;
+    Levels lv;
+    int rc = levels_from(enc, &lv);
+    if (rc) return rc;
+    if (enc->n_levels * 2 > NET_IN) return RTXNERF_ECONFIG;
+    if (n_rays == 0) return RTXNERF_OK;
+    constexpr int MIN_CTAS = 2;
+    auto kern = network_forward_rays_kernel<MIN_CTAS>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        RTX_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, NetRSmem::BYTES));
+        attr_set = true;
+    }
+    const long long groups = ((long long)n_rays + 31) / 32;
+    long long blocks = (groups + NETR_WGS - 1) / NETR_WGS;
+    const long long resident = (long long)RTX_NUM_SMS * MIN_CTAS;
+    if (blocks > resident) blocks = resident;
+    kern<<<(unsigned)blocks, NETR_THREADS, NetRSmem::BYTES, (cudaStream_t)stream>>>(
+        lv, reinterpret_cast<const uint32_t*>(enc->table), mlp->weights, d_samples, sample_stride,
+        mlp->out_activation, d_num_hits, d_indices, n_rays, samples_per_segment, d_out16, d_radiance4);
+    return rtx_launch_status();
+}

@@ -98,9 +98,13 @@ class NetworkRadiance:
     needs_cells = False
     launches = 1
 
-    def __init__(self, network, impl=api.IMPL_TCGEN05):
-        self.net, self.impl = network, impl
+    def __init__(self, network, impl=api.IMPL_TCGEN05, schedule="rays"):
+        self.net, self.impl, self.schedule = network, impl, schedule
 
     def __call__(self, r):
-        self.net.forward(None, r.samples, radiance=r.radiance, n=r.N_cap, d_count=r.hits.total_hits,
-                         count_scale=r.S, impl=self.impl)
+        if self.schedule == "rays" and self.impl == api.IMPL_TCGEN05:
+            self.net.forward_rays(None, r.samples, r.hits.num_hits, r.hits.indices, r.R, r.S,
+                                  radiance=r.radiance)
+        else:
+            self.net.forward(None, r.samples, radiance=r.radiance, n=r.N_cap, d_count=r.hits.total_hits,
+                             count_scale=r.S, impl=self.impl)

@@ -119,3 +119,35 @@ def test_network_render_config2_small(cuda_api, orc):
     assert r.total_hits() == ora.total_hits
     assert np.array_equal(r.hits.num_hits.cpu().numpy(), ora.num_hits)
     np.testing.assert_allclose(px, pxo, rtol=0, atol=1e-3)
+
+
+@pytest.mark.parametrize("n_rays,S", [(1, 4), (33, 4), (700, 3), (257, 32)])
+def test_ray_coherent_schedule_matches_flat_kernel(cuda_api, n_rays, S):
+    """network_forward_rays (lane = ray, warp = sample slot) must write the SAME bits as the flat
+    kernel on every CSR row, and leave rows outside (num_hits, indices) untouched; ragged rays
+    (0 hits, 1 hit, many hits) and a ray count that does not fill a 32-ray group."""
+    import torch
+    net, _, _, _ = _net(cuda_api, seed=11)
+    rng = np.random.default_rng(n_rays * 7 + S)
+    nh = rng.integers(0, 9, n_rays).astype(np.int32)
+    nh[rng.random(n_rays) < 0.2] = 0
+    idx = np.concatenate([[0], np.cumsum(nh)[:-1]]).astype(np.int32)
+    n = int(nh.sum()) * S
+    pad = 37                                   # rows after the last ray: must stay untouched
+    s = _samples(n + pad, n_rays)
+    ds = _t(s)
+    flat16 = torch.zeros((n + pad, 16), dtype=torch.float16, device="cuda")
+    flat4 = torch.zeros((n + pad, 4), dtype=torch.float32, device="cuda")
+    net.forward(None, ds, output=flat16, radiance=flat4)
+    ray16 = torch.full((n + pad, 16), -7.0, dtype=torch.float16, device="cuda")
+    ray4 = torch.full((n + pad, 4), -7.0, dtype=torch.float32, device="cuda")
+    net.forward_rays(None, ds, _t(nh), _t(idx), n_rays, S, output=ray16, radiance=ray4)
+    torch.cuda.synchronize()
+    assert np.array_equal(ray16.cpu().numpy()[:n].view(np.uint16), flat16.cpu().numpy()[:n].view(np.uint16))
+    assert np.array_equal(ray4.cpu().numpy()[:n], flat4.cpu().numpy()[:n])
+    assert np.all(ray4.cpu().numpy()[n:] == -7.0) and np.all(ray16.cpu().numpy()[n:].astype(np.float32) == -7.0)
+    # radiance-only call (no out16): same radiance
+    ray4b = torch.zeros((n + pad, 4), dtype=torch.float32, device="cuda")
+    net.forward_rays(None, ds, _t(nh), _t(idx), n_rays, S, radiance=ray4b)
+    torch.cuda.synchronize()
+    assert np.array_equal(ray4b.cpu().numpy()[:n], flat4.cpu().numpy()[:n])
