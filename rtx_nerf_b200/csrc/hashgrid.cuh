@@ -146,31 +146,71 @@ static inline int levels_from(const rtxnerf_hashgrid* enc, Levels* lv)
     return RTXNERF_OK;
 }
 
-// Branch-free fast path of encode_level for a hashed level of power-of-two size >= 4
-// (mode 1): identical arithmetic and corner order, so identical bits.  On such a level the
-// x-neighbour shares the aligned entry pair exactly when gx is even ((gx+1)^gx == 1).
-__device__ __forceinline__ __half2 encode_level_hashed(const uint32_t* __restrict__ table32, float scale,
-                                                       uint32_t mask, uint32_t offset, float x01, float y01,
-                                                       float z01)
+// base + zero-extended 32-bit byte offset in ONE instruction (IMAD.WIDE.U32 off, 1, base);
+// left to itself the compiler rebuilds every address from 64-bit pieces (5 instructions).
+__device__ __forceinline__ const char* addr_plus_u32(const char* base, uint32_t off)
 {
+    uint64_t r;
+    asm("mad.wide.u32 %0, %1, 1, %2;" : "=l"(r) : "r"(off), "l"(reinterpret_cast<uint64_t>(base)));
+    return reinterpret_cast<const char*>(r);
+}
+
+// Fast paths of encode_level for mode 0 (dense) and mode 1 (hashed, power-of-two size >= 4):
+// identical arithmetic and corner order, so identical bits; straight-line code so the gathers
+// of two levels can be in flight together.  All index arithmetic is done on BYTE offsets
+// (entry index x 4, the table is < 4 GiB): the hash primes are pre-multiplied by 4, one LOP3
+// gives the masked, pair-aligned offset, one IMAD.WIDE the address.  A dense corner block that
+// wraps past the end of its level (far faces of the grid only) takes the generic path.
+template <int MODE>
+__device__ __forceinline__ __half2 encode_level_fast(const Levels& lv, int l, const char* __restrict__ table_bytes,
+                                                     float x01, float y01, float z01)
+{
+    const float scale = lv.scale[l];
+    const uint32_t res = lv.res[l], size = lv.size[l];
+    const char* lb = table_bytes + ((size_t)lv.offset[l] << 2);
     const float px = rn_fma(scale, x01, 0.5f), py = rn_fma(scale, y01, 0.5f), pz = rn_fma(scale, z01, 0.5f);
     const float fx = floorf(px), fy = floorf(py), fz = floorf(pz);
     const float wx = rn_sub(px, fx), wy = rn_sub(py, fy), wz = rn_sub(pz, fz);
     const uint32_t gx = (uint32_t)(int)fx, gy = (uint32_t)(int)fy, gz = (uint32_t)(int)fz;
-    const uint32_t hy0 = gy * HG_PRIME_Y, hy1 = hy0 + HG_PRIME_Y;
-    const uint32_t hz0 = gz * HG_PRIME_Z, hz1 = hz0 + HG_PRIME_Z;
-    const uint32_t yz[4] = {hy0 ^ hz0, hy1 ^ hz0, hy0 ^ hz1, hy1 ^ hz1};
-    const uint32_t* lvl = table32 + offset;
-    const bool gx_odd = gx & 1u;
+    // per corner pair q = (cy, cz): byte offset of the aligned entry pair holding corner x0,
+    // whether x0 is its upper entry, and the byte offset of x1 when it lies outside the pair
+    uint32_t pair_off[4], x1_off[4];
+    bool odd[4];
+    if (MODE == 1) {
+        const uint32_t mask4 = (size - 1u) << 2, mask_pair = mask4 & ~7u;
+        const uint32_t gx4 = gx << 2, gx4n = gx4 + 4u;
+        const uint32_t hy0 = gy * (HG_PRIME_Y << 2), hy1 = hy0 + (HG_PRIME_Y << 2);
+        const uint32_t hz0 = gz * (HG_PRIME_Z << 2), hz1 = hz0 + (HG_PRIME_Z << 2);
+        const uint32_t yz4[4] = {hy0 ^ hz0, hy1 ^ hz0, hy0 ^ hz1, hy1 ^ hz1};
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            pair_off[q] = (gx4 ^ yz4[q]) & mask_pair;
+            odd[q] = ((gx4 ^ yz4[q]) & 4u) != 0u;
+            x1_off[q] = (gx4n ^ yz4[q]) & mask4;
+        }
+    } else {
+        const uint32_t s2 = res * res;
+        const uint32_t base = gx + gy * res + gz * s2;
+        if (base + 1u + res + s2 >= size)
+            return encode_level(reinterpret_cast<const __half2*>(table_bytes), lv, l, x01, y01, z01);
+        const uint32_t base4 = base << 2, r4 = res << 2, s4 = s2 << 2;
+        const uint32_t b0[4] = {base4, base4 + r4, base4 + s4, base4 + r4 + s4};
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            pair_off[q] = b0[q] & ~7u;
+            odd[q] = (b0[q] & 4u) != 0u;
+            x1_off[q] = b0[q] + 4u;
+        }
+    }
     uint32_t v[8];
 #pragma unroll
     for (int q = 0; q < 4; q++) {
-        const uint32_t i0 = (gx ^ yz[q]) & mask;
-        const uint2 e = __ldg(reinterpret_cast<const uint2*>(lvl + (i0 & ~1u)));
-        const bool odd = i0 & 1u;
-        v[2 * q] = odd ? e.y : e.x;
-        uint32_t other = odd ? e.x : e.y;
-        if (gx_odd) other = __ldg(lvl + (((gx + 1u) ^ yz[q]) & mask));
+        const uint2 e = __ldg(reinterpret_cast<const uint2*>(addr_plus_u32(lb, pair_off[q])));
+        v[2 * q] = odd[q] ? e.y : e.x;
+        uint32_t other = odd[q] ? e.x : e.y;
+        // x-neighbour outside the aligned pair: hashed level with odd gx / dense level with odd index
+        const bool split = (MODE == 1) ? ((gx & 1u) != 0u) : odd[q];
+        if (split) other = __ldg(reinterpret_cast<const uint32_t*>(addr_plus_u32(lb, x1_off[q])));
         v[2 * q + 1] = other;
     }
     const float ux = rn_sub(1.0f, wx), uy = rn_sub(1.0f, wy), uz = rn_sub(1.0f, wz);
@@ -185,4 +225,14 @@ __device__ __forceinline__ __half2 encode_level_hashed(const uint32_t* __restric
         a1 = rn_fma(w[c], f.y, a1);
     }
     return __floats2half2_rn(a0, a1);
+}
+
+// one level through whichever path its mode allows
+__device__ __forceinline__ __half2 encode_level_any(const Levels& lv, const char* __restrict__ table_bytes, int l,
+                                                    float x01, float y01, float z01)
+{
+    const uint32_t m = lv.mode[l];
+    if (m == 1u) return encode_level_fast<1>(lv, l, table_bytes, x01, y01, z01);
+    if (m == 0u) return encode_level_fast<0>(lv, l, table_bytes, x01, y01, z01);
+    return encode_level(reinterpret_cast<const __half2*>(table_bytes), lv, l, x01, y01, z01);
 }

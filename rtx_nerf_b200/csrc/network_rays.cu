@@ -14,6 +14,8 @@
 //     tcgen05 layers (a shared-memory mutex between the CTA's 4 warp-groups).  30 KB of shared
 //     memory per 512 threads leaves ~160 KB of the SM's L1 to the hash table.
 //   * weights stay resident in shared memory (UMMA K-major layout) for the CTA's lifetime.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "hashgrid.cuh"
 #include "mlp_tile.cuh"
@@ -35,19 +37,23 @@ __device__ __forceinline__ void wg_barrier(int wg)
     asm volatile("bar.sync %0, %1;" ::"r"(wg + 1), "n"(NET_TILE) : "memory");
 }
 
-// two levels at a time when both are hashed power-of-two levels (the expensive ones): the
-// body is branch-free so the 8-12 gathers of both levels are in flight together
+// Two levels at a time.  When both take the same straight-line fast path (the common case:
+// coarse levels dense, fine levels hashed) the gathers of both are in flight together.
 __device__ __forceinline__ void encode_pair(const Levels& lv, const uint32_t* __restrict__ table32, int l,
                                             float x01, float y01, float z01, uint32_t& f0, uint32_t& f1)
 {
+    const char* tb = reinterpret_cast<const char*>(table32);
     __half2 h0 = __floats2half2_rn(0.f, 0.f), h1 = h0;
-    if (l + 1 < lv.n_levels && lv.mode[l] == 1u && lv.mode[l + 1] == 1u) {
-        h0 = encode_level_hashed(table32, lv.scale[l], lv.size[l] - 1u, lv.offset[l], x01, y01, z01);
-        h1 = encode_level_hashed(table32, lv.scale[l + 1], lv.size[l + 1] - 1u, lv.offset[l + 1], x01, y01, z01);
+    const bool two = l + 1 < lv.n_levels;
+    if (two && lv.mode[l] == 1u && lv.mode[l + 1] == 1u) {
+        h0 = encode_level_fast<1>(lv, l, tb, x01, y01, z01);
+        h1 = encode_level_fast<1>(lv, l + 1, tb, x01, y01, z01);
+    } else if (two && lv.mode[l] == 0u && lv.mode[l + 1] == 0u) {
+        h0 = encode_level_fast<0>(lv, l, tb, x01, y01, z01);
+        h1 = encode_level_fast<0>(lv, l + 1, tb, x01, y01, z01);
     } else {
-        if (l < lv.n_levels) h0 = encode_level(reinterpret_cast<const __half2*>(table32), lv, l, x01, y01, z01);
-        if (l + 1 < lv.n_levels)
-            h1 = encode_level(reinterpret_cast<const __half2*>(table32), lv, l + 1, x01, y01, z01);
+        if (l < lv.n_levels) h0 = encode_level_any(lv, tb, l, x01, y01, z01);
+        if (two) h1 = encode_level_any(lv, tb, l + 1, x01, y01, z01);
     }
     f0 = *reinterpret_cast<const uint32_t*>(&h0);
     f1 = *reinterpret_cast<const uint32_t*>(&h1);
@@ -200,17 +206,21 @@ extern "C" int rtxnerf_network_forward_rays(const rtxnerf_hashgrid* enc, const r
     if (rc) return rc;
     if (enc->n_levels * 2 > NET_IN) return RTXNERF_ECONFIG;
     if (n_rays == 0) return RTXNERF_OK;
-    constexpr int MIN_CTAS = 2;
-    auto kern = network_forward_rays_kernel<MIN_CTAS>;
-    static bool attr_set = false;
-    if (!attr_set) {
-        RTX_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, NetRSmem::BYTES));
-        attr_set = true;
+    // 2 CTAs x 512 threads per SM (64 registers) measured faster than 3 (40 registers, spills)
+    static int min_ctas = 0;
+    if (!min_ctas) {
+        const char* e = getenv("RTXNERF_NETR_CTAS");   // development knob
+        min_ctas = (e && e[0] == '3') ? 3 : 2;
+        RTX_CUDA_TRY(cudaFuncSetAttribute(network_forward_rays_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          NetRSmem::BYTES));
+        RTX_CUDA_TRY(cudaFuncSetAttribute(network_forward_rays_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          NetRSmem::BYTES));
     }
     const long long groups = ((long long)n_rays + 31) / 32;
     long long blocks = (groups + NETR_WGS - 1) / NETR_WGS;
-    const long long resident = (long long)RTX_NUM_SMS * MIN_CTAS;
+    const long long resident = (long long)RTX_NUM_SMS * min_ctas;
     if (blocks > resident) blocks = resident;
+    auto kern = min_ctas == 3 ? network_forward_rays_kernel<3> : network_forward_rays_kernel<2>;
     kern<<<(unsigned)blocks, NETR_THREADS, NetRSmem::BYTES, (cudaStream_t)stream>>>(
         lv, reinterpret_cast<const uint32_t*>(enc->table), mlp->weights, d_samples, sample_stride,
         mlp->out_activation, d_num_hits, d_indices, n_rays, samples_per_segment, d_out16, d_radiance4);
