@@ -1,0 +1,3 @@
+// compat/optix_types.h — intentionally empty: see compat/optix.h (not OptiX).
+#pragma once
+#include "optix.h"

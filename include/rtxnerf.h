@@ -222,11 +222,45 @@ int rtxnerf_network_forward(const rtxnerf_hashgrid* enc, const rtxnerf_mlp* mlp,
  * (sample (j,i) of ray x at row (indices[x]+j)*S+i, sampler/sampler.cu:60-64): a warp covers 32
  * neighbouring rays at one sample slot, so its hash-table gathers coalesce.  Results are
  * identical to rtxnerf_network_forward on the same rows; rows not covered by
- * (num_hits, indices) are not written.  This is what the render pipeline calls. */
+ * (num_hits, indices) are not written.  This is what the render pipeline calls.
+ * d_encoded_out (optional): fp16 [n][32] encoded features, kept by a TRAINING forward
+ * (network->forward(..., prepare_input_gradients), main.cu:721) for the backward pass. */
 int rtxnerf_network_forward_rays(const rtxnerf_hashgrid* enc, const rtxnerf_mlp* mlp,
                                  const float* d_samples, int sample_stride, const int* d_num_hits,
                                  const int* d_indices, int n_rays, int samples_per_segment,
-                                 uint16_t* d_out16, float* d_radiance4, void* stream);
+                                 uint16_t* d_out16, float* d_radiance4, uint16_t* d_encoded_out,
+                                 void* stream);
+
+/* ------------------------------------------------------------------------------------
+ * Training step — replaces network->backward (main.cu:781), loss->evaluate + reduce_sum
+ * (main.cu:755-760) and optimizer->step (main.cu:787) of tiny-cuda-nn (absent from the
+ * archive; restated, PARITY UNPINNED).  Gradients are fp32 and ACCUMULATE into caller-owned,
+ * caller-zeroed buffers (rtxnerf_adam_step re-zeroes them), so that one NCCL all-reduce of
+ * [grad_table | grad_weights] is the only exchange of a data-parallel step.
+ * ---------------------------------------------------------------------------------- */
+
+/* d_dl_dradiance: fp16 [n][4], what launch_volrender_backward_cuda wrote (the wiring the driver
+ * intends at main.cu:765-780, Q5).  d_encoded: the training forward's features.  d_dencoded:
+ * fp16 [n][32] scratch (dL/d features, written then scattered).  Rows: n = min(n_max,
+ * *d_count * samples_per_segment) in CSR order.  grad_table: fp32 [entries][2]; grad_weights:
+ * fp32, same layout as rtxnerf_mlp.weights. */
+int rtxnerf_network_backward_rays(const rtxnerf_hashgrid* enc, const rtxnerf_mlp* mlp,
+                                  const float* d_samples, int sample_stride, const uint16_t* d_encoded,
+                                  const uint16_t* d_dl_dradiance, const int* d_num_hits,
+                                  const int* d_indices, int n_rays, int samples_per_segment,
+                                  const long long* d_count, long long n_max, uint16_t* d_dencoded,
+                                  float* d_grad_table, float* d_grad_weights, void* stream);
+
+/* values[i] = (pred-target)^2 / n (optional), gradients[i] = fp16(loss_scale * 2 (pred-target) / n),
+ * *d_loss_sum += sum(values) (optional, caller-zeroed).  n = batch_size * 3. */
+int rtxnerf_l2_loss(const float* d_pred, const float* d_target, long long n, float loss_scale,
+                    float* d_values, uint16_t* d_gradients, float* d_loss_sum, void* stream);
+
+/* Adam over n parameters: g = grads * grad_scale (1 / (loss_scale * ranks)); grads are zeroed;
+ * master (fp32) and params (fp16 copy) updated; step counts from 1 (bias correction). */
+int rtxnerf_adam_step(long long n, float* d_master, uint16_t* d_params, float* d_grads, float* d_m1,
+                      float* d_m2, float grad_scale, float lr, float beta1, float beta2, float eps,
+                      int step, void* stream);
 
 #ifdef __cplusplus
 }

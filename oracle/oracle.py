@@ -283,6 +283,58 @@ def mlp_forward(weights_h, in_dim, width, n_hidden, out_activation, x_h, nthread
     return out16.view(np.float16), rad
 
 
+def mlp_backward(weights_h, out_activation, enc_h, dl_dradiance_h):
+    """-> (dEnc fp16 [n][32], grad_w float64 [7168]) for the 32->64->64->16 network."""
+    w = np.ascontiguousarray(weights_h, np.float16).view(np.uint16)
+    enc = np.ascontiguousarray(enc_h, np.float16).view(np.uint16)
+    g = np.ascontiguousarray(dl_dradiance_h, np.float16).view(np.uint16)
+    n = enc.shape[0]
+    d_enc = np.zeros((n, 32), np.uint16)
+    gw = np.zeros(w.size, np.float64)
+    lib().orc_mlp_backward(_ptr(w, _u16p), C.c_int(out_activation), _ptr(enc, _u16p), _ptr(g, _u16p),
+                           C.c_longlong(n), _ptr(d_enc, _u16p), _ptr(gw, C.POINTER(C.c_double)))
+    return d_enc.view(np.float16), gw
+
+
+def hashgrid_backward(levels, samples, d_enc_h):
+    """-> grad_table float64 [n_entries][2]."""
+    L = levels["n_levels"]
+    sc = np.ascontiguousarray(levels["scale"], np.float32)
+    rs = np.ascontiguousarray(levels["res"], np.uint32)
+    sz = np.ascontiguousarray(levels["size"], np.uint32)
+    off = np.ascontiguousarray(levels["offset"], np.int64)
+    samples = np.ascontiguousarray(samples, np.float32)
+    d_enc = np.ascontiguousarray(d_enc_h, np.float16).view(np.uint16)
+    gt = np.zeros((int(levels["n_entries"]), 2), np.float64)
+    u32p = C.POINTER(C.c_uint32)
+    lib().orc_hashgrid_backward(C.c_int(L), _ptr(sc, _f32p), _ptr(rs, u32p), _ptr(sz, u32p),
+                                _ptr(off, C.POINTER(C.c_longlong)), _ptr(samples, _f32p),
+                                C.c_int(samples.shape[1]), C.c_longlong(samples.shape[0]), _ptr(d_enc, _u16p),
+                                _ptr(gt, C.POINTER(C.c_double)))
+    return gt
+
+
+def l2_loss(pred, target, loss_scale=1.0):
+    """tcnn L2 loss as called at main.cu:755-760: values, fp16 gradients, scalar sum."""
+    pred = np.asarray(pred, np.float32).reshape(-1)
+    target = np.asarray(target, np.float32).reshape(-1)
+    n = np.float32(pred.size)
+    diff = pred - target
+    values = diff * diff / n
+    grads = (np.float32(loss_scale) * np.float32(2.0) * diff / n).astype(np.float16)
+    return values, grads, float(values.astype(np.float64).sum())
+
+
+def adam_step(master, grads, m1, m2, grad_scale, lr, beta1, beta2, eps, step):
+    """tcnn Adam as configured at main.cu:40-46; returns (master, fp16 params, m1, m2)."""
+    g = np.asarray(grads, np.float32) * np.float32(grad_scale)
+    m1 = np.float32(beta1) * m1 + np.float32(1 - beta1) * g
+    m2 = np.float32(beta2) * m2 + np.float32(1 - beta2) * g * g
+    lr_t = np.float32(lr * np.sqrt(1.0 - beta2 ** step) / (1.0 - beta1 ** step))
+    master = (master - lr_t * m1 / (np.sqrt(m2) + np.float32(eps))).astype(np.float32)
+    return master, master.astype(np.float16), m1.astype(np.float32), m2.astype(np.float32)
+
+
 # --------------------------------------------------------------------------- the reference itself, on the host
 def ref_ray_march(look_at, focal, aspect, W, H, G, aabb, arr_size, rays=None):
     """The reference's own OptiX programs over the emulated runtime (oracle/host_shim/optix.h)."""

@@ -635,3 +635,106 @@ void orc_mlp_forward(const uint16_t* weights, int in_dim, int width, int n_hidde
     }
     free(wf);
 }
+
+/* ---------------------------------------------------------------------------------------
+ * Training step restatements (tiny-cuda-nn network->backward main.cu:781, loss->evaluate
+ * main.cu:755-760, optimizer->step main.cu:787 — tcnn absent: PARITY UNPINNED).  They follow
+ * the rounding points of the CUDA path (fp16 activations / activation gradients, wide
+ * accumulation) so that the comparison tolerance only has to absorb summation order.
+ * ------------------------------------------------------------------------------------- */
+void orc_mlp_backward(const uint16_t* weights, int out_activation, const uint16_t* enc,
+                      const uint16_t* dl_dradiance, long long n, uint16_t* d_enc, double* grad_w)
+{
+    enum { IN = 32, W = 64, OUT = 16 };
+    const size_t o1 = (size_t)W * IN, o2 = o1 + (size_t)W * W, wsz = o2 + (size_t)OUT * W;
+    float* wf = (float*)malloc(sizeof(float) * wsz);
+    for (size_t i = 0; i < wsz; i++) wf[i] = orc_h2f(weights[i]);
+    const float *w0 = wf, *w1 = wf + o1, *w2 = wf + o2;
+    memset(grad_w, 0, sizeof(double) * wsz);
+    for (long long s = 0; s < n; s++) {
+        float a0[IN], h1[W], h2[W], dout[OUT], dh2[W], dh1[W];
+        for (int k = 0; k < IN; k++) a0[k] = orc_h2f(enc[(size_t)s * IN + k]);
+        for (int r = 0; r < W; r++) {
+            double acc = 0.0;
+            for (int k = 0; k < IN; k++) acc += (double)w0[r * IN + k] * a0[k];
+            float v = (float)acc;
+            h1[r] = orc_h2f(orc_f2h(v > 0.f ? v : 0.f));
+        }
+        for (int r = 0; r < W; r++) {
+            double acc = 0.0;
+            for (int k = 0; k < W; k++) acc += (double)w1[r * W + k] * h1[k];
+            float v = (float)acc;
+            h2[r] = orc_h2f(orc_f2h(v > 0.f ? v : 0.f));
+        }
+        for (int r = 0; r < OUT; r++) {
+            dout[r] = 0.f;
+            if (r >= 4) continue;
+            double acc = 0.0;
+            for (int k = 0; k < W; k++) acc += (double)w2[r * W + k] * h2[k];
+            float da = 1.0f;
+            if (out_activation == 1) {
+                float sg = 1.0f / (1.0f + expf(-(float)acc));
+                da = sg * (1.0f - sg);
+            }
+            dout[r] = orc_h2f(orc_f2h(orc_h2f(dl_dradiance[(size_t)s * 4 + r]) * da));
+        }
+        for (int r = 0; r < OUT; r++)
+            for (int k = 0; k < W; k++) grad_w[o2 + (size_t)r * W + k] += (double)dout[r] * h2[k];
+        for (int k = 0; k < W; k++) {
+            double acc = 0.0;
+            for (int r = 0; r < OUT; r++) acc += (double)dout[r] * w2[r * W + k];
+            dh2[k] = orc_h2f(orc_f2h(h2[k] > 0.f ? (float)acc : 0.f));
+        }
+        for (int r = 0; r < W; r++)
+            for (int k = 0; k < W; k++) grad_w[o1 + (size_t)r * W + k] += (double)dh2[r] * h1[k];
+        for (int k = 0; k < W; k++) {
+            double acc = 0.0;
+            for (int r = 0; r < W; r++) acc += (double)dh2[r] * w1[r * W + k];
+            dh1[k] = orc_h2f(orc_f2h(h1[k] > 0.f ? (float)acc : 0.f));
+        }
+        for (int r = 0; r < W; r++)
+            for (int k = 0; k < IN; k++) grad_w[(size_t)r * IN + k] += (double)dh1[r] * a0[k];
+        for (int k = 0; k < IN; k++) {
+            double acc = 0.0;
+            for (int r = 0; r < W; r++) acc += (double)dh1[r] * w0[r * IN + k];
+            d_enc[(size_t)s * IN + k] = orc_f2h((float)acc);
+        }
+    }
+    free(wf);
+}
+
+/* dL/d table: every sample adds w_corner * dEnc[level] to its 8 corner entries (F = 2). */
+void orc_hashgrid_backward(int L, const float* scales, const uint32_t* ress, const uint32_t* sizes,
+                           const long long* offsets, const float* samples, int sample_stride,
+                           long long n, const uint16_t* d_enc, double* grad_table)
+{
+    for (long long s = 0; s < n; s++) {
+        const float* p = samples + (size_t)s * sample_stride;
+        float x01[3];
+        for (int k = 0; k < 3; k++) x01[k] = fmaf(p[k], 0.5f, 0.5f);
+        for (int l = 0; l < L; l++) {
+            float g0 = orc_h2f(d_enc[(size_t)s * L * 2 + (size_t)l * 2]);
+            float g1 = orc_h2f(d_enc[(size_t)s * L * 2 + (size_t)l * 2 + 1]);
+            float frac[3];
+            uint32_t g[3];
+            for (int k = 0; k < 3; k++) {
+                float pos = fmaf(scales[l], x01[k], 0.5f);
+                float fl = floorf(pos);
+                frac[k] = pos - fl;
+                g[k] = (uint32_t)(int)fl;
+            }
+            for (int c = 0; c < 8; c++) {
+                float w = 1.0f;
+                uint32_t q[3];
+                for (int k = 0; k < 3; k++) {
+                    if (c & (1 << k)) { w *= frac[k]; q[k] = g[k] + 1u; }
+                    else { w *= 1.0f - frac[k]; q[k] = g[k]; }
+                }
+                uint32_t idx = grid_index(q[0], q[1], q[2], ress[l], sizes[l]);
+                double* e = grad_table + ((size_t)offsets[l] + idx) * 2;
+                e[0] += (double)(w * g0);
+                e[1] += (double)(w * g1);
+            }
+        }
+    }
+}

@@ -142,6 +142,15 @@ void orc_mlp_forward(const uint16_t* weights, int in_dim, int width, int n_hidde
                      const uint16_t* in, long long n, uint16_t* out16, float* radiance4,
                      int nthreads);
 
+/* Training-step restatements (tcnn backward / L2 loss / Adam: PARITY UNPINNED).  32 -> 64 -> 64
+ * -> 16 network only.  grad_w: double, layout of `weights`; grad_table: double [entries][2],
+ * caller-zeroed (accumulates). */
+void orc_mlp_backward(const uint16_t* weights, int out_activation, const uint16_t* enc,
+                      const uint16_t* dl_dradiance, long long n, uint16_t* d_enc, double* grad_w);
+void orc_hashgrid_backward(int L, const float* scales, const uint32_t* ress, const uint32_t* sizes,
+                           const long long* offsets, const float* samples, int sample_stride,
+                           long long n, const uint16_t* d_enc, double* grad_table);
+
 /* fp16 helpers (round-to-nearest-even), exported for the tests. */
 uint16_t orc_f2h(float f);
 float    orc_h2f(uint16_t h);

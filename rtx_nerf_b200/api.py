@@ -278,8 +278,13 @@ class Network:
     def __init__(self, levels, table_h, weights_h, in_dim=32, width=64, n_hidden=2, out_activation=1,
                  device="cuda"):
         self.levels = levels
-        self.table = torch.as_tensor(np.ascontiguousarray(table_h, np.float16)).to(device)
-        self.weights = torch.as_tensor(np.ascontiguousarray(weights_h, np.float16)).to(device)
+        # one flat fp16 parameter buffer [table | weights] (the reference keeps all tcnn parameters
+        # in one buffer too, main.cu:328-342): a training step all-reduces / updates it in one go
+        t = np.ascontiguousarray(table_h, np.float16).reshape(-1)
+        w = np.ascontiguousarray(weights_h, np.float16).reshape(-1)
+        self.params = torch.as_tensor(np.concatenate([t, w])).to(device)
+        self.table = self.params[:t.size]
+        self.weights = self.params[t.size:]
         self.in_dim, self.width, self.n_hidden, self.out_activation = in_dim, width, n_hidden, out_activation
         hg = _lib.HashGrid()
         hg.table = self.table.data_ptr()
@@ -324,7 +329,7 @@ class Network:
         return output if output is not None else radiance
 
     def forward_rays(self, stream, samples, num_hits, indices, n_rays, samples_per_segment, output=None,
-                     radiance=None):
+                     radiance=None, encoded_out=None):
         """Ray-coherent schedule of forward() over the sampler's CSR sample buffer: same rows,
         same results, gathers coalesced across neighbouring rays (network_rays.cu)."""
         if output is None and radiance is None:
@@ -332,7 +337,35 @@ class Network:
         _lib.check(_lib.load().rtxnerf_network_forward_rays(C.byref(self._hg), C.byref(self._mlp), _p(samples),
                                                             samples.shape[1], _p(num_hits), _p(indices),
                                                             int(n_rays), int(samples_per_segment), _p(output),
-                                                            _p(radiance), _stream_ptr(stream)),
+                                                            _p(radiance), _p(encoded_out), _stream_ptr(stream)),
                    "network_forward_rays")
         _lib.count_launches(1 if n_rays > 0 else 0)
         return output if output is not None else radiance
+
+    def backward_rays(self, stream, samples, encoded, dl_dradiance, num_hits, indices, n_rays,
+                      samples_per_segment, d_count, n_max, dencoded, grad_table, grad_weights):
+        """network->backward (main.cu:781) with the intended wiring (Q5): dl_dradiance is the fp16
+        [N][4] buffer of launch_volrender_backward_cuda.  Gradients accumulate (fp32)."""
+        _lib.check(_lib.load().rtxnerf_network_backward_rays(
+            C.byref(self._hg), C.byref(self._mlp), _p(samples), samples.shape[1], _p(encoded), _p(dl_dradiance),
+            _p(num_hits), _p(indices), int(n_rays), int(samples_per_segment), _p(d_count), int(n_max), _p(dencoded),
+            _p(grad_table), _p(grad_weights), _stream_ptr(stream)), "network_backward_rays")
+        _lib.count_launches(2 if n_rays > 0 and n_max > 0 else 0)
+
+
+def l2_loss(pred, target, loss_scale, gradients, values=None, loss_sum=None, stream=None):
+    """loss->evaluate + reduce_sum (main.cu:755-760): fp16 gradients, optional values / running sum."""
+    n = pred.numel()
+    _lib.check(_lib.load().rtxnerf_l2_loss(_p(pred), _p(target), int(n), float(loss_scale), _p(values), _p(gradients),
+                                           _p(loss_sum), _stream_ptr(stream)), "l2_loss")
+    _lib.count_launches(1 if n > 0 else 0)
+
+
+def adam_step(master, params, grads, m1, m2, grad_scale, step, lr=1e-3, beta1=0.9, beta2=0.999, eps=1e-8,
+              stream=None):
+    """optimizer->step (main.cu:787) with the Adam config of main.cu:40-46; zeroes grads."""
+    n = master.numel()
+    _lib.check(_lib.load().rtxnerf_adam_step(int(n), _p(master), _p(params), _p(grads), _p(m1), _p(m2),
+                                             float(grad_scale), float(lr), float(beta1), float(beta2), float(eps),
+                                             int(step), _stream_ptr(stream)), "adam_step")
+    _lib.count_launches(1 if n > 0 else 0)

@@ -46,5 +46,25 @@ def build(force=False, verbose=False):
     return OUT
 
 
+def build_compat_driver(force=False):
+    """tests/cpp/compat_driver: a C++ host program written against the reference's own headers
+    and call sequence, compiled with -Icompat and linked to librtxnerf_b200.so."""
+    root = os.path.dirname(HERE)
+    src = os.path.join(root, "tests", "cpp", "compat_driver.cu")
+    out = os.path.join(root, "tests", "cpp", "compat_driver")
+    deps = [src, OUT] + glob.glob(os.path.join(root, "compat", "**", "*.h"), recursive=True)
+    if not force and os.path.exists(out) and all(os.path.getmtime(d) <= os.path.getmtime(out) for d in deps):
+        return out
+    r = subprocess.run(["nvcc", "-std=c++17", "-O2", "-gencode", "arch=compute_100a,code=sm_100a",
+                        "-I", os.path.join(root, "compat"), "-I", root, src, "-o", out, "-L", HERE, "-lrtxnerf_b200",
+                        "-Xlinker", "-rpath", "-Xlinker", "$ORIGIN/../../rtx_nerf_b200"],
+                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT)
+    if r.returncode != 0:
+        sys.stderr.write(r.stdout.decode(errors="replace"))
+        raise RuntimeError("compat_driver build failed")
+    return out
+
+
 if __name__ == "__main__":
     print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    print(build_compat_driver(force="--force" in sys.argv))

@@ -64,7 +64,8 @@ __global__ void __launch_bounds__(NETR_THREADS, MIN_CTAS)
 network_forward_rays_kernel(Levels lv, const uint32_t* __restrict__ table32, const uint16_t* __restrict__ weights,
                             const float* __restrict__ samples, int stride, int out_activation,
                             const int* __restrict__ num_hits, const int* __restrict__ indices, int n_rays, int S,
-                            uint16_t* __restrict__ out16, float* __restrict__ radiance4)
+                            uint16_t* __restrict__ out16, float* __restrict__ radiance4,
+                            uint16_t* __restrict__ encoded_out)
 {
     extern __shared__ __align__(128) uint8_t smem[];
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + NetRSmem::BAR);
@@ -132,6 +133,12 @@ network_forward_rays_kernel(Levels lv, const uint32_t* __restrict__ table32, con
                         }
                 }
             }
+            if (encoded_out && valid) {   // training forward: keep the features for the backward pass
+                uint4* eo = reinterpret_cast<uint4*>(encoded_out + s * NET_IN);
+#pragma unroll
+                for (int c = 0; c < NET_IN / 8; c++)
+                    eo[c] = make_uint4(pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
+            }
             // ---- the three layers, holding the CTA's activation tile and TMEM columns
             if (wt == 0) {
                 while (atomicCAS(lock, 0, 1) != 0) __nanosleep(64);
@@ -194,7 +201,8 @@ network_forward_rays_kernel(Levels lv, const uint32_t* __restrict__ table32, con
 extern "C" int rtxnerf_network_forward_rays(const rtxnerf_hashgrid* enc, const rtxnerf_mlp* mlp,
                                             const float* d_samples, int sample_stride, const int* d_num_hits,
                                             const int* d_indices, int n_rays, int samples_per_segment,
-                                            uint16_t* d_out16, float* d_radiance4, void* stream)
+                                            uint16_t* d_out16, float* d_radiance4, uint16_t* d_encoded_out,
+                                            void* stream)
 {
     if (!enc || !mlp || !mlp->weights || !d_samples || !d_num_hits || !d_indices || (!d_out16 && !d_radiance4))
         return RTXNERF_EINVAL;
@@ -223,6 +231,6 @@ extern "C" int rtxnerf_network_forward_rays(const rtxnerf_hashgrid* enc, const r
     auto kern = min_ctas == 3 ? network_forward_rays_kernel<3> : network_forward_rays_kernel<2>;
     kern<<<(unsigned)blocks, NETR_THREADS, NetRSmem::BYTES, (cudaStream_t)stream>>>(
         lv, reinterpret_cast<const uint32_t*>(enc->table), mlp->weights, d_samples, sample_stride,
-        mlp->out_activation, d_num_hits, d_indices, n_rays, samples_per_segment, d_out16, d_radiance4);
+        mlp->out_activation, d_num_hits, d_indices, n_rays, samples_per_segment, d_out16, d_radiance4, d_encoded_out);
     return rtx_launch_status();
 }

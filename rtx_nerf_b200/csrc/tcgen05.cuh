@@ -104,3 +104,20 @@ __device__ __forceinline__ void tmem_ld_x16(uint32_t taddr, uint32_t (&r)[16])
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 }  // namespace tc
+
+// ---- descriptors with explicit operand majors ----------------------------------------------
+// The no-swizzle core-matrix tile the kernels keep in shared memory,
+//   elem(r, c) at (r>>3)*(C*16) + (c>>3)*128 + (r&7)*16 + (c&7)*2      (C columns, fp16)
+// serves BOTH majors (checked on the GPU by scripts/probes/umma_probe.cu):
+//   K-major  operand, rows = M/N index, cols = K:   LBO = 128,   SBO = C*16
+//   MN-major operand, rows = K index, cols = M/N:   LBO = C*16,  SBO = 128
+// so an activation tile [sample][feature] is the K-major A of a forward/dgrad layer and, read
+// MN-major, the A or B of a weight-gradient product over the 128 samples; a weight tile
+// [out][in] is the K-major B of the forward layer and the MN-major B of its dgrad.
+namespace tc {
+__host__ __device__ constexpr uint32_t idesc_f16_f32_major(int M, int N, int a_mn_major, int b_mn_major)
+{
+    return (1u << 4) | ((uint32_t)a_mn_major << 15) | ((uint32_t)b_mn_major << 16) | ((uint32_t)(N >> 3) << 17) |
+           ((uint32_t)(M >> 4) << 24);
+}
+}  // namespace tc

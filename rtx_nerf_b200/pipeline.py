@@ -108,3 +108,94 @@ class NetworkRadiance:
         else:
             self.net.forward(None, r.samples, radiance=r.radiance, n=r.N_cap, d_count=r.hits.total_hits,
                              count_scale=r.S, impl=self.impl)
+
+
+class Trainer:
+    """One data-parallel training step of the reference's loop (main.cu:612-805) on this rank's
+    rays: march -> sampler -> network forward (features kept) -> compositing -> L2 loss ->
+    compositing backward -> network backward -> [all-reduce of the flat fp32 gradient buffer]
+    -> Adam.  Every buffer is allocated once; the step is 12 kernel launches plus the collective.
+
+    Rays of a step are a contiguous range of one view (ray_begin, n_rays); ranks take different
+    views/ranges.  Weights stay replicated: every rank applies the same Adam step to the same
+    summed gradient — the all-reduce is the only exchange."""
+
+    def __init__(self, grid, network, width, height, focal_length, aspect_ratio, samples_per_segment, max_hits,
+                 n_rays, loss_scale=128.0, lr=1e-3, process_group=None, device="cuda"):
+        self.net, self.S, self.R = network, int(samples_per_segment), int(n_rays)
+        self.loss_scale, self.lr = float(loss_scale), float(lr)
+        self.pg = process_group
+        self.world = 1
+        if process_group is not None:
+            import torch.distributed as dist
+            self.world = dist.get_world_size(process_group)
+        self.view = ViewRenderer(grid, width, height, focal_length, aspect_ratio, samples_per_segment, max_hits,
+                                 _EncodedNetworkRadiance(self), n_rays=n_rays, ray_begin=0, device=device)
+        v = self.view
+        dev = torch.device(device)
+        N = v.N_cap
+        self.encoded = torch.empty((N, 32), dtype=torch.float16, device=dev)
+        self.dencoded = torch.empty((N, 32), dtype=torch.float16, device=dev)
+        self.radiance_grad = torch.empty((N, 4), dtype=torch.float16, device=dev)
+        self.target = torch.empty((self.R, 3), dtype=torch.float32, device=dev)
+        self.loss_grad = torch.empty((self.R, 3), dtype=torch.float16, device=dev)
+        self.loss_sum = torch.zeros(1, dtype=torch.float32, device=dev)
+        n_params = network.params.numel()
+        self.n_table = network.table.numel()
+        self.grads = torch.zeros(n_params, dtype=torch.float32, device=dev)      # [table | weights], all-reduced
+        self.master = network.params.float()                                       # fp32 master (main.cu:331)
+        self.m1 = torch.zeros(n_params, dtype=torch.float32, device=dev)
+        self.m2 = torch.zeros(n_params, dtype=torch.float32, device=dev)
+        self.step_count = 0
+
+    def forward(self):
+        v = self.view
+        v.stage_march()
+        v.stage_sampler()
+        v.stage_radiance()
+        v.stage_composite()
+
+    def backward(self):
+        v, h = self.view, self.view.hits
+        api.l2_loss(v.pixels, self.target, self.loss_scale, self.loss_grad, loss_sum=self.loss_sum)
+        api.launch_volrender_backward_cuda(None, self.loss_grad, v.radiance, v.t_vals, h.num_hits, h.indices,
+                                           self.R, self.S, self.radiance_grad)
+        self.net.backward_rays(None, v.samples, self.encoded, self.radiance_grad, h.num_hits, h.indices, self.R,
+                               self.S, h.total_hits, v.N_cap, self.dencoded, self.grads[:self.n_table],
+                               self.grads[self.n_table:])
+
+    def allreduce(self):
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.all_reduce(self.grads, op=dist.ReduceOp.SUM, group=self.pg)
+
+    def optimizer_step(self):
+        self.step_count += 1
+        api.adam_step(self.master, self.net.params, self.grads, self.m1, self.m2,
+                      1.0 / (self.loss_scale * self.world), self.step_count, lr=self.lr)
+
+    def step(self, pose_dev, ray_begin, target_dev):
+        """pose (16 floats) and target pixels [n_rays][3] already on the device."""
+        v = self.view
+        v.pose_dev.copy_(pose_dev, non_blocking=True)
+        v.ray_begin = int(ray_begin)
+        self.target.copy_(target_dev, non_blocking=True)
+        self.forward()
+        self.backward()
+        self.allreduce()
+        self.optimizer_step()
+
+    launches_per_step = 3 + 1 + 1 + 1 + 1 + 1 + 2 + 1
+
+
+class _EncodedNetworkRadiance:
+    """Training forward: NetworkRadiance that also keeps the encoded features."""
+    needs_cells = False
+    launches = 1
+
+    def __init__(self, trainer):
+        self.t = trainer
+
+    def __call__(self, r):
+        self.t.net.forward_rays(None, r.samples, r.hits.num_hits, r.hits.indices, r.R, r.S, radiance=r.radiance,
+                                encoded_out=self.t.encoded)

@@ -1,0 +1,163 @@
+"""GPU tests of the training-step kernels through the C ABI against the CPU oracle:
+network backward (tcgen05 dgrad + TMEM-resident weight gradients + hash-table scatter),
+L2 loss, Adam, and the whole step of pipeline.Trainer.  tiny-cuda-nn is absent from the
+reference archive, so the oracle restates the published algorithms: PARITY UNPINNED.
+Tolerances (fp16 activation gradients, fp32 atomics in arbitrary order) are stated per check."""
+import numpy as np
+import pytest
+
+from rtx_nerf_b200 import synth
+
+pytestmark = [pytest.mark.gpu, pytest.mark.timeout(600)]
+
+
+def _t(a):
+    import torch
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def _net(api, seed=0, out_activation=1, table_scale=1.0):
+    lv = synth.hashgrid_levels()
+    rng = np.random.default_rng(seed)
+    table = (rng.uniform(-1, 1, lv["n_entries"] * 2) * table_scale).astype(np.float16)
+    w = synth.mlp_weights(seed=seed + 1)
+    return api.Network(lv, table, w, out_activation=out_activation), lv, table, w
+
+
+def _rays(n_rays, S, seed, max_h=6):
+    rng = np.random.default_rng(seed)
+    nh = rng.integers(0, max_h + 1, n_rays).astype(np.int32)
+    idx = np.concatenate([[0], np.cumsum(nh)[:-1]]).astype(np.int32)
+    n = int(nh.sum()) * S
+    s = np.zeros((n, 5), np.float32)
+    s[:, :3] = rng.uniform(-1, 1, (n, 3))
+    return nh, idx, n, s
+
+
+@pytest.mark.parametrize("n_rays,S,act", [(40, 4, 1), (333, 3, 1), (130, 4, 0)])
+def test_network_backward_vs_oracle(cuda_api, orc, n_rays, S, act):
+    import torch
+    net, lv, table, w = _net(cuda_api, seed=n_rays, out_activation=act)
+    nh, idx, n, s = _rays(n_rays, S, seed=S + n_rays)
+    rng = np.random.default_rng(5)
+    g = (rng.uniform(-1, 1, (n, 4)) * 0.05).astype(np.float16)
+    ds, dnh, didx = _t(s), _t(nh), _t(idx)
+    enc = torch.zeros((n, 32), dtype=torch.float16, device="cuda")
+    rad = torch.zeros((n, 4), dtype=torch.float32, device="cuda")
+    net.forward_rays(None, ds, dnh, didx, n_rays, S, radiance=rad, encoded_out=enc)
+    torch.cuda.synchronize()
+    enc_h = enc.cpu().numpy()
+    assert np.array_equal(enc_h.view(np.uint16), orc.hashgrid_encode(lv, table, s).view(np.uint16)), \
+        "training forward must store exactly the encoded features"
+    dencoded = torch.full((n, 32), 7.0, dtype=torch.float16, device="cuda")
+    gt = torch.zeros((lv["n_entries"], 2), dtype=torch.float32, device="cuda")
+    gw = torch.zeros(w.size, dtype=torch.float32, device="cuda")
+    cnt = torch.tensor([int(nh.sum())], dtype=torch.int64, device="cuda")
+    net.backward_rays(None, ds, enc, _t(g), dnh, didx, n_rays, S, cnt, n, dencoded, gt, gw)
+    torch.cuda.synchronize()
+    de_o, gw_o = orc.mlp_backward(w, act, enc_h, g)
+    de = dencoded.cpu().numpy().astype(np.float32)
+    # dL/d features: same fp16 inputs, fp32 tensor-core sums vs double sums, one fp16 rounding
+    scale = np.abs(de_o.astype(np.float32)).max()
+    assert scale > 0
+    np.testing.assert_allclose(de, de_o.astype(np.float32), rtol=4e-3, atol=2e-3 * scale)
+    # weight gradients: fp32 TMEM accumulation over all samples vs double
+    np.testing.assert_allclose(gw.cpu().numpy(), gw_o, rtol=0, atol=2e-3 * np.abs(gw_o).max())
+    assert np.abs(gw_o[:64 * 32]).max() > 0 and np.abs(gw_o[64 * 32 + 64 * 64:]).max() > 0
+    # table gradient: the scatter is checked on the GPU's own dL/d features (isolates the kernel)
+    gt_o = orc.hashgrid_backward(lv, s, dencoded.cpu().numpy())
+    np.testing.assert_allclose(gt.cpu().numpy(), gt_o, rtol=0, atol=1e-4 * np.abs(gt_o).max())
+    assert np.count_nonzero(gt_o) > 0
+    # gradients accumulate: a second call doubles them
+    net.backward_rays(None, ds, enc, _t(g), dnh, didx, n_rays, S, cnt, n, dencoded, gt, gw)
+    torch.cuda.synchronize()
+    np.testing.assert_allclose(gw.cpu().numpy(), 2 * gw_o, rtol=0, atol=4e-3 * np.abs(gw_o).max())
+
+
+def test_l2_loss_and_adam_vs_oracle(cuda_api, orc):
+    import torch
+    api = cuda_api
+    rng = np.random.default_rng(1)
+    pred = rng.random((1000, 3), dtype=np.float32)
+    target = rng.random((1000, 3), dtype=np.float32)
+    grads = torch.zeros((1000, 3), dtype=torch.float16, device="cuda")
+    values = torch.zeros((1000, 3), dtype=torch.float32, device="cuda")
+    total = torch.zeros(1, dtype=torch.float32, device="cuda")
+    api.l2_loss(_t(pred), _t(target), 128.0, grads, values=values, loss_sum=total)
+    torch.cuda.synchronize()
+    vo, go, so = orc.l2_loss(pred, target, 128.0)
+    np.testing.assert_allclose(values.cpu().numpy().reshape(-1), vo, rtol=1e-6, atol=0)
+    assert np.abs(grads.cpu().numpy().reshape(-1).view(np.uint16).astype(np.int32) - go.view(np.uint16).astype(np.int32)).max() <= 1
+    assert abs(float(total.item()) - so) < 1e-5 * so
+    n = 5000
+    master = rng.normal(0, 0.1, n).astype(np.float32)
+    m1 = np.zeros(n, np.float32)
+    m2 = np.zeros(n, np.float32)
+    dm, dp = _t(master), torch.zeros(n, dtype=torch.float16, device="cuda")
+    d1, d2 = _t(m1), _t(m2)
+    for step in (1, 2, 3):
+        g = (rng.normal(0, 1, n) * 64).astype(np.float32)
+        dg = _t(g)
+        api.adam_step(dm, dp, dg, d1, d2, 1.0 / 128.0, step)
+        torch.cuda.synchronize()
+        master, p16, m1, m2 = orc.adam_step(master, g, m1, m2, 1.0 / 128.0, 1e-3, 0.9, 0.999, 1e-8, step)
+        np.testing.assert_allclose(dm.cpu().numpy(), master, rtol=0, atol=2e-6)
+        assert np.all(dg.cpu().numpy() == 0.0), "Adam must zero the gradient buffer"
+        np.testing.assert_allclose(dp.cpu().numpy().astype(np.float32), p16.astype(np.float32), rtol=0, atol=2e-3)
+
+
+def test_trainer_step_gradients_vs_oracle_and_loss_decreases(cuda_api, orc):
+    """BASELINE configs[3] in miniature: the whole step against the oracle chain, then a few
+    Adam steps on a fixed batch must reduce the loss."""
+    import torch
+    from rtx_nerf_b200 import pipeline
+    api = cuda_api
+    G, W, H, S, HM, R = 128, 64, 48, 4, 8, 64 * 24
+    occ = synth.occupancy_lego(G)
+    net, lv, table, w = _net(api, seed=9, table_scale=0.5)
+    grid = api.OccupancyGrid.from_occupancy(occ, G)
+    focal = synth.focal_length()
+    pose = synth.poses(1, seed=4)[0]
+    tr = pipeline.Trainer(grid, net, W, H, focal, W / H, S, HM, R, loss_scale=1024.0, lr=1e-2)
+    rng = np.random.default_rng(3)
+    target = rng.random((R, 3), dtype=np.float32)
+    ray_begin = 64 * 10
+    v = tr.view
+    v.pose_dev.copy_(_t(pose.reshape(16)))
+    v.ray_begin = ray_begin
+    tr.target.copy_(_t(target))
+    tr.forward()
+    tr.backward()
+    torch.cuda.synchronize()
+    # oracle chain on the same rays
+    ora = orc.ray_march_dda(pose, focal, W / H, W, H, occ, G, max_hits=HM, csr=True, rays=(ray_begin, ray_begin + R))
+    # the oracle indexes by global ray; rays outside the range have no hits, so the slice is the local CSR
+    nh, idx, vd = ora.num_hits[ray_begin:ray_begin + R], ora.indices[ray_begin:ray_begin + R], ora.view_dirs[ray_begin:ray_begin + R]
+    assert np.array_equal(v.hits.num_hits.cpu().numpy(), nh)
+    so, to = orc.sampler(ora.start_points, ora.end_points, vd, nh, idx, S)
+    enc = orc.hashgrid_encode(lv, table, so)
+    _, rad = orc.mlp_forward(w, 32, 64, 2, 1, enc)
+    px = orc.volrender(rad, nh, idx, to, S)
+    vals, lg, loss = orc.l2_loss(px, target, 1024.0)
+    n = so.shape[0]
+    assert abs(float(tr.loss_sum.item()) - loss) < 2e-3 * loss
+    rg = orc.volrender_backward(lg.reshape(-1, 3), rad, to, nh, idx, S)
+    de, gw = orc.mlp_backward(w, 1, enc, rg)
+    gt = orc.hashgrid_backward(lv, so, de)
+    g = tr.grads.cpu().numpy()
+    nt = lv["n_entries"] * 2
+    # end-to-end tolerance: RGB differs by <= 1e-3 (north_star) before the loss gradient is taken,
+    # the radiance differs in the last fp16 bit; 2 % of the largest gradient covers both
+    np.testing.assert_allclose(g[nt:], gw, rtol=0, atol=2e-2 * np.abs(gw).max())
+    np.testing.assert_allclose(g[:nt].reshape(-1, 2), gt, rtol=0, atol=2e-2 * np.abs(gt).max())
+    assert np.abs(gw).max() > 0 and np.abs(gt).max() > 0
+    # a few optimizer steps on the same batch
+    tr.grads.zero_()
+    losses = []
+    for _ in range(6):
+        tr.loss_sum.zero_()
+        tr.step(_t(pose.reshape(16)), ray_begin, _t(target))
+        torch.cuda.synchronize()
+        losses.append(float(tr.loss_sum.item()))
+    assert losses[-1] < losses[0], losses
+    assert torch.isfinite(tr.master).all()
