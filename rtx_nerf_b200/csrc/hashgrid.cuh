@@ -29,6 +29,7 @@ struct Levels {
 struct LevelPoint {
     uint32_t idx[8];   // entry index of corner c = (cx) | (cy << 1) | (cz << 2) within the level
     float w[8];        // trilinear weight of corner c
+    uint32_t gx, gy, gz;   // the cell (lower corner) on this level
 };
 
 // Corner indices and weights of one level for one point (x01,y01,z01 in [0,1]).
@@ -40,6 +41,7 @@ __device__ __forceinline__ void level_point(const Levels& lv, int l, float x01, 
     const float fx = floorf(px), fy = floorf(py), fz = floorf(pz);
     const float wx = rn_sub(px, fx), wy = rn_sub(py, fy), wz = rn_sub(pz, fz);
     const uint32_t gx = (uint32_t)(int)fx, gy = (uint32_t)(int)fy, gz = (uint32_t)(int)fz;
+    p.gx = gx; p.gy = gy; p.gz = gz;
     if (mode == 0) {
         const uint32_t s2 = res * res;
         const uint32_t base = gx + gy * res + gz * s2;

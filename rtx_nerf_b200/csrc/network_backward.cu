@@ -266,16 +266,24 @@ mlp_backward_kernel(const uint16_t* __restrict__ weights, const uint16_t* __rest
 }
 
 // ---------------------------------------------------------------------------------------
-// (2) dEnc -> table gradient.  lane = ray, warp = sample slot (network_rays.cu): the 32 lanes
-// of one reduction instruction hit the same or neighbouring entries, which the L2 merges.
-// grad_table is fp32 [n_entries][2]; each corner is one 8-byte vector reduction.
+// (2) dEnc -> table gradient.  grad_table is fp32 [n_entries][2]; a corner update is one 8-byte
+// vector reduction.  lane = ray, warp = sample slot (as in network_rays.cu): the 32 lanes of a
+// warp are neighbouring rays at the same depth, so on the coarse and middle levels most of them
+// sit in the SAME cell and would send 32 reductions to one address, which the L2 serialises
+// (first version: 94 ms for 2^18 rays x 128 samples).  So per level the warp groups its lanes
+// by cell (match.any on the cell coordinates); with at most HB_MAX_GROUPS distinct cells each
+// group's 16 corner contributions are summed across its lanes with shuffles and ONE lane
+// issues the 8 reductions; with more distinct cells (fine levels) the lanes hit different
+// addresses anyway and reduce directly.
 // ---------------------------------------------------------------------------------------
 #define HB_WARPS 8
+#define HB_MAX_GROUPS 4
 __global__ void __launch_bounds__(HB_WARPS * 32)
 hashgrid_backward_kernel(Levels lv, const float* __restrict__ samples, int stride,
                          const uint16_t* __restrict__ d_encoded, const int* __restrict__ num_hits,
                          const int* __restrict__ indices, int n_rays, int S, float* __restrict__ grad_table)
 {
+    const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int n_groups = (n_rays + 31) >> 5;
     for (int g = blockIdx.x; g < n_groups; g += gridDim.x) {
@@ -286,22 +294,59 @@ hashgrid_backward_kernel(Levels lv, const float* __restrict__ samples, int strid
             ns = num_hits[ray] * S;
             base = (long long)indices[ray] * S;
         }
-        for (int q = warp; q < ns; q += HB_WARPS) {     // per-lane trip count: no warp-collective inside
+        int maxn = ns;
+#pragma unroll
+        for (int o = 16; o; o >>= 1) maxn = max(maxn, __shfl_xor_sync(FULL, maxn, o));
+        for (int q = warp; q < maxn; q += HB_WARPS) {     // warp-uniform trip count
+            const bool valid = q < ns;
             const long long s = base + q;
-            const float* p = samples + s * stride;
-            const float x01 = rn_fma(ld_stream_f1(p), 0.5f, 0.5f);
-            const float y01 = rn_fma(ld_stream_f1(p + 1), 0.5f, 0.5f);
-            const float z01 = rn_fma(ld_stream_f1(p + 2), 0.5f, 0.5f);
+            float x01 = 0.5f, y01 = 0.5f, z01 = 0.5f;
             const uint32_t* ge = reinterpret_cast<const uint32_t*>(d_encoded + s * NET_IN);
+            if (valid) {
+                const float* p = samples + s * stride;
+                x01 = rn_fma(ld_stream_f1(p), 0.5f, 0.5f);
+                y01 = rn_fma(ld_stream_f1(p + 1), 0.5f, 0.5f);
+                z01 = rn_fma(ld_stream_f1(p + 2), 0.5f, 0.5f);
+            }
 #pragma unroll 1
             for (int l = 0; l < lv.n_levels; l++) {
-                const float2 gl = h2_bits_to_f2(__ldg(ge + l));
-                if (gl.x == 0.0f && gl.y == 0.0f) continue;
+                float2 gl = make_float2(0.f, 0.f);
+                if (valid) gl = h2_bits_to_f2(__ldg(ge + l));
+                const bool live = gl.x != 0.0f || gl.y != 0.0f;
+                if (!__any_sync(FULL, live)) continue;
                 LevelPoint pt;
                 level_point(lv, l, x01, y01, z01, pt);
                 float2* gt = reinterpret_cast<float2*>(grad_table) + lv.offset[l];
+                const unsigned long long key =
+                    live ? ((unsigned long long)pt.gx | ((unsigned long long)pt.gy << 21) | ((unsigned long long)pt.gz << 42))
+                         : ~0ull;
+                const unsigned peers = __match_any_sync(FULL, key);
+                const bool leader = live && lane == __ffs(peers) - 1;
+                unsigned leaders = __ballot_sync(FULL, leader);
+                if (__popc(leaders) > HB_MAX_GROUPS) {
+                    if (live) {
 #pragma unroll
-                for (int c = 0; c < 8; c++) atomicAdd(gt + pt.idx[c], make_float2(pt.w[c] * gl.x, pt.w[c] * gl.y));
+                        for (int c = 0; c < 8; c++) atomicAdd(gt + pt.idx[c], make_float2(pt.w[c] * gl.x, pt.w[c] * gl.y));
+                    }
+                    continue;
+                }
+                while (leaders) {                               // warp-uniform: one pass per distinct cell
+                    const int L = __ffs(leaders) - 1;
+                    leaders &= leaders - 1;
+                    const unsigned grp = __shfl_sync(FULL, peers, L);
+                    const bool in = (grp >> lane) & 1u;
+                    const float gx0 = in ? gl.x : 0.0f, gx1 = in ? gl.y : 0.0f;
+#pragma unroll
+                    for (int c = 0; c < 8; c++) {
+                        float a = pt.w[c] * gx0, b = pt.w[c] * gx1;
+#pragma unroll
+                        for (int o = 16; o; o >>= 1) {
+                            a += __shfl_xor_sync(FULL, a, o);
+                            b += __shfl_xor_sync(FULL, b, o);
+                        }
+                        if (lane == L) atomicAdd(gt + pt.idx[c], make_float2(a, b));
+                    }
+                }
             }
         }
     }
