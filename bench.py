@@ -182,16 +182,36 @@ def run_ours(args):
     stage_fns = [r.stage_march, r.stage_sampler, r.stage_radiance, r.stage_composite]
 
     # ---- warm-up
+    clocks = ClockSampler(local) if rank == 0 else None
+    if clocks:
+        clocks.start()
     for k in range(args.warmup):
         r.render_device(poses_dev[k])
     barrier()
 
-    # ---- timed: K steps, inputs (pose) already resident in HBM, CUDA events on the launch stream
-    clocks = ClockSampler(local) if rank == 0 else None
-    if clocks:
-        clocks.start()
-    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(len(stage_fns) + 1)] for _ in range(args.steps)]
+    # ---- per-stage durations (CUDA events on the launch stream; explains the headline)
+    n_stage_steps = min(args.steps, 10)
+    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(len(stage_fns) + 1)] for _ in range(n_stage_steps)]
+    for k in range(n_stage_steps):
+        r.pose_dev.copy_(poses_dev[args.warmup + k], non_blocking=True)
+        ev[k][0].record()
+        for i, fn in enumerate(stage_fns):
+            fn()
+            ev[k][i + 1].record()
+    barrier()
+    stage_ms = [float(np.mean([ev[k][i].elapsed_time(ev[k][i + 1]) for k in range(n_stage_steps)]))
+                for i in range(len(stage_fns))]
+
+    # ---- timed: EXACTLY K steps.  The six launches of a view are captured once in a CUDA graph
+    # (every size that depends on the hit count is read on the device), each step = pose copy +
+    # one graph launch; pose already resident in HBM.
     launches0 = _lib.launch_count
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        for fn in stage_fns:
+            fn()
+    launches_per_step = _lib.launch_count - launches0
+    graph.replay()
     hits_total = torch.zeros(1, dtype=torch.int64, device="cuda")
     barrier()
     t_start = torch.cuda.Event(enable_timing=True)
@@ -199,16 +219,12 @@ def run_ours(args):
     t_start.record()
     for k in range(args.steps):
         r.pose_dev.copy_(poses_dev[args.warmup + k], non_blocking=True)
-        ev[k][0].record()
-        for i, fn in enumerate(stage_fns):
-            fn()
-            ev[k][i + 1].record()
+        graph.replay()
         hits_total += r.hits.total_hits
     t_end.record()
     barrier()
-    launches = _lib.launch_count - launches0
+    launches = launches_per_step * args.steps
     ms_total = t_start.elapsed_time(t_end)
-    stage_ms = [float(np.mean([ev[k][i].elapsed_time(ev[k][i + 1]) for k in range(args.steps)])) for i in range(len(stage_fns))]
     hits = int(hits_total.item())
 
     # ---- e2e: the user's call, host pose in / host pixels out every step
@@ -220,8 +236,44 @@ def run_ours(args):
     e2e_s = time.perf_counter() - t0
     clock_summary = clocks.summary() if clocks else None
 
+    # ---- training step (BASELINE configs[3]): 2^18 rays x (S=4, H_max=32), fwd + bwd + Adam,
+    # NCCL all-reduce of the flat fp32 gradient buffer when N > 1; a short run, reported beside
+    # the headline
+    train = None
+    if not args.no_train:
+        del graph
+        TR, TS, THM, t_warm, t_steps = 1 << 18, 4, 32, 2, 5
+        tr = pipeline.Trainer(grid, net, W, H, focal, W / H, TS, THM, TR,
+                              process_group=dist.group.WORLD if world > 1 else None)
+        target = torch.rand((TR, 3), device="cuda")
+        tposes = poses_dev[:t_warm + t_steps]
+        for k in range(t_warm):
+            tr.step(tposes[k % len(tposes)], (k * 7919) % (W * H - TR), target)
+        barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        c, d = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ar_ms = 0.0
+        a.record()
+        for k in range(t_steps):
+            v = tr.view
+            v.pose_dev.copy_(tposes[(t_warm + k) % len(tposes)], non_blocking=True)
+            v.ray_begin = ((t_warm + k) * 7919) % (W * H - TR)
+            tr.forward()
+            tr.backward()
+            c.record()
+            tr.allreduce()
+            d.record()
+            tr.optimizer_step()
+        b.record()
+        barrier()
+        ar_ms = c.elapsed_time(d)   # the last step's collective
+        train = dict(ms=a.elapsed_time(b) / t_steps, allreduce_ms=ar_ms, rays=TR,
+                     samples=float(tr.view.hits.total_hits.item()) * TS, grad_bytes=tr.grads.numel() * 4,
+                     launches_per_step=tr.launches_per_step, loss=float(tr.loss_sum.item()) / (t_warm + t_steps))
+
     # ---- max over ranks
-    vals = torch.tensor([ms_total, e2e_s * 1e3, float(hits)] + stage_ms, dtype=torch.float64, device="cuda")
+    tv = [train["ms"], train["allreduce_ms"], train["samples"]] if train else [0.0, 0.0, 0.0]
+    vals = torch.tensor([ms_total, e2e_s * 1e3, float(hits)] + tv + stage_ms, dtype=torch.float64, device="cuda")
     if world > 1:
         mx = vals.clone()
         dist.all_reduce(mx, op=dist.ReduceOp.MAX)
@@ -229,9 +281,13 @@ def run_ours(args):
         dist.all_reduce(sm, op=dist.ReduceOp.SUM)
         ms_total, e2e_ms = float(mx[0]), float(mx[1])
         hits_all = float(sm[2])
-        stage_ms = [float(x) for x in mx[3:]]
+        if train:
+            train["ms"], train["allreduce_ms"], train["samples_all"] = float(mx[3]), float(mx[4]), float(sm[5])
+        stage_ms = [float(x) for x in mx[6:]]
     else:
         e2e_ms, hits_all = e2e_s * 1e3, float(hits)
+        if train:
+            train["samples_all"] = train["samples"]
 
     if rank == 0:
         R = W * H
@@ -266,6 +322,14 @@ def run_ours(args):
                     e2e=dict(value=rays_all / (e2e_ms * 1e-3), unit="rays/s", h2d_bytes_per_step=64,
                              d2h_bytes_per_step=R * 12, ms_per_step=e2e_ms / args.steps),
                     gpu_launches=launches, roofline=roofline, stages=stages, clocks=clock_summary)
+        if train:
+            line["train_step"] = dict(
+                workload="configs[3]: 2^18 rays per GPU per step, S=4 x H_max=32 (128 samples/ray), network fwd+bwd, "
+                         "compositing fwd+bwd, L2 loss, Adam; NCCL all-reduce(sum) of the fp32 gradient buffer",
+                ms_per_step=train["ms"], rays_per_s=train["rays"] * world / (train["ms"] * 1e-3),
+                samples_per_s=train["samples_all"] / (train["ms"] * 1e-3), allreduce_ms=train["allreduce_ms"],
+                allreduce_bytes=train["grad_bytes"], launches_per_step=train["launches_per_step"],
+                mean_loss=train["loss"], scaling="weak")
         if world == 1 and not args.no_cpu:
             nthreads = os.cpu_count() or 1
             cpu_path(1000, my_poses, nthreads)
@@ -286,6 +350,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
+    ap.add_argument("--no-train", action="store_true", help="skip the training-step leg (profiling runs)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":

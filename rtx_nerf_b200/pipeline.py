@@ -10,7 +10,7 @@ import ctypes as C
 import numpy as np
 import torch
 
-from . import _lib, api
+from . import _lib, api, parallel
 
 
 class ViewRenderer:
@@ -166,13 +166,13 @@ class Trainer:
 
     def allreduce(self):
         if self.world > 1:
-            import torch.distributed as dist
-            dist.all_reduce(self.grads, op=dist.ReduceOp.SUM, group=self.pg)
+            parallel.allreduce_sum_(self.grads, self.pg)
 
     def optimizer_step(self):
         self.step_count += 1
         api.adam_step(self.master, self.net.params, self.grads, self.m1, self.m2,
-                      1.0 / (self.loss_scale * self.world), self.step_count, lr=self.lr)
+                      parallel.grad_scale(self.loss_scale, self.pg) if self.world > 1 else 1.0 / self.loss_scale,
+                      self.step_count, lr=self.lr)
 
     def step(self, pose_dev, ray_begin, target_dev):
         """pose (16 floats) and target pixels [n_rays][3] already on the device."""
