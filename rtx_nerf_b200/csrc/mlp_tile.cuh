@@ -47,26 +47,37 @@ __device__ __forceinline__ void issue_layer(uint32_t d_tmem, uint32_t a_saddr, u
     tc::mma_commit(bar);
 }
 
-// hidden-layer epilogue: TMEM row -> ReLU -> fp16 -> this thread's row of the next A tile
+// two fp32 -> ReLU -> one packed fp16x2 in ONE instruction (F2FP.RELU): rounding is monotonic and
+// keeps 0, so relu-then-round == round-then-relu bit for bit
+__device__ __forceinline__ uint32_t relu_pack_f16x2(float lo, float hi)
+{
+    uint32_t d;
+    asm("cvt.rn.relu.f16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
+    return d;
+}
+
+// hidden-layer epilogue: TMEM row -> ReLU -> fp16 -> this thread's row of the next A tile.
+// Both 16-column loads of a half row are issued before the single wait.
 __device__ __forceinline__ void relu_row_to_smem(uint32_t taddr, uint8_t* a_next, int row)
 {
 #pragma unroll
-    for (int q = 0; q < NET_W / 16; q++) {
-        uint32_t r[16];
-        tc::tmem_ld_x16(taddr + q * 16, r);
+    for (int h = 0; h < NET_W / 32; h++) {
+        uint32_t r0[16], r1[16];
+        tc::tmem_ld_x16(taddr + h * 32, r0);
+        tc::tmem_ld_x16(taddr + h * 32 + 16, r1);
         tc::tmem_ld_wait();
-        uint32_t pk[8];
+        uint32_t pk[16];
 #pragma unroll
         for (int j = 0; j < 8; j++) {
-            const float a = fmaxf(__uint_as_float(r[2 * j]), 0.0f), b = fmaxf(__uint_as_float(r[2 * j + 1]), 0.0f);
-            const __half2 h = __floats2half2_rn(a, b);
-            pk[j] = *reinterpret_cast<const uint32_t*>(&h);
+            pk[j] = relu_pack_f16x2(__uint_as_float(r0[2 * j]), __uint_as_float(r0[2 * j + 1]));
+            pk[8 + j] = relu_pack_f16x2(__uint_as_float(r1[2 * j]), __uint_as_float(r1[2 * j + 1]));
         }
-        *reinterpret_cast<uint4*>(a_next + tile_chunk_off(row, 2 * q, NET_W)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-        *reinterpret_cast<uint4*>(a_next + tile_chunk_off(row, 2 * q + 1, NET_W)) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+#pragma unroll
+        for (int c = 0; c < 4; c++)
+            *reinterpret_cast<uint4*>(a_next + tile_chunk_off(row, 4 * h + c, NET_W)) =
+                make_uint4(pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
     }
 }
-
 
 // output-layer epilogue: TMEM row (16 fp32) -> optional sigmoid -> fp16 -> out16[s][16] and/or
 // radiance4[s] = float(half(.)) of the first four (main.cu:723-728, the intended gather of Q3)
@@ -85,9 +96,9 @@ __device__ __forceinline__ void output_row_store(const uint32_t (&r)[16], int ou
     for (int j = 0; j < 8; j++) {
         if (j >= n_pairs) break;
         float a = __uint_as_float(r[2 * j]), b = __uint_as_float(r[2 * j + 1]);
-        if (out_activation == 1) {
-            a = 1.0f / (1.0f + expf(-a));
-            b = 1.0f / (1.0f + expf(-b));
+        if (out_activation == 1) {   // fast exp / divide: ~2 ulp in fp32, invisible after the fp16 rounding
+            a = __fdividef(1.0f, 1.0f + __expf(-a));
+            b = __fdividef(1.0f, 1.0f + __expf(-b));
         }
         const __half2 h = __floats2half2_rn(a, b);
         pk[j] = *reinterpret_cast<const uint32_t*>(&h);

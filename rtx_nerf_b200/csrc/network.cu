@@ -81,6 +81,13 @@ network_forward_tc_kernel(Levels lv, const __half2* __restrict__ table, const ui
     const long long n = row_count(d_count, count_scale, n_max);
     const long long n_tiles = (n + NET_TILE - 1) / NET_TILE;
     uint32_t phase = 0;
+    uint4 pre[NET_IN / 8];   // software pipeline of the pre-encoded input rows (ENCODE == false)
+    if (!ENCODE) {
+        const long long s0 = (long long)blockIdx.x * NET_TILE + tid;
+        const uint4* src = reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(input) + s0 * NET_IN);
+#pragma unroll
+        for (int c = 0; c < NET_IN / 8; c++) pre[c] = s0 < n ? __ldg(src + c) : make_uint4(0, 0, 0, 0);
+    }
     for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         const long long s = tile * NET_TILE + tid;
         const bool valid = s < n;
@@ -104,12 +111,14 @@ network_forward_tc_kernel(Levels lv, const __half2* __restrict__ table, const ui
                 *reinterpret_cast<__half2*>(act + tile_chunk_off(tid, l >> 2, NET_IN) + (l & 3) * 4) = f;
             }
         } else {
-            const uint4* src = reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(input) + s * NET_IN);
+            // this tile's row was fetched while the previous tile ran its layers; fetch the next one now
 #pragma unroll
-            for (int c = 0; c < NET_IN / 8; c++) {
-                const uint4 v = valid ? __ldg(src + c) : make_uint4(0, 0, 0, 0);
-                *reinterpret_cast<uint4*>(act + tile_chunk_off(tid, c, NET_IN)) = v;
-            }
+            for (int c = 0; c < NET_IN / 8; c++)
+                *reinterpret_cast<uint4*>(act + tile_chunk_off(tid, c, NET_IN)) = pre[c];
+            const long long sn = (tile + gridDim.x) * NET_TILE + tid;
+            const uint4* src = reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(input) + sn * NET_IN);
+#pragma unroll
+            for (int c = 0; c < NET_IN / 8; c++) pre[c] = sn < n ? __ldg(src + c) : make_uint4(0, 0, 0, 0);
         }
         tc::fence_proxy_async_smem();
         tc::fence_before_thread_sync();   // also orders the previous tile's tcgen05.ld before the next MMA
@@ -147,37 +156,8 @@ network_forward_tc_kernel(Levels lv, const __half2* __restrict__ table, const ui
         phase ^= 1;
         tc::fence_after_thread_sync();
         uint32_t r[16];
-        tc::tmem_ld_x16(t_row, r);
-        tc::tmem_ld_wait();
-        if (valid) {
-            uint32_t pk[8];
-            float first4[4];
-            const int n_pairs = out16 ? 8 : 2;     // only (r,g,b,sigma) are needed without out16
-#pragma unroll
-            for (int j = 0; j < 8; j++) {
-                if (j >= n_pairs) break;
-                float a = __uint_as_float(r[2 * j]), b = __uint_as_float(r[2 * j + 1]);
-                if (out_activation == 1) {
-                    a = 1.0f / (1.0f + expf(-a));
-                    b = 1.0f / (1.0f + expf(-b));
-                }
-                const __half2 h = __floats2half2_rn(a, b);
-                pk[j] = *reinterpret_cast<const uint32_t*>(&h);
-                if (j < 2) {
-                    const float2 back = __half22float2(h);   // main.cu:723-728: radiance = float(half(out))
-                    first4[2 * j] = back.x;
-                    first4[2 * j + 1] = back.y;
-                }
-            }
-            if (out16) {
-                uint4* o = reinterpret_cast<uint4*>(out16 + s * NET_OUT);
-                o[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-                o[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
-            }
-            if (radiance4)
-                st_stream_f4(reinterpret_cast<float4*>(radiance4) + s,
-                             make_float4(first4[0], first4[1], first4[2], first4[3]));
-        }
+        output_row_load(t_row, r);
+        if (valid) output_row_store(r, out_activation, s, out16, radiance4);
     }
     tc::fence_before_thread_sync();
     __syncthreads();

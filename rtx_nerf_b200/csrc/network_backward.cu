@@ -149,17 +149,27 @@ mlp_backward_kernel(const uint16_t* __restrict__ weights, const uint16_t* __rest
 
     const long long n = row_count(d_count, count_scale, n_max);
     const long long n_tiles = (n + NET_TILE - 1) / NET_TILE;
+    uint4 pre[NET_IN / 8];   // software pipeline: the next tile's inputs are in flight during this tile's layers
+    uint2 pre_g;
+    auto fetch_row = [&](long long t) {
+        const long long sn = t * NET_TILE + tid;
+        const bool ok = sn < n;
+        const uint4* src = reinterpret_cast<const uint4*>(encoded + sn * NET_IN);
+#pragma unroll
+        for (int c = 0; c < NET_IN / 8; c++) pre[c] = ok ? __ldg(src + c) : make_uint4(0, 0, 0, 0);
+        pre_g = ok ? __ldg(reinterpret_cast<const uint2*>(dl_dradiance + sn * 4)) : make_uint2(0, 0);
+    };
+    fetch_row(blockIdx.x);
     for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         const long long s = tile * NET_TILE + tid;
         const bool valid = s < n;
-        {   // A0: the stored encoded features of this row
-            const uint4* src = reinterpret_cast<const uint4*>(encoded + s * NET_IN);
+        {   // A0: the stored encoded features of this row (fetched during the previous tile)
 #pragma unroll
-            for (int c = 0; c < NET_IN / 8; c++) {
-                const uint4 v = valid ? __ldg(src + c) : make_uint4(0, 0, 0, 0);
-                *reinterpret_cast<uint4*>(smem + NbSmem::A0 + tile_chunk_off(tid, c, NET_IN)) = v;
-            }
+            for (int c = 0; c < NET_IN / 8; c++)
+                *reinterpret_cast<uint4*>(smem + NbSmem::A0 + tile_chunk_off(tid, c, NET_IN)) = pre[c];
         }
+        const uint2 gb = pre_g;
+        fetch_row(tile + gridDim.x);
         // ---- forward recompute
         sync_then([&] { mma_fwd<NET_W, NET_IN>(tm + NB_D, s_a0, s_w0); });
         relu_row_to_smem(t_row + NB_D, smem + NbSmem::H1, tid);
@@ -171,14 +181,13 @@ mlp_backward_kernel(const uint16_t* __restrict__ weights, const uint16_t* __rest
             output_row_load(t_row + NB_D, r);
             float d[4] = {0.f, 0.f, 0.f, 0.f};
             if (valid) {
-                const uint2 gb = __ldg(reinterpret_cast<const uint2*>(dl_dradiance + s * 4));
                 const float2 g01 = h2_bits_to_f2(gb.x), g23 = h2_bits_to_f2(gb.y);
                 const float g[4] = {g01.x, g01.y, g23.x, g23.y};
 #pragma unroll
                 for (int j = 0; j < 4; j++) {
                     float da = 1.0f;
                     if (out_activation == 1) {
-                        const float sg = 1.0f / (1.0f + expf(-__uint_as_float(r[j])));
+                        const float sg = __fdividef(1.0f, 1.0f + __expf(-__uint_as_float(r[j])));
                         da = sg * (1.0f - sg);
                     }
                     d[j] = g[j] * da;
