@@ -276,23 +276,24 @@ mlp_backward_kernel(const uint16_t* __restrict__ weights, const uint16_t* __rest
 
 // ---------------------------------------------------------------------------------------
 // (2) dEnc -> table gradient.  grad_table is fp32 [n_entries][2]; a corner update is one 8-byte
-// vector reduction.  lane = ray, warp = sample slot (as in network_rays.cu): the 32 lanes of a
-// warp are neighbouring rays at the same depth, so on the coarse and middle levels most of them
-// sit in the SAME cell and would send 32 reductions to one address, which the L2 serialises
-// (first version: 94 ms for 2^18 rays x 128 samples).  So per level the warp groups its lanes
-// by cell (match.any on the cell coordinates); with at most HB_MAX_GROUPS distinct cells each
-// group's 16 corner contributions are summed across its lanes with shuffles and ONE lane
-// issues the 8 reductions; with more distinct cells (fine levels) the lanes hit different
-// addresses anyway and reduce directly.
+// vector reduction, an x-pair of corners that shares an aligned entry pair one 16-byte one.
+// lane = ray, warp = sample slot (as in network_rays.cu): the 32 lanes of a warp are
+// neighbouring rays at the same depth, so consecutive lanes sit in the SAME cell — all 32 on the
+// coarse levels, runs of 2-8 on the fine ones — and would send their reductions to the same
+// addresses, which L1TEX/L2 serialise (first version: 94 ms for 2^18 rays x 128 samples; ncu:
+// L1TEX 89 % busy).  Per level the warp therefore sums the 16 corner contributions over each
+// run of consecutive lanes with equal cell (a segmented shuffle reduction whose run structure
+// comes from one ballot; it stops at the longest run) and only the head lane of a run issues
+// the reductions.
 // ---------------------------------------------------------------------------------------
 #define HB_WARPS 8
-#define HB_MAX_GROUPS 4
 __global__ void __launch_bounds__(HB_WARPS * 32)
 hashgrid_backward_kernel(Levels lv, const float* __restrict__ samples, int stride,
                          const uint16_t* __restrict__ d_encoded, const int* __restrict__ num_hits,
                          const int* __restrict__ indices, int n_rays, int S, float* __restrict__ grad_table)
 {
     const unsigned FULL = 0xffffffffu;
+    __shared__ uint32_t stage[HB_WARPS * 32][NET_IN / 2 + 1];   // +1: conflict-free per-thread rows
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int n_groups = (n_rays + 31) >> 5;
     for (int g = blockIdx.x; g < n_groups; g += gridDim.x) {
@@ -310,50 +311,67 @@ hashgrid_backward_kernel(Levels lv, const float* __restrict__ samples, int strid
             const bool valid = q < ns;
             const long long s = base + q;
             float x01 = 0.5f, y01 = 0.5f, z01 = 0.5f;
-            const uint32_t* ge = reinterpret_cast<const uint32_t*>(d_encoded + s * NET_IN);
+            // the row's 16 feature-gradient pairs: four 16-byte loads staged in shared memory (the
+            // level loop is rolled; a 4-byte load per level would cost 32 L1TEX wavefronts each)
+            uint32_t* my = stage[threadIdx.x];
             if (valid) {
                 const float* p = samples + s * stride;
                 x01 = rn_fma(ld_stream_f1(p), 0.5f, 0.5f);
                 y01 = rn_fma(ld_stream_f1(p + 1), 0.5f, 0.5f);
                 z01 = rn_fma(ld_stream_f1(p + 2), 0.5f, 0.5f);
+                const uint4* ge = reinterpret_cast<const uint4*>(d_encoded + s * NET_IN);
+#pragma unroll
+                for (int c = 0; c < NET_IN / 8; c++) {
+                    const uint4 e = ld_stream_u4(ge + c);
+                    my[4 * c] = e.x; my[4 * c + 1] = e.y; my[4 * c + 2] = e.z; my[4 * c + 3] = e.w;
+                }
             }
 #pragma unroll 1
             for (int l = 0; l < lv.n_levels; l++) {
                 float2 gl = make_float2(0.f, 0.f);
-                if (valid) gl = h2_bits_to_f2(__ldg(ge + l));
+                if (valid) gl = h2_bits_to_f2(my[l]);
                 const bool live = gl.x != 0.0f || gl.y != 0.0f;
                 if (!__any_sync(FULL, live)) continue;
                 LevelPoint pt;
                 level_point(lv, l, x01, y01, z01, pt);
-                float2* gt = reinterpret_cast<float2*>(grad_table) + lv.offset[l];
-                const unsigned long long key =
-                    live ? ((unsigned long long)pt.gx | ((unsigned long long)pt.gy << 21) | ((unsigned long long)pt.gz << 42))
-                         : ~0ull;
-                const unsigned peers = __match_any_sync(FULL, key);
-                const bool leader = live && lane == __ffs(peers) - 1;
-                unsigned leaders = __ballot_sync(FULL, leader);
-                if (__popc(leaders) > HB_MAX_GROUPS) {
-                    if (live) {
+                // cell key; dead lanes get a key of their own so that they end a run
+                const uint32_t k0 = live ? (pt.gx | (pt.gy << 16)) : 0xffffffffu;
+                const uint32_t k1 = live ? pt.gz : 0xffffffffu;
+                const uint32_t p0 = __shfl_up_sync(FULL, k0, 1), p1 = __shfl_up_sync(FULL, k1, 1);
+                const bool head = lane == 0 || p0 != k0 || p1 != k1;
+                const unsigned heads = __ballot_sync(FULL, head);
+                float v[16];
 #pragma unroll
-                        for (int c = 0; c < 8; c++) atomicAdd(gt + pt.idx[c], make_float2(pt.w[c] * gl.x, pt.w[c] * gl.y));
-                    }
-                    continue;
+                for (int c = 0; c < 8; c++) {
+                    v[2 * c] = pt.w[c] * gl.x;
+                    v[2 * c + 1] = pt.w[c] * gl.y;
                 }
-                while (leaders) {                               // warp-uniform: one pass per distinct cell
-                    const int L = __ffs(leaders) - 1;
-                    leaders &= leaders - 1;
-                    const unsigned grp = __shfl_sync(FULL, peers, L);
-                    const bool in = (grp >> lane) & 1u;
-                    const float gx0 = in ? gl.x : 0.0f, gx1 = in ? gl.y : 0.0f;
+                // lanes i and i+d are in the same run iff no head in (i, i+d]
+                const unsigned after = lane < 31 ? (heads >> (lane + 1)) : 1u;
 #pragma unroll
-                    for (int c = 0; c < 8; c++) {
-                        float a = pt.w[c] * gx0, b = pt.w[c] * gx1;
+                for (int d = 1; d < 32; d <<= 1) {
+                    const bool same = (lane + d < 32) && (after & ((1u << d) - 1u)) == 0u;
+                    if (!__any_sync(FULL, same)) break;     // longest run reached
 #pragma unroll
-                        for (int o = 16; o; o >>= 1) {
-                            a += __shfl_xor_sync(FULL, a, o);
-                            b += __shfl_xor_sync(FULL, b, o);
+                    for (int i = 0; i < 16; i++) {
+                        const float t = __shfl_down_sync(FULL, v[i], d);
+                        if (same) v[i] += t;
+                    }
+                }
+                if (head && live) {
+                    float2* gt = reinterpret_cast<float2*>(grad_table) + lv.offset[l];
+#pragma unroll
+                    for (int qd = 0; qd < 4; qd++) {
+                        const uint32_t i0 = pt.idx[2 * qd], i1 = pt.idx[2 * qd + 1];
+                        const float2 a = make_float2(v[4 * qd], v[4 * qd + 1]), b = make_float2(v[4 * qd + 2], v[4 * qd + 3]);
+                        if ((i0 ^ i1) == 1u) {
+                            const bool odd = i0 & 1u;
+                            atomicAdd(reinterpret_cast<float4*>(gt + (i0 & ~1u)),
+                                      odd ? make_float4(b.x, b.y, a.x, a.y) : make_float4(a.x, a.y, b.x, b.y));
+                        } else {
+                            atomicAdd(gt + i0, a);
+                            atomicAdd(gt + i1, b);
                         }
-                        if (lane == L) atomicAdd(gt + pt.idx[c], make_float2(a, b));
                     }
                 }
             }
