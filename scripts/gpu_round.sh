@@ -1,0 +1,23 @@
+#!/bin/bash
+# One gpurun call: gpu tests, smoke, contract bench, ncu launch list, ncu --set full captures.
+# Usage (here): gpurun --timeout 1500 -- 'bash scripts/gpu_round.sh TAG'
+TAG=${1:-x}
+O=gpurun_out/$TAG
+mkdir -p $O
+nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > $O/smi.txt 2>&1
+timeout 900 python -m pytest tests -m gpu -x -q > $O/pytest.log 2>&1; echo "pytest rc=$?" | tee -a $O/rc.txt
+timeout 300 python -c 'import __graft_entry__ as g; g.smoke()' > $O/smoke.log 2>&1; echo "smoke rc=$?" | tee -a $O/rc.txt
+timeout 600 python bench.py > $O/bench.json 2> $O/bench.err; echo "bench rc=$?" | tee -a $O/rc.txt
+timeout 300 python bench.py --impl reference --steps 3 --warmup 1 > $O/bench_ref.json 2> $O/bench_ref.err; echo "ref rc=$?" | tee -a $O/rc.txt
+timeout 300 python scripts/stage_bench.py > $O/stage_bench.txt 2>&1
+timeout 300 python scripts/train_bench.py > $O/train_bench.txt 2>&1
+if [ "$2" != "noprof" ]; then
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/launches.csv \
+  python bench.py --steps 2 --warmup 3 --no-cpu > $O/ncu_launch.log 2>&1; echo "ncu-list rc=$?" | tee -a $O/rc.txt
+# full captures: one launch of each product kernel in the view (skip warm-up launches with -s)
+timeout 900 ncu --set full --clock-control none --import-source on -s 12 -c 6 -o $O/view_full -f \
+  python bench.py --steps 2 --warmup 3 --no-cpu --no-train > $O/ncu_full.log 2>&1; echo "ncu-full rc=$?" | tee -a $O/rc.txt
+timeout 900 ncu --set full --clock-control none --import-source on -s 24 -c 14 -o $O/train_full -f \
+  python scripts/train_bench.py --steps 1 > $O/ncu_train.log 2>&1; echo "ncu-train rc=$?" | tee -a $O/rc.txt
+fi
+tail -3 $O/pytest.log; cat $O/smoke.log | tail -2; cat $O/bench.json | cut -c1-600; cat $O/stage_bench.txt; cat $O/train_bench.txt
