@@ -205,12 +205,12 @@ def run_ours(args):
     # ---- timed: EXACTLY K steps.  The six launches of a view are captured once in a CUDA graph
     # (every size that depends on the hit count is read on the device), each step = pose copy +
     # one graph launch; pose already resident in HBM.
-    launches0 = _lib.launch_count
+    launches0 = _lib.kernel_launches()
     graph = torch.cuda.CUDAGraph()
     with torch.cuda.graph(graph):
         for fn in stage_fns:
             fn()
-    launches_per_step = _lib.launch_count - launches0
+    launches_per_step = _lib.kernel_launches() - launches0
     graph.replay()
     hits_total = torch.zeros(1, dtype=torch.int64, device="cuda")
     barrier()

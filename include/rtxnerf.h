@@ -36,6 +36,8 @@ enum {
 };
 
 int rtxnerf_abi_version(void);
+/* Number of CUDA kernels this library has launched in this process (all entry points). */
+unsigned long long rtxnerf_kernel_launches(void);
 /* Static string for a code returned by this library (CUDA codes map to cudaGetErrorString). */
 const char* rtxnerf_error_string(int code);
 
@@ -122,7 +124,9 @@ typedef struct rtxnerf_hits {
 /* Bytes of device scratch rtxnerf_ray_march_csr needs for n_rays. */
 size_t rtxnerf_ray_march_workspace_bytes(long long n_rays);
 
-/* count -> scan -> fill, all on `stream`.  max_hits caps hits per ray (H_max).  Hits
+/* All on `stream`.  max_hits <= 32: ONE kernel (march once, hits parked in shared memory,
+ * decoupled look-back for the CSR base, coalesced copy-out) after a memset of the status
+ * words; larger caps: count -> scan -> fill.  max_hits caps hits per ray (H_max).  Hits
  * beyond `capacity` are dropped and *total_hits still reports the true total, so the
  * caller can detect overflow; rays are never split. */
 int rtxnerf_ray_march_csr(const rtxnerf_grid* grid, const rtxnerf_camera* cam,

@@ -55,6 +55,7 @@ class Mlp(C.Structure):
 SIGNATURES = {
     "rtxnerf_abi_version": (c_int, []),
     "rtxnerf_error_string": (C.c_char_p, [c_int]),
+    "rtxnerf_kernel_launches": (C.c_ulonglong, []),
     "rtxnerf_grid_create": (c_int, [c_void_p, c_int, C.POINTER(c_void_p)]),
     "rtxnerf_grid_create_from_aabbs": (c_int, [c_void_p, c_int, c_int, C.POINTER(c_void_p)]),
     "rtxnerf_grid_update": (c_int, [c_void_p, c_void_p, c_void_p]),
@@ -118,10 +119,11 @@ def check(code, what=""):
         raise RtxNerfError("%s failed: %s (code %d)" % (what or "rtxnerf call", msg.decode() if msg else "?", code))
 
 
-# number of kernels this process has launched through the ABI (bench.py's gpu_launches claim)
-launch_count = 0
+def kernel_launches():
+    """Kernels the library itself has launched in this process (bench.py's gpu_launches claim)."""
+    return int(load().rtxnerf_kernel_launches())
 
 
 def count_launches(n):
-    global launch_count
-    launch_count += n
+    """Kept for callers; the authoritative count is the library's own (kernel_launches())."""
+    return None

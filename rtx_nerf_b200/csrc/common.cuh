@@ -15,7 +15,14 @@
         if (_e != cudaSuccess) return (int)_e;  \
     } while (0)
 
-static inline int rtx_launch_status() { return (int)cudaGetLastError(); }
+// Kernels launched by this library in this process (rtxnerf_kernel_launches(), general.cu):
+// bench.py's gpu_launches claim is read from here, not counted by the caller.
+extern unsigned long long g_rtx_kernel_launches;
+static inline int rtx_launch_status(int n_launched = 1)
+{
+    __atomic_fetch_add(&g_rtx_kernel_launches, (unsigned long long)n_launched, __ATOMIC_RELAXED);
+    return (int)cudaGetLastError();
+}
 
 // ---------------------------------------------------------------------------------------
 // Bit-defined fp32 arithmetic.  The hit-cell lists must equal the reference's bit for bit,

@@ -1,6 +1,13 @@
 // general.cu — version and error reporting of librtxnerf_b200.so.
 #include "common.cuh"
 
+unsigned long long g_rtx_kernel_launches = 0;
+
+extern "C" unsigned long long rtxnerf_kernel_launches(void)
+{
+    return __atomic_load_n(&g_rtx_kernel_launches, __ATOMIC_RELAXED);
+}
+
 extern "C" int rtxnerf_abi_version(void) { return RTXNERF_ABI_VERSION; }
 
 extern "C" const char* rtxnerf_error_string(int code)

@@ -19,6 +19,7 @@
 #include "common.cuh"
 
 #include <math.h>
+#include <stdlib.h>
 #include <new>
 #include <vector>
 
@@ -89,6 +90,42 @@ struct HitRecord {
     int cell;
 };
 
+// IEEE-754 a/d (round to nearest even) with the reciprocal hoisted out of the march loop.
+// A ray divides by the same three direction components hundreds of times
+// (optixPrograms.cu:140-151,204-206 evaluate (plane - o)/d for every candidate cell);
+// div.rn.f32 costs MUFU.RCP + 2 refinement FMAs + FCHK + branch + 5 FMAs each time.  With
+// r = RN(1/d) computed once per ray, two Markstein correction steps give the correctly
+// rounded quotient whenever no intermediate can underflow or overflow: the residual
+// a - d*q is an exact multiple of 2^(exp(a)-46), representable for |a| >= 2^-103.  `fast`
+// certifies the operand ranges (set per ray for d, per relaunch for o, see axis_fast);
+// anything else takes div.rn itself.  a is never -0 here (a = plane - o with plane != -0),
+// so the sign of a zero quotient is the IEEE one as well.  Checked against a/d on the host
+// for 3e8 random and patterned operand pairs: 0 mismatches.
+__device__ __forceinline__ float div_exact(float a, float d, float r, bool fast)
+{
+    const float q0 = rn_mul(a, r);
+    const float e0 = rn_fma(-d, q0, a);
+    const float q1 = rn_fma(e0, r, q0);
+    const float e1 = rn_fma(-d, q1, a);
+    float q = rn_fma(e1, r, q1);
+    if (!fast) q = rn_div(a, d);
+    return q;
+}
+
+// d certifies the fast path when 2^-30 <= |d| <= 2 (direction components are <= 1)
+__device__ __forceinline__ bool dir_fast(float d)
+{
+    const uint32_t e = (__float_as_uint(d) >> 23) & 0xffu;
+    return e >= 127u - 30u && e <= 128u;
+}
+// o certifies it when o == 0 or 2^-90 <= |o| < 2^60: then a = plane - o (planes are
+// multiples of 2/G, |plane| <= 1) is 0 or has 2^-103 <= |a| < 2^61
+__device__ __forceinline__ bool origin_fast(float o)
+{
+    const uint32_t e = (__float_as_uint(o) >> 23) & 0xffu;
+    return (e >= 127u - 90u && e < 127u + 60u) || (__float_as_uint(o) << 1) == 0u;
+}
+
 // Marches one ray; calls emit(j, HitRecord) for hit j.  Returns the number of hits (<= cap).
 template <bool WANT_START, class Emit>
 __device__ __forceinline__ int march_ray(const uint32_t* __restrict__ bits, int G, float ox, float oy,
@@ -96,14 +133,20 @@ __device__ __forceinline__ int march_ray(const uint32_t* __restrict__ bits, int 
 {
     const float L = 2.0f / (float)G;
     const float half_g = 0.5f * (float)G;
+    const float rx = __frcp_rn(dx), ry = __frcp_rn(dy), rz = __frcp_rn(dz);
+    const bool dfx = dir_fast(dx), dfy = dir_fast(dy), dfz = dir_fast(dz);
     int nh = 0;
     while (nh < cap) {
         int ix = locate_cell(ox, G, L, half_g);
         int iy = locate_cell(oy, G, L, half_g);
         int iz = locate_cell(oz, G, L, half_g);
-        float tlx = rn_div(rn_sub(plane_at(ix, L), ox), dx), thx = rn_div(rn_sub(plane_at(ix + 1, L), ox), dx);
-        float tly = rn_div(rn_sub(plane_at(iy, L), oy), dy), thy = rn_div(rn_sub(plane_at(iy + 1, L), oy), dy);
-        float tlz = rn_div(rn_sub(plane_at(iz, L), oz), dz), thz = rn_div(rn_sub(plane_at(iz + 1, L), oz), dz);
+        const bool fx = dfx && origin_fast(ox), fy = dfy && origin_fast(oy), fz = dfz && origin_fast(oz);
+        float tlx = div_exact(rn_sub(plane_at(ix, L), ox), dx, rx, fx),
+              thx = div_exact(rn_sub(plane_at(ix + 1, L), ox), dx, rx, fx);
+        float tly = div_exact(rn_sub(plane_at(iy, L), oy), dy, ry, fy),
+              thy = div_exact(rn_sub(plane_at(iy + 1, L), oy), dy, ry, fy);
+        float tlz = div_exact(rn_sub(plane_at(iz, L), oz), dz, rz, fz),
+              thz = div_exact(rn_sub(plane_at(iz + 1, L), oz), dz, rz, fz);
         bool found = false;
         for (;;) {
             if ((unsigned)ix >= (unsigned)G || (unsigned)iy >= (unsigned)G || (unsigned)iz >= (unsigned)G) break;
@@ -148,17 +191,19 @@ __device__ __forceinline__ int march_ray(const uint32_t* __restrict__ bits, int 
             if (ks < 0 || best > RAY_TMAX) break;
             float os = ks == 0 ? ox : (ks == 1 ? oy : oz);
             float ds = ks == 0 ? dx : (ks == 1 ? dy : dz);
+            float rs = ks == 0 ? rx : (ks == 1 ? ry : rz);
+            bool fs = ks == 0 ? fx : (ks == 1 ? fy : fz);
             int is = ks == 0 ? ix : (ks == 1 ? iy : iz);
             float tls = ks == 0 ? tlx : (ks == 1 ? tly : tlz);
             float ths = ks == 0 ? thx : (ks == 1 ? thy : thz);
             if (ds > 0.0f) {
                 is++;
                 tls = ths;
-                ths = rn_div(rn_sub(plane_at(is + 1, L), os), ds);
+                ths = div_exact(rn_sub(plane_at(is + 1, L), os), ds, rs, fs);
             } else {
                 is--;
                 ths = tls;
-                tls = rn_div(rn_sub(plane_at(is, L), os), ds);
+                tls = div_exact(rn_sub(plane_at(is, L), os), ds, rs, fs);
             }
             if (ks == 0) { ix = is; tlx = tls; thx = ths; }
             else if (ks == 1) { iy = is; tly = tls; thy = ths; }
@@ -300,6 +345,190 @@ march_fill_kernel(const uint32_t* __restrict__ bits, int G, CamArgs cam, long lo
                     [&](int j, const HitRecord& h) { store_hit(out, base + j, h); });
 }
 
+// ------------------------------------------------------------------------------------ one pass
+// Single-pass CSR march for max_hits <= ONEPASS_MAX_CAP: every ray is marched ONCE.
+//   1. a CTA takes the next tile of MARCH_BLOCK consecutive rays from a ticket counter
+//      (tickets = launch order, so a tile only ever waits on tiles that are already running);
+//   2. each thread marches its ray and parks 6 words per hit in shared memory
+//      (t_start, t_end, exit point, cell; row stride 6*cap+1 words: conflict-free);
+//   3. block scan of the counts, then a decoupled look-back over the per-tile status words
+//      ([flag:2 | hit count:62], flag 1 = tile aggregate, 2 = inclusive prefix) gives the
+//      tile's CSR base without a second kernel or a second march;
+//   4. the tile's hits are contiguous in every CSR array, so the CTA copies them out with
+//      slot = thread: fully coalesced stores (the two-pass fill wrote 9 scalars per hit at
+//      64..192-byte strides between lanes: 593 MB of DRAM traffic for 368 MB of records,
+//      profiles/r01_d_view_full.txt).  Entry points are rebuilt on the way out from the
+//      previous exit point (start = fma(t_start, d, o_prev), optixPrograms.cu:194-196).
+#define ONEPASS_MAX_CAP 32
+#define LOOKBACK_SPIN_LIMIT (1u << 24)
+
+__device__ __forceinline__ unsigned long long ld_status(const unsigned long long* p)
+{
+    unsigned long long v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_status(unsigned long long* p, unsigned long long v)
+{
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+__global__ void __launch_bounds__(MARCH_BLOCK)
+march_onepass_kernel(const uint32_t* __restrict__ bits, int G, CamArgs cam, long long ray_begin, long long n_rays,
+                     int cap, int* __restrict__ num_hits, float* __restrict__ view_dirs,
+                     float* __restrict__ ray_origins, int* __restrict__ indices, FillOut out,
+                     unsigned long long* __restrict__ status, unsigned long long* __restrict__ ticket,
+                     long long* __restrict__ total_hits, int n_tiles)
+{
+    extern __shared__ __align__(16) uint32_t dyn[];
+    const int row = 6 * cap + 1;
+    uint32_t* rec = dyn;                                        // [MARCH_BLOCK][row]
+    float* pts = reinterpret_cast<float*>(dyn + MARCH_BLOCK * row);   // [2][MARCH_BLOCK*3]
+    float* dirs = pts + 2 * MARCH_BLOCK * 3;                    // [MARCH_BLOCK][3]
+    int* excl = reinterpret_cast<int*>(dirs + MARCH_BLOCK * 3); // [MARCH_BLOCK + 1]
+    __shared__ int warp_sums[MARCH_BLOCK / 32];
+    __shared__ int tile_s;
+    __shared__ long long base_s;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+    if (tid == 0) tile_s = (int)atomicAdd(ticket, 1ull);
+    __syncthreads();
+    const int tile = tile_s;
+    if (tile >= n_tiles) return;
+    const long long lr = (long long)tile * MARCH_BLOCK + tid;
+
+    // ---- 1+2: march, park the hits
+    int nh = 0;
+    float ox0 = 0.f, oy0 = 0.f, oz0 = 0.f;
+    if (lr < n_rays) {
+        unsigned long long ray = (unsigned long long)(ray_begin + lr);
+        RayGen r = raygen(cam.look_at, cam.focal, cam.aspect, cam.width, cam.height,
+                          (unsigned)(ray % cam.width), (unsigned)(ray / cam.width));
+        ox0 = r.ox; oy0 = r.oy; oz0 = r.oz;
+        dirs[3 * tid] = r.dx; dirs[3 * tid + 1] = r.dy; dirs[3 * tid + 2] = r.dz;
+        uint32_t* my = rec + tid * row;
+        nh = march_ray<false>(bits, G, r.ox, r.oy, r.oz, r.dx, r.dy, r.dz, cap, [&](int j, const HitRecord& h) {
+            uint32_t* w = my + 6 * j;
+            w[0] = __float_as_uint(h.t_start);
+            w[1] = __float_as_uint(h.t_end);
+            w[2] = __float_as_uint(h.ex);
+            w[3] = __float_as_uint(h.ey);
+            w[4] = __float_as_uint(h.ez);
+            w[5] = (uint32_t)h.cell;
+        });
+        num_hits[lr] = nh;
+        reinterpret_cast<float2*>(view_dirs)[lr] = make_float2(r.theta, r.phi);
+        if (ray_origins) {
+            ray_origins[3 * lr] = r.ox;
+            ray_origins[3 * lr + 1] = r.oy;
+            ray_origins[3 * lr + 2] = r.oz;
+        }
+    }
+    // ---- 3: block scan + look-back
+    const int inc = warp_incl_scan_i32(nh, lane);
+    if (lane == 31) warp_sums[warp] = inc;
+    __syncthreads();
+    int woff = 0, block_total = 0;
+#pragma unroll
+    for (int w = 0; w < MARCH_BLOCK / 32; w++) {
+        woff += (w < warp) ? warp_sums[w] : 0;
+        block_total += warp_sums[w];
+    }
+    excl[tid] = woff + inc - nh;
+    if (tid == 0) excl[MARCH_BLOCK] = block_total;
+    if (warp == 0) {
+        long long exclusive = 0;
+        if (tile > 0) {
+            if (lane == 0) st_status(status + tile, (1ull << 62) | (unsigned long long)block_total);
+            int idx = tile - 1;
+            unsigned spins = 0;
+            for (;;) {
+                const int mine = idx - lane;
+                unsigned long long v = 2ull << 62;                       // before tile 0: prefix 0
+                if (mine >= 0) v = ld_status(status + mine);
+                while (__any_sync(0xffffffffu, (v >> 62) == 0ull)) {
+                    if (++spins > LOOKBACK_SPIN_LIMIT) __trap();         // never hang the GPU
+                    __nanosleep(20);
+                    if (mine >= 0 && (v >> 62) == 0ull) v = ld_status(status + mine);
+                }
+                const unsigned prefix_mask = __ballot_sync(0xffffffffu, (v >> 62) == 2ull);
+                const int first = prefix_mask ? (__ffs(prefix_mask) - 1) : 31;
+                long long contrib = (lane <= first) ? (long long)(v & ((1ull << 62) - 1ull)) : 0ll;
+#pragma unroll
+                for (int o = 16; o; o >>= 1) contrib += __shfl_xor_sync(0xffffffffu, contrib, o);
+                exclusive += contrib;
+                if (prefix_mask) break;
+                idx -= 32;
+            }
+        }
+        if (lane == 0) {
+            st_status(status + tile, (2ull << 62) | (unsigned long long)(exclusive + block_total));
+            base_s = exclusive;
+            if (tile == n_tiles - 1) *total_hits = exclusive + block_total;
+        }
+    }
+    __syncthreads();
+    const long long base = base_s;
+    if (lr < n_rays) indices[lr] = (int)(base + excl[tid]);
+    // the origin is the same for every ray of a view (optixPrograms.cu:75-78); thread 0 of a
+    // tile always holds a ray
+    __shared__ float origin_s[3];
+    if (tid == 0) { origin_s[0] = ox0; origin_s[1] = oy0; origin_s[2] = oz0; }
+    __syncthreads();
+    const float o0x = origin_s[0], o0y = origin_s[1], o0z = origin_s[2];
+
+    // ---- 4: copy out, slot = thread
+    for (int k0 = 0; k0 < block_total; k0 += MARCH_BLOCK) {
+        const int k = k0 + tid;
+        const bool live = k < block_total;
+        if (live) {
+            int lo = 0, hi = MARCH_BLOCK - 1;                    // largest r with excl[r] <= k
+            while (lo < hi) {
+                const int mid = (lo + hi + 1) >> 1;
+                if (excl[mid] <= k) lo = mid; else hi = mid - 1;
+            }
+            const int j = k - excl[lo];
+            const uint32_t* w = rec + lo * row + 6 * j;
+            const float ts = __uint_as_float(w[0]), te = __uint_as_float(w[1]);
+            const float ex = __uint_as_float(w[2]), ey = __uint_as_float(w[3]), ez = __uint_as_float(w[4]);
+            float px = o0x, py = o0y, pz = o0z;                  // the origin this hit was launched from
+            if (j > 0) { px = __uint_as_float(w[-4]); py = __uint_as_float(w[-3]); pz = __uint_as_float(w[-2]); }
+            const float* d = dirs + 3 * lo;
+            pts[3 * tid] = rn_fma(ts, d[0], px);                 // optixPrograms.cu:194-196
+            pts[3 * tid + 1] = rn_fma(ts, d[1], py);
+            pts[3 * tid + 2] = rn_fma(ts, d[2], pz);
+            pts[3 * MARCH_BLOCK + 3 * tid] = ex;
+            pts[3 * MARCH_BLOCK + 3 * tid + 1] = ey;
+            pts[3 * MARCH_BLOCK + 3 * tid + 2] = ez;
+            const long long slot = base + k;
+            if (slot < out.capacity) {
+                if (out.t_start) out.t_start[slot] = ts;
+                if (out.t_end) out.t_end[slot] = te;
+                if (out.hit_cells) out.hit_cells[slot] = (int)w[5];
+            }
+        }
+        __syncthreads();
+        const int words = 3 * min(MARCH_BLOCK, block_total - k0);
+        const long long w0 = 3 * (base + k0);
+        const long long wcap = 3 * out.capacity;
+#pragma unroll
+        for (int m = 0; m < 3; m++) {
+            const int wi = tid + m * MARCH_BLOCK;
+            if (wi < words && w0 + wi < wcap) {
+                out.start_points[w0 + wi] = pts[wi];
+                out.end_points[w0 + wi] = pts[3 * MARCH_BLOCK + wi];
+            }
+        }
+        __syncthreads();
+    }
+}
+
+static size_t onepass_smem_bytes(int cap)
+{
+    return sizeof(uint32_t) * ((size_t)MARCH_BLOCK * (6 * cap + 1) + 2 * MARCH_BLOCK * 3 + MARCH_BLOCK * 3 +
+                               MARCH_BLOCK + 1 + 3);
+}
+
 // Dense layout of the reference (slot = ray*arr + j, optixPrograms.cu:184), one pass.
 __global__ void __launch_bounds__(MARCH_BLOCK)
 march_dense_kernel(const uint32_t* __restrict__ bits, int G, CamArgs cam, long long n_rays, int arr_size,
@@ -416,7 +645,9 @@ extern "C" size_t rtxnerf_ray_march_workspace_bytes(long long n_rays)
 {
     long long nb = (n_rays + MARCH_BLOCK - 1) / MARCH_BLOCK;
     if (nb < 1) nb = 1;
-    return (size_t)nb * (sizeof(int) + sizeof(long long)) + 256;
+    // [block_offsets nb x i64][block_sums nb x i32, padded to 8][status nb x u64][ticket u64]
+    return (size_t)nb * sizeof(long long) + (((size_t)nb * sizeof(int) + 7) & ~(size_t)7) +
+           (size_t)nb * sizeof(unsigned long long) + sizeof(unsigned long long) + 256;
 }
 
 extern "C" int rtxnerf_ray_march_csr(const rtxnerf_grid* grid, const rtxnerf_camera* cam, long long ray_begin,
@@ -440,14 +671,36 @@ extern "C" int rtxnerf_ray_march_csr(const rtxnerf_grid* grid, const rtxnerf_cam
     long long* block_offsets = reinterpret_cast<long long*>(workspace);
     int* block_sums = reinterpret_cast<int*>(block_offsets + nb);
     CamArgs c{cam->look_at, cam->focal_length, cam->aspect_ratio, cam->width, cam->height};
+    FillOut fo{hits->t_start, hits->t_end, hits->start_points, hits->end_points, hits->hit_cells, hits->capacity};
+    static int two_pass = -1;   // development knob: RTXNERF_MARCH_TWO_PASS=1 forces count -> scan -> fill
+    if (two_pass < 0) {
+        const char* e = getenv("RTXNERF_MARCH_TWO_PASS");
+        two_pass = (e && e[0] == '1') ? 1 : 0;
+    }
+    if (max_hits <= ONEPASS_MAX_CAP && !two_pass) {
+        unsigned long long* status = reinterpret_cast<unsigned long long*>(
+            reinterpret_cast<char*>(block_sums) + (((size_t)nb * sizeof(int) + 7) & ~(size_t)7));
+        unsigned long long* ticket = status + nb;
+        const size_t smem = onepass_smem_bytes(max_hits);
+        static size_t smem_set = 0;
+        if (smem > smem_set) {
+            RTX_CUDA_TRY(cudaFuncSetAttribute(march_onepass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              (int)onepass_smem_bytes(ONEPASS_MAX_CAP)));
+            smem_set = onepass_smem_bytes(ONEPASS_MAX_CAP);
+        }
+        RTX_CUDA_TRY(cudaMemsetAsync(status, 0, ((size_t)nb + 1) * sizeof(unsigned long long), s));
+        march_onepass_kernel<<<(unsigned)nb, MARCH_BLOCK, smem, s>>>(
+            grid->d_bits, grid->G, c, ray_begin, n_rays, max_hits, hits->num_hits, hits->view_dirs,
+            hits->ray_origins, hits->indices, fo, status, ticket, hits->total_hits, (int)nb);
+        return rtx_launch_status();
+    }
     march_count_kernel<<<(unsigned)nb, MARCH_BLOCK, 0, s>>>(grid->d_bits, grid->G, c, ray_begin, n_rays, max_hits,
                                                           hits->num_hits, hits->view_dirs, hits->ray_origins,
                                                           block_sums);
     block_scan_kernel<<<1, 1024, 0, s>>>(block_sums, (int)nb, block_offsets, hits->total_hits);
-    FillOut fo{hits->t_start, hits->t_end, hits->start_points, hits->end_points, hits->hit_cells, hits->capacity};
     march_fill_kernel<<<(unsigned)nb, MARCH_BLOCK, 0, s>>>(grid->d_bits, grid->G, c, ray_begin, n_rays, max_hits,
                                                          hits->num_hits, block_offsets, hits->indices, fo);
-    return rtx_launch_status();
+    return rtx_launch_status(3);
 }
 
 extern "C" int rtxnerf_ray_march_dense(const rtxnerf_params* p, void* stream)

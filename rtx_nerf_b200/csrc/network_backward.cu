@@ -465,7 +465,7 @@ extern "C" int rtxnerf_network_backward_rays(const rtxnerf_hashgrid* enc, const 
     const long long max_blocks = (long long)RTX_NUM_SMS * 8;
     hashgrid_backward_kernel<<<(unsigned)(groups < max_blocks ? groups : max_blocks), HB_WARPS * 32, 0, s>>>(
         lv, d_samples, sample_stride, d_dencoded, d_num_hits, d_indices, n_rays, samples_per_segment, d_grad_table);
-    return rtx_launch_status();
+    return rtx_launch_status(2);
 }
 
 extern "C" int rtxnerf_l2_loss(const float* d_pred, const float* d_target, long long n, float loss_scale,

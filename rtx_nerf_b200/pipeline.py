@@ -37,7 +37,7 @@ class ViewRenderer:
         self.pose_dev = torch.empty(16, dtype=torch.float32, device=dev)
         self.pose_pinned = torch.empty(16, dtype=torch.float32).pin_memory()
         self.pixels_pinned = torch.empty((self.R, 3), dtype=torch.float32).pin_memory()
-        self.launches_per_view = 3 + 1 + radiance.launches + 1
+        self.launches_per_view = (1 if max_hits <= 32 else 3) + 1 + radiance.launches + 1
 
     # --- stages (all asynchronous on the current stream) -------------------------------
     def stage_march(self):
@@ -185,7 +185,9 @@ class Trainer:
         self.allreduce()
         self.optimizer_step()
 
-    launches_per_step = 3 + 1 + 1 + 1 + 1 + 1 + 2 + 1
+    @property
+    def launches_per_step(self):
+        return self.view.launches_per_view + 1 + 1 + 2 + 1   # + loss, compositing bwd, network bwd (2), Adam
 
 
 class _EncodedNetworkRadiance:

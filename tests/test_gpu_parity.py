@@ -72,6 +72,59 @@ def test_ray_march_csr_bit_exact(cuda_api, orc, G, p, W, H, max_hits, seed):
         _assert_march_equal(gpu, ora)
 
 
+@pytest.mark.parametrize("G,kind,W,H,max_hits,seed", [
+    (128, "lego", 200, 150, 16, 0),   # bench shape (S=4 x H_max=16), 235 tiles: multi-window look-back
+    (128, "lego", 96, 64, 32, 1),     # training shape (H_max=32), largest one-pass cap
+    (32, 0.15, 64, 64, 8, 2),
+    (64, 0.5, 50, 30, 1, 3),          # one hit per ray
+    (16, 0.02, 37, 29, 5, 4),         # sparse: most rays miss, ragged last tile
+])
+def test_ray_march_one_pass_bit_exact(cuda_api, orc, G, kind, W, H, max_hits, seed):
+    """max_hits <= 32 takes the single-pass kernel (shared-memory hit staging, decoupled look-back,
+    coalesced copy-out); same bit-exact contract as the two-pass path."""
+    occ = synth.occupancy_lego(G, seed=seed) if kind == "lego" else synth.occupancy_bernoulli(G, kind, seed=seed)
+    focal = synth.focal_length()
+    for pose in synth.poses(2, seed=300 + seed):
+        gpu = _march_gpu(cuda_api, occ, G, pose, focal, W / H, W, H, max_hits)
+        ora = orc.ray_march_dda(pose, focal, W / H, W, H, occ, G, max_hits=max_hits, csr=True)
+        _assert_march_equal(gpu, ora)
+
+
+def test_ray_march_one_pass_edges(cuda_api, orc):
+    focal = synth.focal_length()
+    G = 16
+    occ = synth.occupancy_bernoulli(G, 0.4, seed=9)
+    pose = synth.poses(1, seed=8)[0]
+    full = orc.ray_march_dda(pose, focal, 1.0, 24, 24, occ, G, max_hits=12, csr=True)
+    # empty grid
+    gpu = _march_gpu(cuda_api, np.zeros(G ** 3, np.uint8), G, pose, focal, 1.0, 16, 16, 8)
+    assert gpu["total"] == 0 and gpu["num_hits"].sum() == 0 and np.all(gpu["indices"] == 0)
+    # ragged ray sub-range
+    gpu = _march_gpu(cuda_api, occ, G, pose, focal, 1.0, 24, 24, 12, ray_begin=100, n_rays=333)
+    assert np.array_equal(gpu["num_hits"], full.num_hits[100:433])
+    lo, hi = full.indices[100], full.indices[432] + full.num_hits[432]
+    assert np.array_equal(gpu["hit_cells"], full.hit_prims[lo:hi])
+    assert np.array_equal(gpu["start_points"], full.start_points[lo:hi])
+    assert np.array_equal(gpu["end_points"], full.end_points[lo:hi])
+    # capacity overflow
+    gpu = _march_gpu(cuda_api, occ, G, pose, focal, 1.0, 24, 24, 12, capacity=100)
+    assert gpu["total"] == full.total_hits and gpu["hit_cells"].shape[0] == 100
+    assert np.array_equal(gpu["hit_cells"], full.hit_prims[:100])
+    assert np.array_equal(gpu["end_points"], full.end_points[:100])
+    # operands outside the certified range of the hoisted-reciprocal division: zero, denormal
+    # and huge origin components, axis-parallel view (identity rotation: tiny direction components)
+    for t in ((0.0, 0.0, 0.0), (1e-37, -3e-39, 0.0), (0.0, 2.5, 1e-30), (40.0, 0.0, -1e20)):
+        odd = np.eye(4, dtype=np.float32)
+        odd[:3, 3] = np.array(t, np.float32)
+        for W, H in ((24, 24), (1, 1), (3, 1)):
+            gpu = _march_gpu(cuda_api, occ, G, odd, np.float32(40.0), W / H, W, H, 12)
+            ora = orc.ray_march_dda(odd, np.float32(40.0), W / H, W, H, occ, G, max_hits=12, csr=True)
+            _assert_march_equal(gpu, ora)
+            gpu = _march_gpu(cuda_api, occ, G, odd, np.float32(40.0), W / H, W, H, 48)   # two-pass path
+            ora = orc.ray_march_dda(odd, np.float32(40.0), W / H, W, H, occ, G, max_hits=48, csr=True)
+            _assert_march_equal(gpu, ora)
+
+
 def test_ray_march_lego_config1(cuda_api, orc):
     G, W, H = 128, 64, 64
     occ = synth.occupancy_lego(G, seed=0)
