@@ -75,15 +75,6 @@ __device__ __forceinline__ RayGen raygen(const float* __restrict__ l, float foca
 // ------------------------------------------------------------------------------------ sweep
 __device__ __forceinline__ float plane_at(int i, float L) { return rn_fma((float)i, L, -1.0f); }  // exact
 
-__device__ __forceinline__ int locate_cell(float ok, int G, float L, float half_g)
-{
-    int i = (int)floorf(rn_mul(rn_add(ok, 1.0f), half_g));
-    i = max(0, min(G - 1, i));
-    while (i > 0 && ok < plane_at(i, L)) i--;
-    while (i < G - 1 && ok >= plane_at(i + 1, L)) i++;
-    return i;
-}
-
 struct HitRecord {
     float t_start, t_end;
     float sx, sy, sz, ex, ey, ez;
@@ -96,34 +87,210 @@ struct HitRecord {
 // div.rn.f32 costs MUFU.RCP + 2 refinement FMAs + FCHK + branch + 5 FMAs each time.  With
 // r = RN(1/d) computed once per ray, two Markstein correction steps give the correctly
 // rounded quotient whenever no intermediate can underflow or overflow: the residual
-// a - d*q is an exact multiple of 2^(exp(a)-46), representable for |a| >= 2^-103.  `fast`
-// certifies the operand ranges (set per ray for d, per relaunch for o, see axis_fast);
+// a - d*q is an exact multiple of 2^(exp(a)-46), representable for |a| >= 2^-103.  FAST
+// certifies the operand ranges (per ray for d, per relaunch for o: dir_fast/origin_fast);
 // anything else takes div.rn itself.  a is never -0 here (a = plane - o with plane != -0),
 // so the sign of a zero quotient is the IEEE one as well.  Checked against a/d on the host
 // for 3e8 random and patterned operand pairs: 0 mismatches.
-__device__ __forceinline__ float div_exact(float a, float d, float r, bool fast)
+__device__ __forceinline__ float div_exact(float a, float d, float r)
 {
     const float q0 = rn_mul(a, r);
     const float e0 = rn_fma(-d, q0, a);
     const float q1 = rn_fma(e0, r, q0);
     const float e1 = rn_fma(-d, q1, a);
-    float q = rn_fma(e1, r, q1);
-    if (!fast) q = rn_div(a, d);
-    return q;
+    return rn_fma(e1, r, q1);
 }
 
-// d certifies the fast path when 2^-30 <= |d| <= 2 (direction components are <= 1)
+// d certifies the fast path when 2^-30 <= |d| < 4 (direction components are <= 1)
 __device__ __forceinline__ bool dir_fast(float d)
 {
-    const uint32_t e = (__float_as_uint(d) >> 23) & 0xffu;
-    return e >= 127u - 30u && e <= 128u;
+    return ((__float_as_uint(d) >> 23) & 0xffu) - (127u - 30u) < 32u;
 }
 // o certifies it when o == 0 or 2^-90 <= |o| < 2^60: then a = plane - o (planes are
 // multiples of 2/G, |plane| <= 1) is 0 or has 2^-103 <= |a| < 2^61
 __device__ __forceinline__ bool origin_fast(float o)
 {
-    const uint32_t e = (__float_as_uint(o) >> 23) & 0xffu;
-    return (e >= 127u - 90u && e < 127u + 60u) || (__float_as_uint(o) << 1) == 0u;
+    const uint32_t b = __float_as_uint(o);
+    return (((b >> 23) & 0xffu) - (127u - 90u) < 150u) | ((b << 1) == 0u);
+}
+
+// Per-axis sweep state.  near/far are the two slab values of the current cell labelled by the
+// sign of d (far = (lo-o)/d when d<0 else (hi-o)/d, the value optixPrograms.cu:201-206 picks as
+// the exit candidate); {near, far} == {tl, th}, so min/max of the pair are the reference's.
+struct AxisState {
+    float near_t, far_t;   // slab values of the current cell
+    float far_plane;       // plane the far value belongs to (exact float)
+    int i;                 // cell index on this axis
+};
+
+__device__ __forceinline__ void axis_enter(AxisState& a, float o, float d, float r, int G, float L, float half_g)
+{
+    // cell containing o (planes compared exactly), clamped to the grid
+    int i = (int)floorf(rn_mul(rn_add(o, 1.0f), half_g));
+    i = max(0, min(G - 1, i));
+    float lo = plane_at(i, L);
+    while (i > 0 && o < lo) { i--; lo = plane_at(i, L); }
+    float hi = plane_at(i + 1, L);
+    while (i < G - 1 && o >= hi) { i++; lo = hi; hi = plane_at(i + 1, L); }
+    const float tl = div_exact(rn_sub(lo, o), d, r), th = div_exact(rn_sub(hi, o), d, r);
+    const bool neg = d < 0.0f;
+    a.i = i;
+    a.near_t = neg ? th : tl;
+    a.far_t = neg ? tl : th;
+    a.far_plane = neg ? lo : hi;
+}
+
+// One launch of the reference's relaunch loop (optixPrograms.cu:99-115): sweep from origin o
+// until a cell is accepted (emit + true) or the ray leaves the grid / interval (false).
+// Certified operands only (every d normal and non-zero, every slab value finite): the sweep
+// direction and the exit candidate both follow the sign of d, so the state is (near, far).
+template <bool WANT_START, class Emit>
+__device__ __forceinline__ bool march_segment(const uint32_t* __restrict__ bits, int G, float L, float half_g,
+                                              float& ox, float& oy, float& oz, float dx, float dy, float dz,
+                                              float rx, float ry, float rz, int& nh, Emit& emit)
+{
+    AxisState X, Y, Z;
+    axis_enter(X, ox, dx, rx, G, L, half_g);
+    axis_enter(Y, oy, dy, ry, G, L, half_g);
+    axis_enter(Z, oz, dz, rz, G, L, half_g);
+    // signed plane step per axis; the sign of d is fixed for the ray (d == 0 never advances)
+    const float slx = dx < 0.0f ? -L : L, sly = dy < 0.0f ? -L : L, slz = dz < 0.0f ? -L : L;
+    const int six = dx < 0.0f ? -1 : 1, siy = dy < 0.0f ? -1 : 1, siz = dz < 0.0f ? -1 : 1;
+    for (;;) {
+        // optixPrograms.cu:143-156 (fminf/fmaxf == PTX min/max: a NaN operand yields the other)
+        const float txx = fmaxf(X.near_t, X.far_t), txy = fmaxf(Y.near_t, Y.far_t), txz = fmaxf(Z.near_t, Z.far_t);
+        const unsigned p = ((unsigned)X.i * (unsigned)G + (unsigned)Y.i) * (unsigned)G + (unsigned)Z.i;
+        const bool occ = (__ldg(bits + (p >> 5)) >> (p & 31u)) & 1u;
+        if (occ) {
+            const float tmin = fmaxf(fmaxf(fmaxf(-INFINITY, fminf(X.near_t, X.far_t)), fminf(Y.near_t, Y.far_t)),
+                                     fminf(Z.near_t, Z.far_t));
+            const float tmax = fminf(fminf(fminf(INFINITY, txx), txy), txz);
+            if (tmax > tmin) {                                              // :164
+                const float t = (tmin < 0.0f && tmax > CLAMP_EPS) ? 0.0f : tmin;  // :165-166
+                if (t >= 0.0f && t <= RAY_TMAX) {                          // OptiX ray interval
+                    HitRecord h;
+                    h.t_start = t;                                          // :188-189
+                    if (WANT_START) {
+                        h.sx = rn_fma(t, dx, ox);                           // :194-196
+                        h.sy = rn_fma(t, dy, oy);
+                        h.sz = rn_fma(t, dz, oz);
+                    }
+                    // :201-207 exit plane by the sign of d = the far value of each axis
+                    const float t_e = fminf(fminf(X.far_t, Y.far_t), Z.far_t);
+                    h.t_end = t_e;
+                    h.ex = rn_fma(dx, t_e, ox);                             // :209-211
+                    h.ey = rn_fma(dy, t_e, oy);
+                    h.ez = rn_fma(dz, t_e, oz);
+                    h.cell = (int)p;
+                    emit(nh, h);
+                    nh++;                                                   // :241
+                    ox = h.ex;                                              // :245-247 relaunch from the exit point
+                    oy = h.ey;
+                    oz = h.ez;
+                    return true;
+                }
+            }
+        }
+        // advance the axis whose interval ends first (ties: lowest axis; NaN/inf never advance)
+        int ks = -1;
+        float best = INFINITY;
+        if (txx < best) { best = txx; ks = 0; }
+        if (txy < best) { best = txy; ks = 1; }
+        if (txz < best) { best = txz; ks = 2; }
+        if (ks < 0 || best > RAY_TMAX) return false;
+        const float os = ks == 0 ? ox : (ks == 1 ? oy : oz);
+        const float ds = ks == 0 ? dx : (ks == 1 ? dy : dz);
+        const float rs = ks == 0 ? rx : (ks == 1 ? ry : rz);
+        const float pl = (ks == 0 ? X.far_plane : (ks == 1 ? Y.far_plane : Z.far_plane)) +
+                         (ks == 0 ? slx : (ks == 1 ? sly : slz));          // next plane: exact
+        const float tn = div_exact(rn_sub(pl, os), ds, rs);
+        int moved;
+        if (ks == 0) { X.i += six; X.near_t = X.far_t; X.far_t = tn; X.far_plane = pl; moved = X.i; }
+        else if (ks == 1) { Y.i += siy; Y.near_t = Y.far_t; Y.far_t = tn; Y.far_plane = pl; moved = Y.i; }
+        else { Z.i += siz; Z.near_t = Z.far_t; Z.far_t = tn; Z.far_plane = pl; moved = Z.i; }
+        if ((unsigned)moved >= (unsigned)G) return false;                   // left the grid
+    }
+}
+
+// The same launch for operands outside the certified range (zero / denormal / huge origin
+// components, |d| < 2^-30, d == +-0): div.rn everywhere, (tl, th) state, and the sweep
+// direction taken from `ds > 0` exactly as the oracle does, so the degenerate cases
+// (inf / NaN slab values) resolve identically.
+__device__ __forceinline__ int locate_cell(float ok, int G, float L, float half_g)
+{
+    int i = (int)floorf(rn_mul(rn_add(ok, 1.0f), half_g));
+    i = max(0, min(G - 1, i));
+    while (i > 0 && ok < plane_at(i, L)) i--;
+    while (i < G - 1 && ok >= plane_at(i + 1, L)) i++;
+    return i;
+}
+
+template <bool WANT_START, class Emit>
+__device__ __noinline__ bool march_segment_generic(const uint32_t* __restrict__ bits, int G, float L, float half_g,
+                                                   float& ox, float& oy, float& oz, float dx, float dy, float dz,
+                                                   int& nh, Emit& emit)
+{
+    int ix = locate_cell(ox, G, L, half_g);
+    int iy = locate_cell(oy, G, L, half_g);
+    int iz = locate_cell(oz, G, L, half_g);
+    float tlx = rn_div(rn_sub(plane_at(ix, L), ox), dx), thx = rn_div(rn_sub(plane_at(ix + 1, L), ox), dx);
+    float tly = rn_div(rn_sub(plane_at(iy, L), oy), dy), thy = rn_div(rn_sub(plane_at(iy + 1, L), oy), dy);
+    float tlz = rn_div(rn_sub(plane_at(iz, L), oz), dz), thz = rn_div(rn_sub(plane_at(iz + 1, L), oz), dz);
+    for (;;) {
+        if ((unsigned)ix >= (unsigned)G || (unsigned)iy >= (unsigned)G || (unsigned)iz >= (unsigned)G) return false;
+        float txx = fmaxf(tlx, thx), txy = fmaxf(tly, thy), txz = fmaxf(tlz, thz);
+        float tmin = fmaxf(fmaxf(fmaxf(-INFINITY, fminf(tlx, thx)), fminf(tly, thy)), fminf(tlz, thz));
+        float tmax = fminf(fminf(fminf(INFINITY, txx), txy), txz);
+        unsigned p = ((unsigned)ix * (unsigned)G + (unsigned)iy) * (unsigned)G + (unsigned)iz;
+        bool occ = (__ldg(bits + (p >> 5)) >> (p & 31u)) & 1u;
+        if (occ && tmax > tmin) {
+            float t = (tmin < 0.0f && tmax > CLAMP_EPS) ? 0.0f : tmin;
+            if (t >= 0.0f && t <= RAY_TMAX) {
+                HitRecord h;
+                h.t_start = t;
+                if (WANT_START) {
+                    h.sx = rn_fma(t, dx, ox);
+                    h.sy = rn_fma(t, dy, oy);
+                    h.sz = rn_fma(t, dz, oz);
+                }
+                float t_e = fminf(fminf(dx < 0.0f ? tlx : thx, dy < 0.0f ? tly : thy), dz < 0.0f ? tlz : thz);
+                h.t_end = t_e;
+                h.ex = rn_fma(dx, t_e, ox);
+                h.ey = rn_fma(dy, t_e, oy);
+                h.ez = rn_fma(dz, t_e, oz);
+                h.cell = (int)p;
+                emit(nh, h);
+                nh++;
+                ox = h.ex;
+                oy = h.ey;
+                oz = h.ez;
+                return true;
+            }
+        }
+        int ks = -1;
+        float best = INFINITY;
+        if (txx < best) { best = txx; ks = 0; }
+        if (txy < best) { best = txy; ks = 1; }
+        if (txz < best) { best = txz; ks = 2; }
+        if (ks < 0 || best > RAY_TMAX) return false;
+        float os = ks == 0 ? ox : (ks == 1 ? oy : oz);
+        float ds = ks == 0 ? dx : (ks == 1 ? dy : dz);
+        int is = ks == 0 ? ix : (ks == 1 ? iy : iz);
+        float tls = ks == 0 ? tlx : (ks == 1 ? tly : tlz);
+        float ths = ks == 0 ? thx : (ks == 1 ? thy : thz);
+        if (ds > 0.0f) {
+            is++;
+            tls = ths;
+            ths = rn_div(rn_sub(plane_at(is + 1, L), os), ds);
+        } else {
+            is--;
+            ths = tls;
+            tls = rn_div(rn_sub(plane_at(is, L), os), ds);
+        }
+        if (ks == 0) { ix = is; tlx = tls; thx = ths; }
+        else if (ks == 1) { iy = is; tly = tls; thy = ths; }
+        else { iz = is; tlz = tls; thz = ths; }
+    }
 }
 
 // Marches one ray; calls emit(j, HitRecord) for hit j.  Returns the number of hits (<= cap).
@@ -134,81 +301,15 @@ __device__ __forceinline__ int march_ray(const uint32_t* __restrict__ bits, int 
     const float L = 2.0f / (float)G;
     const float half_g = 0.5f * (float)G;
     const float rx = __frcp_rn(dx), ry = __frcp_rn(dy), rz = __frcp_rn(dz);
-    const bool dfx = dir_fast(dx), dfy = dir_fast(dy), dfz = dir_fast(dz);
+    const bool dfast = dir_fast(dx) & dir_fast(dy) & dir_fast(dz);
     int nh = 0;
     while (nh < cap) {
-        int ix = locate_cell(ox, G, L, half_g);
-        int iy = locate_cell(oy, G, L, half_g);
-        int iz = locate_cell(oz, G, L, half_g);
-        const bool fx = dfx && origin_fast(ox), fy = dfy && origin_fast(oy), fz = dfz && origin_fast(oz);
-        float tlx = div_exact(rn_sub(plane_at(ix, L), ox), dx, rx, fx),
-              thx = div_exact(rn_sub(plane_at(ix + 1, L), ox), dx, rx, fx);
-        float tly = div_exact(rn_sub(plane_at(iy, L), oy), dy, ry, fy),
-              thy = div_exact(rn_sub(plane_at(iy + 1, L), oy), dy, ry, fy);
-        float tlz = div_exact(rn_sub(plane_at(iz, L), oz), dz, rz, fz),
-              thz = div_exact(rn_sub(plane_at(iz + 1, L), oz), dz, rz, fz);
-        bool found = false;
-        for (;;) {
-            if ((unsigned)ix >= (unsigned)G || (unsigned)iy >= (unsigned)G || (unsigned)iz >= (unsigned)G) break;
-            // optixPrograms.cu:143-156 (fminf/fmaxf == PTX min/max: a NaN operand yields the other)
-            float txx = fmaxf(tlx, thx), txy = fmaxf(tly, thy), txz = fmaxf(tlz, thz);
-            float tmin = fmaxf(fmaxf(fmaxf(-INFINITY, fminf(tlx, thx)), fminf(tly, thy)), fminf(tlz, thz));
-            float tmax = fminf(fminf(fminf(INFINITY, txx), txy), txz);
-            unsigned p = ((unsigned)ix * (unsigned)G + (unsigned)iy) * (unsigned)G + (unsigned)iz;
-            bool occ = (__ldg(bits + (p >> 5)) >> (p & 31u)) & 1u;
-            if (occ && tmax > tmin) {                                  // :164
-                float t = (tmin < 0.0f && tmax > CLAMP_EPS) ? 0.0f : tmin;  // :165-166
-                if (t >= 0.0f && t <= RAY_TMAX) {                      // OptiX ray interval
-                    HitRecord h;
-                    h.t_start = t;                                      // :188-189
-                    if (WANT_START) {
-                        h.sx = rn_fma(t, dx, ox);                       // :194-196
-                        h.sy = rn_fma(t, dy, oy);
-                        h.sz = rn_fma(t, dz, oz);
-                    }
-                    // :201-207 exit plane by the sign of d: (lo-o)/d when d<0 else (hi-o)/d
-                    float t_e = fminf(fminf(dx < 0.0f ? tlx : thx, dy < 0.0f ? tly : thy), dz < 0.0f ? tlz : thz);
-                    h.t_end = t_e;
-                    h.ex = rn_fma(dx, t_e, ox);                         // :209-211
-                    h.ey = rn_fma(dy, t_e, oy);
-                    h.ez = rn_fma(dz, t_e, oz);
-                    h.cell = (int)p;
-                    emit(nh, h);
-                    nh++;                                               // :241
-                    ox = h.ex;                                          // :245-247 relaunch from the exit point
-                    oy = h.ey;
-                    oz = h.ez;
-                    found = true;
-                    break;
-                }
-            }
-            // advance the axis whose interval ends first (ties: lowest axis; NaN/inf never advance)
-            int ks = -1;
-            float best = INFINITY;
-            if (txx < best) { best = txx; ks = 0; }
-            if (txy < best) { best = txy; ks = 1; }
-            if (txz < best) { best = txz; ks = 2; }
-            if (ks < 0 || best > RAY_TMAX) break;
-            float os = ks == 0 ? ox : (ks == 1 ? oy : oz);
-            float ds = ks == 0 ? dx : (ks == 1 ? dy : dz);
-            float rs = ks == 0 ? rx : (ks == 1 ? ry : rz);
-            bool fs = ks == 0 ? fx : (ks == 1 ? fy : fz);
-            int is = ks == 0 ? ix : (ks == 1 ? iy : iz);
-            float tls = ks == 0 ? tlx : (ks == 1 ? tly : tlz);
-            float ths = ks == 0 ? thx : (ks == 1 ? thy : thz);
-            if (ds > 0.0f) {
-                is++;
-                tls = ths;
-                ths = div_exact(rn_sub(plane_at(is + 1, L), os), ds, rs, fs);
-            } else {
-                is--;
-                ths = tls;
-                tls = div_exact(rn_sub(plane_at(is, L), os), ds, rs, fs);
-            }
-            if (ks == 0) { ix = is; tlx = tls; thx = ths; }
-            else if (ks == 1) { iy = is; tly = tls; thy = ths; }
-            else { iz = is; tlz = tls; thz = ths; }
-        }
+        const bool fast = dfast & origin_fast(ox) & origin_fast(oy) & origin_fast(oz);
+        bool found;
+        if (fast)
+            found = march_segment<WANT_START>(bits, G, L, half_g, ox, oy, oz, dx, dy, dz, rx, ry, rz, nh, emit);
+        else
+            found = march_segment_generic<WANT_START>(bits, G, L, half_g, ox, oy, oz, dx, dy, dz, nh, emit);
         if (!found) break;
     }
     return nh;
@@ -386,6 +487,7 @@ march_onepass_kernel(const uint32_t* __restrict__ bits, int G, CamArgs cam, long
     float* pts = reinterpret_cast<float*>(dyn + MARCH_BLOCK * row);   // [2][MARCH_BLOCK*3]
     float* dirs = pts + 2 * MARCH_BLOCK * 3;                    // [MARCH_BLOCK][3]
     int* excl = reinterpret_cast<int*>(dirs + MARCH_BLOCK * 3); // [MARCH_BLOCK + 1]
+    uint8_t* owner = reinterpret_cast<uint8_t*>(excl + MARCH_BLOCK + 4);   // [MARCH_BLOCK * cap]: slot -> ray
     __shared__ int warp_sums[MARCH_BLOCK / 32];
     __shared__ int tile_s;
     __shared__ long long base_s;
@@ -434,8 +536,10 @@ march_onepass_kernel(const uint32_t* __restrict__ bits, int G, CamArgs cam, long
         woff += (w < warp) ? warp_sums[w] : 0;
         block_total += warp_sums[w];
     }
-    excl[tid] = woff + inc - nh;
+    const int my_excl = woff + inc - nh;
+    excl[tid] = my_excl;
     if (tid == 0) excl[MARCH_BLOCK] = block_total;
+    for (int j = 0; j < nh; j++) owner[my_excl + j] = (uint8_t)tid;
     if (warp == 0) {
         long long exclusive = 0;
         if (tile > 0) {
@@ -482,11 +586,7 @@ march_onepass_kernel(const uint32_t* __restrict__ bits, int G, CamArgs cam, long
         const int k = k0 + tid;
         const bool live = k < block_total;
         if (live) {
-            int lo = 0, hi = MARCH_BLOCK - 1;                    // largest r with excl[r] <= k
-            while (lo < hi) {
-                const int mid = (lo + hi + 1) >> 1;
-                if (excl[mid] <= k) lo = mid; else hi = mid - 1;
-            }
+            const int lo = owner[k];                             // the ray that owns slot k
             const int j = k - excl[lo];
             const uint32_t* w = rec + lo * row + 6 * j;
             const float ts = __uint_as_float(w[0]), te = __uint_as_float(w[1]);
@@ -526,7 +626,7 @@ march_onepass_kernel(const uint32_t* __restrict__ bits, int G, CamArgs cam, long
 static size_t onepass_smem_bytes(int cap)
 {
     return sizeof(uint32_t) * ((size_t)MARCH_BLOCK * (6 * cap + 1) + 2 * MARCH_BLOCK * 3 + MARCH_BLOCK * 3 +
-                               MARCH_BLOCK + 1 + 3);
+                               MARCH_BLOCK + 4) + (size_t)MARCH_BLOCK * cap;
 }
 
 // Dense layout of the reference (slot = ray*arr + j, optixPrograms.cu:184), one pass.
