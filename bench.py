@@ -178,15 +178,18 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    stage_names = ["march", "sampler", "network", "composite"]
-    stage_fns = [r.stage_march, r.stage_sampler, r.stage_radiance, r.stage_composite]
+    # the render path: march + ONE fused sampler/network/compositing kernel (view_fused.cu);
+    # --staged times the reference-shaped four-stage path through its separate entry points
+    stage_list = r.stages(fused=not args.staged)
+    stage_names = [n for n, _ in stage_list]
+    stage_fns = [f for _, f in stage_list]
 
     # ---- warm-up
     clocks = ClockSampler(local) if rank == 0 else None
     if clocks:
         clocks.start()
     for k in range(args.warmup):
-        r.render_device(poses_dev[k])
+        r.render_device(poses_dev[k], fused=not args.staged)
     barrier()
 
     # ---- per-stage durations (CUDA events on the launch stream; explains the headline)
@@ -202,7 +205,7 @@ def run_ours(args):
     stage_ms = [float(np.mean([ev[k][i].elapsed_time(ev[k][i + 1]) for k in range(n_stage_steps)]))
                 for i in range(len(stage_fns))]
 
-    # ---- timed: EXACTLY K steps.  The six launches of a view are captured once in a CUDA graph
+    # ---- timed: EXACTLY K steps.  The launches of a view are captured once in a CUDA graph
     # (every size that depends on the hit count is read on the device), each step = pose copy +
     # one graph launch; pose already resident in HBM.
     launches0 = _lib.kernel_launches()
@@ -212,6 +215,13 @@ def run_ours(args):
             fn()
     launches_per_step = _lib.kernel_launches() - launches0
     graph.replay()
+    # untimed clock spin-up: a B200 coming out of idle needs a few hundred ms of load to reach
+    # its steady SM clock; without it the first process on a fresh box measures the ramp
+    t_spin = time.perf_counter()
+    while time.perf_counter() - t_spin < args.spinup:
+        for _ in range(8):
+            graph.replay()
+        torch.cuda.synchronize()
     hits_total = torch.zeros(1, dtype=torch.int64, device="cuda")
     barrier()
     t_start = torch.cuda.Event(enable_timing=True)
@@ -231,7 +241,7 @@ def run_ours(args):
     barrier()
     t0 = time.perf_counter()
     for k in range(args.steps):
-        r.render_host(my_poses[args.warmup + k])
+        r.render_host(my_poses[args.warmup + k], fused=not args.staged)
     barrier()
     e2e_s = time.perf_counter() - t0
     clock_summary = clocks.summary() if clocks else None
@@ -297,11 +307,11 @@ def run_ours(args):
         # per-launch algorithmic work of this rank's kernels, per step
         Hh = hits / args.steps
         Ns = Hh * S
-        byts = dict(march=28 * R + 32 * Hh + G ** 3 / 8 + 64, sampler=16 * R + 24 * Hh + 24 * Ns,
-                    composite=20 * Ns + 8 * R + 12 * R)
+        byts = {"march": 28 * R + 32 * Hh + G ** 3 / 8 + 64, "sampler": 16 * R + 24 * Hh + 24 * Ns,
+                "composite": 20 * Ns + 8 * R + 12 * R}
         stages = {}
         for nme, ms in zip(stage_names, stage_ms):
-            if nme == "network":
+            if "network" in nme:
                 tf = FLOP_PER_SAMPLE * Ns / (ms * 1e-3) / 1e12
                 stages[nme] = dict(ms=ms, bound="tensor", achieved=tf, peak=pk["tf"], unit="TFLOP/s", frac=tf / pk["tf"],
                                    samples_per_s=Ns / (ms * 1e-3))
@@ -317,7 +327,9 @@ def run_ours(args):
         line = dict(metric="rays/s", value=value, unit="rays/s", n_gpus=world, steps=args.steps, warmup=args.warmup,
                     ms_per_step=ms_total / args.steps, higher_is_better=True, scaling="weak", vs_baseline=None,
                     dtype="f16 tensor-core MLP (fp32 accumulate), f32 march/sampler/compositing", data="synthetic",
-                    config=WORKLOAD, samples_per_s=samples_all / (ms_total * 1e-3),
+                    config=dict(WORKLOAD, path="staged: march, sampler, network, compositing kernels" if args.staged
+                                else "march kernel + one fused sampler/encoding/MLP/compositing kernel"),
+                    samples_per_s=samples_all / (ms_total * 1e-3),
                     rays_per_step_per_gpu=R, samples_per_step_per_gpu=Ns,
                     e2e=dict(value=rays_all / (e2e_ms * 1e-3), unit="rays/s", h2d_bytes_per_step=64,
                              d2h_bytes_per_step=R * 12, ms_per_step=e2e_ms / args.steps),
@@ -351,6 +363,10 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     ap.add_argument("--no-train", action="store_true", help="skip the training-step leg (profiling runs)")
+    ap.add_argument("--spinup", type=float, default=0.5, help="seconds of untimed load before the timed steps")
+    ap.add_argument("--staged", action="store_true",
+                    help="render through the separate sampler / network / compositing entry points instead of the "
+                         "fused kernel")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":

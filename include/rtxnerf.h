@@ -235,6 +235,17 @@ int rtxnerf_network_forward_rays(const rtxnerf_hashgrid* enc, const rtxnerf_mlp*
                                  uint16_t* d_out16, float* d_radiance4, uint16_t* d_encoded_out,
                                  void* stream);
 
+/* Render path in ONE kernel: REGULAR sampling of the CSR segments (launchSampler,
+ * sampler/sampler.cu:14-131), encoding + MLP forward (main.cu:715-728) and front-to-back
+ * compositing (launch_volrender_cuda, vol_render/vol_render.cu:19-73) without the samples /
+ * t_vals / radiance buffers ever reaching HBM.  Same arithmetic per sample as the three staged
+ * entry points; the per-ray accumulation runs in the reference's sequential order.
+ * sample_type must be 0 (REGULAR).  pixels: [n_rays][3] fp32. */
+int rtxnerf_render_rays_fused(const rtxnerf_hashgrid* enc, const rtxnerf_mlp* mlp,
+                              const float* d_start_points, const float* d_end_points,
+                              const int* d_num_hits, const int* d_indices, int n_rays,
+                              int samples_per_segment, int sample_type, float* d_pixels, void* stream);
+
 /* ------------------------------------------------------------------------------------
  * Training step — replaces network->backward (main.cu:781), loss->evaluate + reduce_sum
  * (main.cu:755-760) and optimizer->step (main.cu:787) of tiny-cuda-nn (absent from the

@@ -79,6 +79,8 @@ SIGNATURES = {
                                         c_void_p, c_void_p, c_int, c_void_p]),
     "rtxnerf_network_forward_rays": (c_int, [C.POINTER(HashGrid), C.POINTER(Mlp), c_void_p, c_int, c_void_p,
                                              c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "rtxnerf_render_rays_fused": (c_int, [C.POINTER(HashGrid), C.POINTER(Mlp), c_void_p, c_void_p, c_void_p, c_void_p,
+                                          c_int, c_int, c_int, c_void_p, c_void_p]),
     "rtxnerf_network_backward_rays": (c_int, [C.POINTER(HashGrid), C.POINTER(Mlp), c_void_p, c_int, c_void_p,
                                               c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_ll, c_void_p,
                                               c_void_p, c_void_p, c_void_p]),

@@ -342,6 +342,16 @@ class Network:
         _lib.count_launches(1 if n_rays > 0 else 0)
         return output if output is not None else radiance
 
+    def render_rays_fused(self, stream, start_points, end_points, num_hits, indices, n_rays, samples_per_segment,
+                          pixels, sample_type=0):
+        """launchSampler + forward + launch_volrender_cuda of the render path in one kernel
+        (view_fused.cu): CSR segments in, pixels out, no sample / radiance buffers."""
+        _lib.check(_lib.load().rtxnerf_render_rays_fused(C.byref(self._hg), C.byref(self._mlp), _p(start_points),
+                                                         _p(end_points), _p(num_hits), _p(indices), int(n_rays),
+                                                         int(samples_per_segment), int(sample_type), _p(pixels),
+                                                         _stream_ptr(stream)), "render_rays_fused")
+        return pixels
+
     def backward_rays(self, stream, samples, encoded, dl_dradiance, num_hits, indices, n_rays,
                       samples_per_segment, d_count, n_max, dencoded, grad_table, grad_weights):
         """network->backward (main.cu:781) with the intended wiring (Q5): dl_dradiance is the fp16

@@ -86,6 +86,24 @@ __device__ __forceinline__ void output_row_load(uint32_t taddr, uint32_t (&r)[16
     tc::tmem_ld_x16(taddr, r);
     tc::tmem_ld_wait();
 }
+// (r,g,b,sigma) of a row exactly as output_row_store writes them to radiance4: activation,
+// one rounding to fp16, back to fp32
+__device__ __forceinline__ float4 output_row_rgba(const uint32_t (&r)[16], int out_activation)
+{
+    float v[4];
+#pragma unroll
+    for (int j = 0; j < 2; j++) {
+        float a = __uint_as_float(r[2 * j]), b = __uint_as_float(r[2 * j + 1]);
+        if (out_activation == 1) {
+            a = __fdividef(1.0f, 1.0f + __expf(-a));
+            b = __fdividef(1.0f, 1.0f + __expf(-b));
+        }
+        const float2 back = __half22float2(__floats2half2_rn(a, b));
+        v[2 * j] = back.x;
+        v[2 * j + 1] = back.y;
+    }
+    return make_float4(v[0], v[1], v[2], v[3]);
+}
 __device__ __forceinline__ void output_row_store(const uint32_t (&r)[16], int out_activation, long long s,
                                                  uint16_t* __restrict__ out16, float* __restrict__ radiance4)
 {

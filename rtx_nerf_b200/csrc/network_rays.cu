@@ -45,12 +45,16 @@ __device__ __forceinline__ void encode_pair(const Levels& lv, const uint32_t* __
     const char* tb = reinterpret_cast<const char*>(table32);
     __half2 h0 = __floats2half2_rn(0.f, 0.f), h1 = h0;
     const bool two = l + 1 < lv.n_levels;
-    if (two && lv.mode[l] == 1u && lv.mode[l + 1] == 1u) {
+    const uint32_t m0 = lv.mode[l], m1 = two ? lv.mode[l + 1] : 2u;
+    if (m0 == 1u && m1 == 1u) {
         h0 = encode_level_fast<1>(lv, l, tb, x01, y01, z01);
         h1 = encode_level_fast<1>(lv, l + 1, tb, x01, y01, z01);
-    } else if (two && lv.mode[l] == 0u && lv.mode[l + 1] == 0u) {
+    } else if (m0 == 0u && m1 == 0u) {
         h0 = encode_level_fast<0>(lv, l, tb, x01, y01, z01);
         h1 = encode_level_fast<0>(lv, l + 1, tb, x01, y01, z01);
+    } else if (m0 == 0u && m1 == 1u) {      // the pair that straddles the dense -> hashed boundary
+        h0 = encode_level_fast<0>(lv, l, tb, x01, y01, z01);
+        h1 = encode_level_fast<1>(lv, l + 1, tb, x01, y01, z01);
     } else {
         if (l < lv.n_levels) h0 = encode_level_any(lv, tb, l, x01, y01, z01);
         if (two) h1 = encode_level_any(lv, tb, l + 1, x01, y01, z01);
@@ -198,6 +202,137 @@ network_forward_rays_kernel(Levels lv, const uint32_t* __restrict__ table32, con
     if (warp == 0) tc::tmem_dealloc<NET_TMEM_COLS>(tmem_base);
 }
 
+// ---------------------------------------------------------------------------------------
+// Version 2: no mutex.  Every warp-group owns a 16 KB activation tile and 64 TMEM columns
+// (4 x 64 = 256 columns per CTA, two CTAs fill the SM's 512), so the four groups of a CTA
+// never wait on each other: the tensor pipe interleaves their layers.  Features go from the
+// blend straight into the group's A tile (one 16-byte store per four levels) instead of
+// being held in 16 registers until the tile is free; those registers go to gathers in flight.
+// ---------------------------------------------------------------------------------------
+template <int WGS>
+struct NetR2Smem {
+    static constexpr int W0 = 0;
+    static constexpr int W1 = W0 + NET_W * NET_IN * 2;
+    static constexpr int W2 = W1 + NET_W * NET_W * 2;
+    static constexpr int ACT = W2 + NET_OUT * NET_W * 2;                 // WGS tiles of 128 x 64 fp16
+    static constexpr int BAR = ACT + WGS * NET_TILE * NET_W * 2;    // WGS mbarriers, tmem slot
+    static constexpr int BYTES = BAR + 8 * WGS + 16;
+};
+
+template <int WGS, int MINB>
+__global__ void __launch_bounds__(WGS * NET_TILE, MINB)
+network_forward_rays2_kernel(Levels lv, const uint32_t* __restrict__ table32, const uint16_t* __restrict__ weights,
+                             const float* __restrict__ samples, int stride, int out_activation,
+                             const int* __restrict__ num_hits, const int* __restrict__ indices, int n_rays, int S,
+                             uint16_t* __restrict__ out16, float* __restrict__ radiance4,
+                             uint16_t* __restrict__ encoded_out)
+{
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + NetR2Smem<WGS>::BAR);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + NetR2Smem<WGS>::BAR + 8 * WGS);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int wg = tid >> 7, wt = tid & (NET_TILE - 1), wk = warp & 3;
+
+    load_weight_tile(smem + NetR2Smem<WGS>::W0, weights, NET_W, NET_IN, tid, (WGS * NET_TILE));
+    load_weight_tile(smem + NetR2Smem<WGS>::W1, weights + NET_W * NET_IN, NET_W, NET_W, tid, (WGS * NET_TILE));
+    load_weight_tile(smem + NetR2Smem<WGS>::W2, weights + NET_W * NET_IN + NET_W * NET_W, NET_OUT, NET_W, tid, (WGS * NET_TILE));
+    if (tid == 0) {
+        for (int i = 0; i < WGS; i++) tc::mbar_init(bars + i, 1);
+        tc::fence_mbar_init();
+    }
+    if (warp == 0) tc::tmem_alloc<(WGS == 3 ? 4 : WGS) * NET_TMEM_COLS>(tmem_slot);
+    tc::fence_proxy_async_smem();
+    tc::fence_before_thread_sync();
+    __syncthreads();
+    tc::fence_after_thread_sync();
+    const uint32_t tmem_wg = *tmem_slot + (uint32_t)(wg * NET_TMEM_COLS);
+    const uint32_t t_row = tmem_wg + ((uint32_t)(wk * 32) << 16);   // TMEM lanes of this warp's quarter
+    uint8_t* act = smem + NetR2Smem<WGS>::ACT + wg * (NET_TILE * NET_W * 2);
+    const uint32_t s_w0 = tc::smem_u32(smem + NetR2Smem<WGS>::W0), s_w1 = tc::smem_u32(smem + NetR2Smem<WGS>::W1),
+                   s_w2 = tc::smem_u32(smem + NetR2Smem<WGS>::W2), s_act = tc::smem_u32(act);
+    uint64_t* bar = bars + wg;
+    uint32_t phase = 0;
+
+    const int n_groups = (n_rays + 31) >> 5;
+    for (int g = blockIdx.x * WGS + wg; g < n_groups; g += gridDim.x * WGS) {
+        const int ray = g * 32 + lane;
+        int ns = 0;
+        long long base = 0;
+        if (ray < n_rays) {
+            ns = num_hits[ray] * S;
+            base = (long long)indices[ray] * S;
+        }
+        int maxn = ns;
+#pragma unroll
+        for (int o = 16; o; o >>= 1) maxn = max(maxn, __shfl_xor_sync(0xffffffffu, maxn, o));
+
+        for (int q0 = 0; q0 < maxn; q0 += 4) {
+            const int q = q0 + wk;
+            const bool valid = q < ns;
+            const long long s = base + q;
+            // ---- gather: four levels (one 16-byte chunk of this row of the A tile) at a time
+            if (valid) {
+                const float* p = samples + s * stride;
+                const float x01 = rn_fma(ld_stream_f1(p), 0.5f, 0.5f);
+                const float y01 = rn_fma(ld_stream_f1(p + 1), 0.5f, 0.5f);
+                const float z01 = rn_fma(ld_stream_f1(p + 2), 0.5f, 0.5f);
+#pragma unroll 1
+                for (int c = 0; c < NET_IN / 8; c++) {
+                    uint4 f;
+                    encode_pair(lv, table32, 4 * c, x01, y01, z01, f.x, f.y);
+                    encode_pair(lv, table32, 4 * c + 2, x01, y01, z01, f.z, f.w);
+                    *reinterpret_cast<uint4*>(act + tile_chunk_off(wt, c, NET_IN)) = f;
+                    if (encoded_out) reinterpret_cast<uint4*>(encoded_out + s * NET_IN)[c] = f;
+                }
+            } else {
+#pragma unroll
+                for (int c = 0; c < NET_IN / 8; c++)
+                    *reinterpret_cast<uint4*>(act + tile_chunk_off(wt, c, NET_IN)) = make_uint4(0u, 0u, 0u, 0u);
+            }
+            tc::fence_proxy_async_smem();
+            tc::fence_before_thread_sync();
+            wg_barrier(wg);
+            if (wt == 0) {
+                tc::fence_after_thread_sync();
+                issue_layer<NET_W, NET_IN>(tmem_wg, s_act, s_w0, bar);
+            }
+            tc::mbar_wait(bar, phase);
+            phase ^= 1;
+            tc::fence_after_thread_sync();
+            relu_row_to_smem(t_row, act, wt);
+            tc::fence_proxy_async_smem();
+            tc::fence_before_thread_sync();
+            wg_barrier(wg);
+            if (wt == 0) {
+                tc::fence_after_thread_sync();
+                issue_layer<NET_W, NET_W>(tmem_wg, s_act, s_w1, bar);
+            }
+            tc::mbar_wait(bar, phase);
+            phase ^= 1;
+            tc::fence_after_thread_sync();
+            relu_row_to_smem(t_row, act, wt);
+            tc::fence_proxy_async_smem();
+            tc::fence_before_thread_sync();
+            wg_barrier(wg);
+            if (wt == 0) {
+                tc::fence_after_thread_sync();
+                issue_layer<NET_OUT, NET_W>(tmem_wg, s_act, s_w2, bar);
+            }
+            tc::mbar_wait(bar, phase);
+            phase ^= 1;
+            tc::fence_after_thread_sync();
+            uint32_t r[16];
+            output_row_load(t_row, r);
+            tc::fence_before_thread_sync();
+            if (valid) output_row_store(r, out_activation, s, out16, radiance4);
+        }
+    }
+    tc::fence_before_thread_sync();
+    __syncthreads();
+    tc::fence_after_thread_sync();
+    if (warp == 0) tc::tmem_dealloc<(WGS == 3 ? 4 : WGS) * NET_TMEM_COLS>(*tmem_slot);
+}
+
 extern "C" int rtxnerf_network_forward_rays(const rtxnerf_hashgrid* enc, const rtxnerf_mlp* mlp,
                                             const float* d_samples, int sample_stride, const int* d_num_hits,
                                             const int* d_indices, int n_rays, int samples_per_segment,
@@ -224,7 +359,37 @@ extern "C" int rtxnerf_network_forward_rays(const rtxnerf_hashgrid* enc, const r
         RTX_CUDA_TRY(cudaFuncSetAttribute(network_forward_rays_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                           NetRSmem::BYTES));
     }
+    static int version = 0;
+    if (!version) {
+        const char* e = getenv("RTXNERF_NETR_VERSION");   // development knob: 1 = mutex kernel, 2x = v2 shapes
+        version = e ? atoi(e) : 2;
+        if (version < 1) version = 2;
+    }
     const long long groups = ((long long)n_rays + 31) / 32;
+    if (version >= 2) {
+#define NETR2_LAUNCH(WGS, MINB)                                                                                     \
+    do {                                                                                                            \
+        static bool attr = false;                                                                                   \
+        if (!attr) {                                                                                                \
+            RTX_CUDA_TRY(cudaFuncSetAttribute(network_forward_rays2_kernel<WGS, MINB>,                              \
+                                              cudaFuncAttributeMaxDynamicSharedMemorySize, NetR2Smem<WGS>::BYTES)); \
+            attr = true;                                                                                            \
+        }                                                                                                           \
+        long long nb = (groups + WGS - 1) / WGS;                                                                    \
+        if (nb > (long long)RTX_NUM_SMS * MINB) nb = (long long)RTX_NUM_SMS * MINB;                                 \
+        network_forward_rays2_kernel<WGS, MINB><<<(unsigned)nb, WGS * NET_TILE, NetR2Smem<WGS>::BYTES,              \
+                                                  (cudaStream_t)stream>>>(                                          \
+            lv, reinterpret_cast<const uint32_t*>(enc->table), mlp->weights, d_samples, sample_stride,              \
+            mlp->out_activation, d_num_hits, d_indices, n_rays, samples_per_segment, d_out16, d_radiance4,          \
+            d_encoded_out);                                                                                         \
+    } while (0)
+        if (version == 23) NETR2_LAUNCH(2, 3);        // 3 CTAs x 256 threads: 24 warps, 80 registers
+        else if (version == 32) NETR2_LAUNCH(3, 2);   // 2 CTAs x 384 threads: 24 warps, 80 registers
+        else if (version == 24) NETR2_LAUNCH(2, 4);   // 4 CTAs x 256 threads: 32 warps, 64 registers
+        else NETR2_LAUNCH(4, 2);                      // 2 CTAs x 512 threads: 32 warps, 64 registers
+#undef NETR2_LAUNCH
+        return rtx_launch_status();
+    }
     long long blocks = (groups + NETR_WGS - 1) / NETR_WGS;
     const long long resident = (long long)RTX_NUM_SMS * min_ctas;
     if (blocks > resident) blocks = resident;

@@ -37,7 +37,8 @@ class ViewRenderer:
         self.pose_dev = torch.empty(16, dtype=torch.float32, device=dev)
         self.pose_pinned = torch.empty(16, dtype=torch.float32).pin_memory()
         self.pixels_pinned = torch.empty((self.R, 3), dtype=torch.float32).pin_memory()
-        self.launches_per_view = (1 if max_hits <= 32 else 3) + 1 + radiance.launches + 1
+        march = 1 if max_hits <= 32 else 3
+        self.launches_per_view = march + 1 if self.can_fuse else march + 1 + radiance.launches + 1
 
     # --- stages (all asynchronous on the current stream) -------------------------------
     def stage_march(self):
@@ -57,21 +58,37 @@ class ViewRenderer:
         api.launch_volrender_cuda(self.samples, self.radiance, h.num_hits, h.indices, self.t_vals, self.R, self.S,
                                   self.pixels)
 
-    def render_device(self, pose_dev=None):
+    def stage_fused(self):
+        """Sampler + network + compositing in one kernel (render path with a NetworkRadiance)."""
+        h = self.hits
+        self.radiance_stage.net.render_rays_fused(None, h.start_points, h.end_points, h.num_hits, h.indices,
+                                                  self.R, self.S, self.pixels)
+
+    @property
+    def can_fuse(self):
+        return isinstance(self.radiance_stage, NetworkRadiance) and self.radiance_stage.fusable
+
+    def stages(self, fused=None):
+        """[(name, callable)] of one view: the fused render path when available (or asked for)."""
+        fused = self.can_fuse if fused is None else fused
+        if fused:
+            return [("march", self.stage_march), ("sample+network+composite", self.stage_fused)]
+        return [("march", self.stage_march), ("sampler", self.stage_sampler), ("network", self.stage_radiance),
+                ("composite", self.stage_composite)]
+
+    def render_device(self, pose_dev=None, fused=None):
         """Pose already on the device; returns the device pixel buffer."""
         if pose_dev is not None:
             self.pose_dev.copy_(pose_dev, non_blocking=True)
-        self.stage_march()
-        self.stage_sampler()
-        self.stage_radiance()
-        self.stage_composite()
+        for _, fn in self.stages(fused):
+            fn()
         return self.pixels
 
-    def render_host(self, pose_host):
+    def render_host(self, pose_host, fused=None):
         """The user-facing call: host pose in, host pixels out (H2D + D2H inside)."""
         self.pose_pinned.copy_(torch.as_tensor(np.asarray(pose_host, np.float32).reshape(16)))
         self.pose_dev.copy_(self.pose_pinned, non_blocking=True)
-        self.render_device()
+        self.render_device(fused=fused)
         self.pixels_pinned.copy_(self.pixels, non_blocking=True)
         torch.cuda.current_stream().synchronize()
         return self.pixels_pinned
@@ -100,6 +117,7 @@ class NetworkRadiance:
 
     def __init__(self, network, impl=api.IMPL_TCGEN05, schedule="rays"):
         self.net, self.impl, self.schedule = network, impl, schedule
+        self.fusable = schedule == "rays" and impl == api.IMPL_TCGEN05
 
     def __call__(self, r):
         if self.schedule == "rays" and self.impl == api.IMPL_TCGEN05:

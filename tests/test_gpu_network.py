@@ -111,7 +111,9 @@ def test_network_render_config2_small(cuda_api, orc):
     focal = synth.focal_length()
     grid = api.OccupancyGrid.from_occupancy(occ, G)
     r = pipeline.ViewRenderer(grid, W, H, focal, 1.0, S, HM, pipeline.NetworkRadiance(net))
-    px = r.render_host(pose).numpy().copy()
+    assert r.can_fuse
+    px = r.render_host(pose, fused=False).numpy().copy()          # staged: sampler, network, compositing
+    px_fused = r.render_host(pose, fused=True).numpy().copy()     # the same in one kernel (view_fused.cu)
     ora = orc.ray_march_dda(pose, focal, 1.0, W, H, occ, G, max_hits=HM, csr=True)
     so, to = orc.sampler(ora.start_points, ora.end_points, ora.view_dirs, ora.num_hits, ora.indices, S)
     _, rado = orc.mlp_forward(w, 32, 64, 2, 1, orc.hashgrid_encode(lv, table, so))
@@ -119,6 +121,38 @@ def test_network_render_config2_small(cuda_api, orc):
     assert r.total_hits() == ora.total_hits
     assert np.array_equal(r.hits.num_hits.cpu().numpy(), ora.num_hits)
     np.testing.assert_allclose(px, pxo, rtol=0, atol=1e-3)
+    np.testing.assert_allclose(px_fused, pxo, rtol=0, atol=1e-3)
+    # same per-sample arithmetic; only the order of the per-ray sums differs (sequential vs warp scan)
+    np.testing.assert_allclose(px_fused, px, rtol=0, atol=2e-6)
+
+
+@pytest.mark.parametrize("G,kind,W,H,S,HM", [
+    (32, 0.2, 40, 24, 3, 12),       # S not a power of two: repeated-addition t (sampler.cu:65)
+    (16, 0.3, 33, 17, 32, 8),       # the reference's literal S = 32 (sampler.h:4)
+    (64, 0.02, 50, 30, 4, 16),      # sparse: most rays miss, ragged groups
+    (16, 0.0, 20, 20, 4, 4),        # empty grid: every pixel black
+])
+def test_fused_render_matches_staged_and_oracle(cuda_api, orc, G, kind, W, H, S, HM):
+    from rtx_nerf_b200 import pipeline
+    api = cuda_api
+    occ = synth.occupancy_bernoulli(G, kind, seed=5) if kind > 0 else np.zeros(G ** 3, np.uint8)
+    net, lv, table, w = _net(api, table_scale=1.0, seed=7)
+    pose = synth.poses(1, seed=9)[0]
+    focal = synth.focal_length()
+    grid = api.OccupancyGrid.from_occupancy(occ, G)
+    r = pipeline.ViewRenderer(grid, W, H, focal, W / H, S, HM, pipeline.NetworkRadiance(net))
+    px = r.render_host(pose, fused=False).numpy().copy()
+    r.pixels.fill_(-3.0)
+    px_fused = r.render_host(pose, fused=True).numpy().copy()
+    np.testing.assert_allclose(px_fused, px, rtol=0, atol=2e-6)
+    ora = orc.ray_march_dda(pose, focal, W / H, W, H, occ, G, max_hits=HM, csr=True)
+    if ora.total_hits:
+        so, to = orc.sampler(ora.start_points, ora.end_points, ora.view_dirs, ora.num_hits, ora.indices, S)
+        _, rado = orc.mlp_forward(w, 32, 64, 2, 1, orc.hashgrid_encode(lv, table, so))
+        pxo = orc.volrender(rado, ora.num_hits, ora.indices, to, S)
+    else:
+        pxo = np.zeros((W * H, 3), np.float32)
+    np.testing.assert_allclose(px_fused, pxo, rtol=0, atol=1e-3)
 
 
 @pytest.mark.parametrize("n_rays,S", [(1, 4), (33, 4), (700, 3), (257, 32)])
