@@ -235,6 +235,36 @@ int rtxnerf_network_forward_rays(const rtxnerf_hashgrid* enc, const rtxnerf_mlp*
                                  uint16_t* d_out16, float* d_radiance4, uint16_t* d_encoded_out,
                                  void* stream);
 
+/* ------------------------------------------------------------------------------------
+ * The reference's literal network (main.cu:47-68): Composite[Frequency(xyz, 10 frequencies) +
+ * Frequency(theta/phi, tiny-cuda-nn's default 12)] padded with ones to 112 inputs ->
+ * FullyFusedMLP 8 x 128 ReLU -> 16 outputs (sigmoid), bias-free fp16.  Feature order:
+ * out[d*2F + 2k] = sin(pi 2^k x_d), out[d*2F + 2k + 1] = cos(pi 2^k x_d).  Weights: fp16
+ * row-major [128][112], 7 x [128][128], [16][128] concatenated (rtxnerf_freqnet_param_count()
+ * values); weights_packed is the same data in the tensor-core operand layout, produced once by
+ * rtxnerf_freqnet_pack (repeat after every optimizer step).  PARITY UNPINNED (tiny-cuda-nn
+ * absent), see DESIGN.md.
+ * ---------------------------------------------------------------------------------- */
+typedef struct rtxnerf_freqnet {
+    const uint16_t* weights_packed;  /* device, 16-byte aligned */
+    int n_freq_xyz;                  /* 10 */
+    int n_freq_dir;                  /* 12 */
+    int width;                       /* 128 */
+    int n_hidden;                    /* 8 */
+    int out_activation;              /* 0 none, 1 sigmoid */
+} rtxnerf_freqnet;
+
+size_t rtxnerf_freqnet_param_count(void);
+int rtxnerf_freqnet_pack(const uint16_t* d_weights, uint16_t* d_packed, void* stream);
+/* [n][sample_stride >= 5] fp32 rows (x,y,z,theta,phi) -> fp16 [n][112] */
+int rtxnerf_freqnet_encode(const float* d_samples, int sample_stride, long long n, uint16_t* d_encoded,
+                           void* stream);
+/* Rows as rtxnerf_network_forward: n = min(n_max, d_count ? *d_count * count_scale : n_max);
+ * d_out16 fp16 [n][16] and/or d_radiance4 fp32 [n][4]. */
+int rtxnerf_freqnet_forward(const rtxnerf_freqnet* net, const float* d_samples, int sample_stride,
+                            const long long* d_count, long long count_scale, long long n_max,
+                            uint16_t* d_out16, float* d_radiance4, void* stream);
+
 /* Render path in ONE kernel: REGULAR sampling of the CSR segments (launchSampler,
  * sampler/sampler.cu:14-131), encoding + MLP forward (main.cu:715-728) and front-to-back
  * compositing (launch_volrender_cuda, vol_render/vol_render.cu:19-73) without the samples /

@@ -271,6 +271,17 @@ def hashgrid_encode(levels, table_h, samples, nthreads=None):
     return out.view(np.float16)
 
 
+def frequency_encode(samples, n_freq_xyz=10, n_freq_dir=12, padded_width=112, nthreads=None):
+    """Composite Frequency encoding of [n][5] (x,y,z,theta,phi) rows -> fp16 [n][padded_width]."""
+    samples = np.ascontiguousarray(samples, np.float32)
+    n = samples.shape[0]
+    out = np.empty((n, padded_width), np.uint16)
+    lib().orc_frequency_encode(_ptr(samples, _f32p), C.c_int(samples.shape[1]), C.c_longlong(n), C.c_int(n_freq_xyz),
+                               C.c_int(n_freq_dir), C.c_int(padded_width), _ptr(out, _u16p),
+                               C.c_int(nthreads or default_threads()))
+    return out.view(np.float16)
+
+
 def mlp_forward(weights_h, in_dim, width, n_hidden, out_activation, x_h, nthreads=None):
     w = np.ascontiguousarray(weights_h, np.float16).view(np.uint16)
     x = np.ascontiguousarray(x_h, np.float16).view(np.uint16)

@@ -591,6 +591,37 @@ void orc_hashgrid_encode(int L, int F, const float* scales, const uint32_t* ress
 /* FullyFusedMLP forward — restated from the published description (bias-free, fp16
  * weights and activations, fp32 accumulate, output padded to 16).  PARITY UNPINNED.
  * Call site: main.cu:721; output slice + half->float: main.cu:723-728. */
+/* ---------------------------------------------------------------------------------------
+ * Frequency (positional) encoding of the reference's literal network config, main.cu:47-61:
+ * Composite[Frequency(3 dims, n_frequencies 10) + Frequency(2 dims; the "n_bins" key is not a
+ * Frequency parameter, so tiny-cuda-nn's default of 12 frequencies applies)], output padded
+ * to a multiple of 16 with ones (108 -> 112).  tiny-cuda-nn is absent from the archive
+ * (PARITY UNPINNED); the published definition is restated: for input dim d and k < F
+ *   out[d*2F + 2k] = sin(pi * 2^k * x_d),  out[d*2F + 2k + 1] = cos(pi * 2^k * x_d)
+ * evaluated in double here and rounded once to fp16.  The kernel reduces the argument
+ * exactly (mod 2) and uses the hardware sine: equal up to one fp16 ulp.
+ * ------------------------------------------------------------------------------------- */
+void orc_frequency_encode(const float* samples, int stride, long long n, int n_freq_xyz, int n_freq_dir,
+                          int padded_width, uint16_t* out, int nthreads)
+{
+    const double PI = 3.14159265358979323846;
+#pragma omp parallel for schedule(static) num_threads(nthreads > 0 ? nthreads : 1)
+    for (long long s = 0; s < n; s++) {
+        const float* p = samples + (size_t)s * stride;
+        uint16_t* o = out + (size_t)s * padded_width;
+        int j = 0;
+        for (int d = 0; d < 5; d++) {
+            const int F = d < 3 ? n_freq_xyz : n_freq_dir;
+            for (int k = 0; k < F; k++) {
+                const double y = ldexp((double)p[d], k);
+                o[j++] = orc_f2h((float)sin(PI * y));
+                o[j++] = orc_f2h((float)cos(PI * y));
+            }
+        }
+        for (; j < padded_width; j++) o[j] = orc_f2h(1.0f);
+    }
+}
+
 void orc_mlp_forward(const uint16_t* weights, int in_dim, int width, int n_hidden,
                      int out_activation, const uint16_t* in, long long n, uint16_t* out16,
                      float* radiance4, int nthreads)

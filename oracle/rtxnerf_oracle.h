@@ -129,6 +129,8 @@ void orc_hashgrid_geometry(const orc_hashgrid_cfg* cfg, float* scales, uint32_t*
 
 /* Multiresolution hash encoding of xyz in [-1,1]^3 (samples rows, stride floats):
  * explicit per-level geometry; table fp16 [entries][F], out fp16 [N][L*F]. */
+void orc_frequency_encode(const float* samples, int stride, long long n, int n_freq_xyz, int n_freq_dir,
+                          int padded_width, uint16_t* out, int nthreads);
 void orc_hashgrid_encode(int L, int F, const float* scales, const uint32_t* ress,
                          const uint32_t* sizes, const long long* offsets, const uint16_t* table,
                          const float* samples, int sample_stride, long long n, uint16_t* encoded,

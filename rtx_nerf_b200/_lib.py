@@ -45,6 +45,12 @@ class HashGrid(C.Structure):
                 ("res", C.c_uint32 * 16), ("size", C.c_uint32 * 16), ("offset", C.c_uint32 * 16)]
 
 
+class FreqNet(C.Structure):
+    """rtxnerf_freqnet (include/rtxnerf.h)."""
+    _fields_ = [("weights_packed", c_void_p), ("n_freq_xyz", c_int), ("n_freq_dir", c_int), ("width", c_int),
+                ("n_hidden", c_int), ("out_activation", c_int)]
+
+
 class Mlp(C.Structure):
     """rtxnerf_mlp (include/rtxnerf.h)."""
     _fields_ = [("weights", c_void_p), ("in_dim", c_int), ("width", c_int), ("n_hidden", c_int),
@@ -81,6 +87,11 @@ SIGNATURES = {
                                              c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
     "rtxnerf_render_rays_fused": (c_int, [C.POINTER(HashGrid), C.POINTER(Mlp), c_void_p, c_void_p, c_void_p, c_void_p,
                                           c_int, c_int, c_int, c_void_p, c_void_p]),
+    "rtxnerf_freqnet_param_count": (c_size_t, []),
+    "rtxnerf_freqnet_pack": (c_int, [c_void_p, c_void_p, c_void_p]),
+    "rtxnerf_freqnet_encode": (c_int, [c_void_p, c_int, c_ll, c_void_p, c_void_p]),
+    "rtxnerf_freqnet_forward": (c_int, [C.POINTER(FreqNet), c_void_p, c_int, c_void_p, c_ll, c_ll, c_void_p, c_void_p,
+                                        c_void_p]),
     "rtxnerf_network_backward_rays": (c_int, [C.POINTER(HashGrid), C.POINTER(Mlp), c_void_p, c_int, c_void_p,
                                               c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_ll, c_void_p,
                                               c_void_p, c_void_p, c_void_p]),

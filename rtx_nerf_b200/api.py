@@ -266,6 +266,59 @@ IMPL_TCGEN05 = 0
 IMPL_SIMT = 1
 
 
+class FrequencyNetwork:
+    """The network main.cu itself configures (main.cu:47-68): Composite Frequency encoding
+    (10 frequencies on xyz, tiny-cuda-nn's default 12 on theta/phi, padded with ones to 112) +
+    FullyFusedMLP 8 x 128 ReLU, sigmoid output, driven like network->forward(stream, input,
+    &output) (main.cu:721).  tcgen05 kernel with the activations resident in TMEM
+    (network_freq.cu)."""
+
+    n_input_dims = 5
+    n_output_dims = 4
+    IN, WIDTH, N_HIDDEN = 112, 128, 8
+
+    def __init__(self, weights_h, out_activation=1, device="cuda"):
+        w = np.ascontiguousarray(weights_h, np.float16).reshape(-1)
+        n = int(_lib.load().rtxnerf_freqnet_param_count())
+        if w.size != n:
+            raise ValueError("FrequencyNetwork needs %d fp16 weights, got %d" % (n, w.size))
+        self.weights = torch.as_tensor(w).to(device)
+        self.packed = torch.empty_like(self.weights)
+        self.out_activation = int(out_activation)
+        self.repack()
+
+    def repack(self, stream=None):
+        """Row-major weights -> tensor-core operand layout (after construction / every optimizer step)."""
+        _lib.check(_lib.load().rtxnerf_freqnet_pack(_p(self.weights), _p(self.packed), _stream_ptr(stream)),
+                   "freqnet_pack")
+        self._net = _lib.FreqNet(self.packed.data_ptr(), 10, 12, self.WIDTH, self.N_HIDDEN, self.out_activation)
+
+    def padded_output_width(self):
+        return 16            # main.cu:715
+
+    def n_params(self):
+        return self.weights.numel()
+
+    def encode(self, samples, n=None, encoded=None, stream=None):
+        n = samples.shape[0] if n is None else n
+        if encoded is None:
+            encoded = torch.empty((n, self.IN), dtype=torch.float16, device=samples.device)
+        _lib.check(_lib.load().rtxnerf_freqnet_encode(_p(samples), samples.shape[1], int(n), _p(encoded),
+                                                      _stream_ptr(stream)), "freqnet_encode")
+        return encoded
+
+    def forward(self, stream, input, output=None, radiance=None, n=None, d_count=None, count_scale=1):
+        """input: fp32 [N][>=5] sample rows (GPUMatrix<float>(5,N)); output: fp16 [N][16]
+        (GPUMatrix<half>(16,N)); radiance: fp32 [N][4] (rows 0..3 as float, main.cu:723-728)."""
+        n_max = input.shape[0] if n is None else n
+        if output is None and radiance is None:
+            output = torch.empty((n_max, 16), dtype=torch.float16, device=input.device)
+        _lib.check(_lib.load().rtxnerf_freqnet_forward(C.byref(self._net), _p(input), input.shape[1], _p(d_count),
+                                                       int(count_scale), int(n_max), _p(output), _p(radiance),
+                                                       _stream_ptr(stream)), "freqnet_forward")
+        return output if output is not None else radiance
+
+
 class Network:
     """Encoding + fully fused MLP: the object the reference gets from tcnn::create_from_config
     (main.cu:325) and drives with network->forward(stream, input, &output) (main.cu:721).

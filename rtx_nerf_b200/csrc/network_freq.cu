@@ -1,0 +1,333 @@
+// network_freq.cu — the reference's LITERAL network on tcgen05: Composite Frequency encoding +
+// FullyFusedMLP 8 x 128, ReLU, sigmoid output, no bias, fp16 (config at main.cu:47-68, created at
+// main.cu:325, forward at main.cu:715-728).  SURVEY §8 row f2.  tiny-cuda-nn is absent from the
+// archive (PARITY UNPINNED): the published definitions are restated, see oracle/rtxnerf_oracle.c
+// orc_frequency_encode / orc_mlp_forward.
+//
+// 262 144 FLOP per sample against 20 B in and 8..32 B out: this one IS tensor-bound, and the
+// kernel is built so that the tensor pipe never waits for shared memory:
+//   * activations never leave the tensor core's own memory.  A layer's accumulators
+//     (128 x 128 fp32, 128 TMEM columns) are read with tcgen05.ld, ReLU'd and rounded to fp16
+//     in registers, and written back with tcgen05.st as the A OPERAND of the next layer
+//     (64 TMEM columns, A-from-TMEM form of tcgen05.mma).  With A in shared memory an
+//     M128 N128 K16 MMA reads 8 KB per 64 cycles — the whole 128 B/clk of the SM's shared
+//     memory — and the epilogue's stores would stall it; with A in TMEM shared memory only
+//     feeds B (the weights).
+//   * two tiles of 128 samples are in flight per SM (2 x (128 + 64) of the 512 TMEM columns):
+//     while the tensor core multiplies tile 0 by W_l, four warps run tile 1's epilogue.
+//   * the weights (256 KB, more than shared memory) are pre-packed once into the UMMA
+//     core-matrix layout and streamed from L2 layer by layer through a 4-slot ring with
+//     cp.async.bulk + mbarrier transaction counts; one load serves both tiles.
+//   * roles: warps 0-3 / 4-7 = encode + epilogue of tile slot 0 / 1 (TMEM lane quarters),
+//     warp 8 = MMA issue (one thread), warp 9 = weight loader (one thread).
+#include "common.cuh"
+#include "mlp_tile.cuh"
+
+#define FN_XYZ_FREQS 10
+#define FN_DIR_FREQS 12
+#define FN_IN 112            // 3*10*2 + 2*12*2 = 108, padded with ones to a multiple of 16
+#define FN_W 128
+#define FN_HIDDEN 8
+#define FN_LAYERS 9          // 112->128, 7 x 128->128, 128->16
+#define FN_RING 4
+#define FN_SLOT_BYTES (FN_W * FN_W * 2)
+#define FN_THREADS 320
+#define FN_PACKED_BYTES (FN_W * FN_IN * 2 + (FN_HIDDEN - 1) * FN_W * FN_W * 2 + NET_OUT * FN_W * 2)
+
+__host__ __device__ constexpr int fn_layer_k(int l) { return l == 0 ? FN_IN : FN_W; }
+__host__ __device__ constexpr int fn_layer_n(int l) { return l == FN_LAYERS - 1 ? NET_OUT : FN_W; }
+__host__ __device__ constexpr uint32_t fn_layer_bytes(int l) { return (uint32_t)(fn_layer_n(l) * fn_layer_k(l) * 2); }
+__host__ __device__ constexpr uint32_t fn_layer_offset(int l)
+{
+    return l == 0 ? 0u : (uint32_t)(FN_W * FN_IN * 2 + (l - 1) * FN_W * FN_W * 2);
+}
+
+// row-major [out][in] per layer -> the no-swizzle K-major core-matrix layout the MMA reads
+// (mlp_tile.cuh tile_chunk_off), layers concatenated: a ring slot is filled by ONE bulk copy.
+__global__ void freqnet_pack_kernel(const uint16_t* __restrict__ w, uint8_t* __restrict__ packed)
+{
+    const int total_chunks = FN_PACKED_BYTES / 16;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total_chunks; i += gridDim.x * blockDim.x) {
+        int l = 0;
+        while (l + 1 < FN_LAYERS && (uint32_t)i * 16u >= fn_layer_offset(l + 1)) l++;
+        const int K = fn_layer_k(l), chunks = K >> 3;
+        const int local = i - (int)(fn_layer_offset(l) / 16);
+        const int r = local / chunks, c = local - r * chunks;
+        const uint16_t* src = w + fn_layer_offset(l) / 2 + (size_t)r * K + c * 8;   // row-major offsets coincide
+        *reinterpret_cast<uint4*>(packed + fn_layer_offset(l) + tile_chunk_off(r, c, K)) =
+            *reinterpret_cast<const uint4*>(src);
+    }
+}
+
+// sin(pi*y), cos(pi*y) packed as fp16x2 {lo = sin, hi = cos}.  y - 2*rint(y/2) is exact in
+// fp32, so the hardware sine sees an argument in [-pi, pi] whatever the octave.
+__device__ __forceinline__ uint32_t sincospi_f16x2(float y)
+{
+    const float r = rn_fma(-2.0f, rintf(rn_mul(y, 0.5f)), y);
+    const float a = rn_mul(r, 3.14159265358979323846f);
+    const __half2 h = __floats2half2_rn(__sinf(a), __cosf(a));
+    return *reinterpret_cast<const uint32_t*>(&h);
+}
+
+// the 56 packed columns (112 features) of one sample row, main.cu:47-61 order:
+// x: f0..f9 (sin, cos), y, z, theta: f0..f11, phi, then ones
+template <class Sink>
+__device__ __forceinline__ void frequency_row(const float* __restrict__ p, bool valid, Sink sink)
+{
+    uint32_t col[16];
+    int nc = 0, base = 0;
+#pragma unroll
+    for (int d = 0; d < 5; d++) {
+        float y = valid ? __ldg(p + d) : 0.0f;
+        const int F = d < 3 ? FN_XYZ_FREQS : FN_DIR_FREQS;
+#pragma unroll
+        for (int k = 0; k < F; k++) {
+            col[nc++] = valid ? sincospi_f16x2(y) : 0u;
+            y = rn_add(y, y);
+            if (nc == 16) { sink(base, col); base += 16; nc = 0; }
+        }
+    }
+    // 54 columns so far: 6 in col[]; two columns of ones complete the last 8
+    col[6] = valid ? 0x3c003c00u : 0u;
+    col[7] = col[6];
+    uint32_t last[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) last[i] = col[i];
+    sink.tail(base, last);
+}
+
+struct TmemRowSink {
+    uint32_t taddr;   // this thread's lane row, first A column
+    __device__ __forceinline__ void operator()(int base, const uint32_t (&c)[16]) const { tc::tmem_st_x16(taddr + base, c); }
+    __device__ __forceinline__ void tail(int base, const uint32_t (&c)[8]) const { tc::tmem_st_x8(taddr + base, c); }
+};
+struct GlobalRowSink {
+    uint32_t* row;    // [56] packed columns of this sample, or nullptr
+    __device__ __forceinline__ void operator()(int base, const uint32_t (&c)[16]) const
+    {
+#pragma unroll
+        for (int i = 0; i < 4; i++)
+            reinterpret_cast<uint4*>(row + base)[i] = make_uint4(c[4 * i], c[4 * i + 1], c[4 * i + 2], c[4 * i + 3]);
+    }
+    __device__ __forceinline__ void tail(int base, const uint32_t (&c)[8]) const
+    {
+#pragma unroll
+        for (int i = 0; i < 2; i++)
+            reinterpret_cast<uint4*>(row + base)[i] = make_uint4(c[4 * i], c[4 * i + 1], c[4 * i + 2], c[4 * i + 3]);
+    }
+};
+
+// encoding alone (tests, and the pre-encoded path of callers that want the features)
+__global__ void freqnet_encode_kernel(const float* __restrict__ samples, int stride, long long n,
+                                      uint16_t* __restrict__ encoded)
+{
+    const long long s = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n) return;
+    GlobalRowSink sink{reinterpret_cast<uint32_t*>(encoded + s * FN_IN)};
+    frequency_row(samples + s * stride, true, sink);
+}
+
+struct FnSmem {
+    static constexpr int RING = 0;                                   // FN_RING slots of 32 KB
+    static constexpr int BAR = RING + FN_RING * FN_SLOT_BYTES;       // w_full[R], w_empty[R], a_ready[2], d_ready[2]
+    static constexpr int TMEM_SLOT = BAR + 8 * (2 * FN_RING + 4);
+    static constexpr int BYTES = TMEM_SLOT + 16;
+};
+
+// hidden-layer epilogue of one row: 128 fp32 accumulator columns -> ReLU -> fp16 -> 64 A columns
+__device__ __forceinline__ void fn_hidden_epilogue(uint32_t t_d, uint32_t t_a)
+{
+#pragma unroll
+    for (int h = 0; h < FN_W / 32; h++) {
+        uint32_t r0[16], r1[16];
+        tc::tmem_ld_x16(t_d + h * 32, r0);
+        tc::tmem_ld_x16(t_d + h * 32 + 16, r1);
+        tc::tmem_ld_wait();
+        uint32_t pk[16];
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            pk[j] = relu_pack_f16x2(__uint_as_float(r0[2 * j]), __uint_as_float(r0[2 * j + 1]));
+            pk[8 + j] = relu_pack_f16x2(__uint_as_float(r1[2 * j]), __uint_as_float(r1[2 * j + 1]));
+        }
+        tc::tmem_st_x16(t_a + h * 16, pk);
+    }
+}
+
+__global__ void __launch_bounds__(FN_THREADS, 1)
+freqnet_forward_kernel(const uint8_t* __restrict__ packed, const float* __restrict__ samples, int stride,
+                       int out_activation, const long long* __restrict__ d_count, long long count_scale,
+                       long long n_max, uint16_t* __restrict__ out16, float* __restrict__ radiance4)
+{
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint64_t* w_full = reinterpret_cast<uint64_t*>(smem + FnSmem::BAR);
+    uint64_t* w_empty = w_full + FN_RING;
+    uint64_t* a_ready = w_empty + FN_RING;
+    uint64_t* d_ready = a_ready + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + FnSmem::TMEM_SLOT);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+    if (tid == 0) {
+        for (int i = 0; i < FN_RING; i++) {
+            tc::mbar_init(w_full + i, 1);
+            tc::mbar_init(w_empty + i, 1);
+        }
+        for (int i = 0; i < 2; i++) {
+            tc::mbar_init(a_ready + i, NET_TILE);
+            tc::mbar_init(d_ready + i, 1);
+        }
+        tc::fence_mbar_init();
+    }
+    if (warp == 0) tc::tmem_alloc<512>(tmem_slot);
+    tc::fence_before_thread_sync();
+    __syncthreads();
+    tc::fence_after_thread_sync();
+    const uint32_t tmem_base = *tmem_slot;
+
+    long long n = n_max;
+    if (d_count) {
+        const long long c = *d_count * count_scale;
+        n = c < n_max ? c : n_max;
+    }
+    const long long n_tiles = (n + NET_TILE - 1) / NET_TILE;
+    const long long n_pairs = (n_tiles + 1) / 2;
+
+    if (warp < 8) {
+        // ------------------------------------------------ encode + epilogue group of tile slot s
+        const int s = warp >> 2, wk = warp & 3;
+        const uint32_t t_d = tmem_base + (uint32_t)(s * 256) + ((uint32_t)(wk * 32) << 16);
+        const uint32_t t_a = t_d + 128;
+        const int row_in_tile = wk * 32 + lane;
+        uint32_t d_par = 0;
+        for (long long pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
+            const long long row = (pair * 2 + s) * NET_TILE + row_in_tile;
+            const bool valid = row < n;
+            TmemRowSink sink{t_a};
+            frequency_row(samples + (valid ? row : 0) * stride, valid, sink);
+            tc::tmem_st_wait();
+            tc::fence_before_thread_sync();
+            tc::mbar_arrive(a_ready + s);
+            for (int l = 0; l < FN_HIDDEN; l++) {
+                tc::mbar_wait(d_ready + s, d_par);
+                d_par ^= 1;
+                tc::fence_after_thread_sync();
+                fn_hidden_epilogue(t_d, t_a);
+                tc::tmem_st_wait();
+                tc::fence_before_thread_sync();
+                tc::mbar_arrive(a_ready + s);
+            }
+            tc::mbar_wait(d_ready + s, d_par);
+            d_par ^= 1;
+            tc::fence_after_thread_sync();
+            uint32_t r[16];
+            output_row_load(t_d, r);
+            tc::fence_before_thread_sync();
+            if (valid) output_row_store(r, out_activation, row, out16, radiance4);
+        }
+    } else if (warp == 8) {
+        // ------------------------------------------------ MMA issue
+        if (lane == 0) {
+            uint32_t cnt = 0, a_par0 = 0, a_par1 = 0;
+            const uint32_t ring = tc::smem_u32(smem + FnSmem::RING);
+            for (long long pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
+#pragma unroll 1
+                for (int l = 0; l < FN_LAYERS; l++, cnt++) {
+                    const uint32_t slot = cnt % FN_RING;
+                    tc::mbar_wait(w_full + slot, (cnt / FN_RING) & 1u);
+                    const int K = fn_layer_k(l);
+                    const uint32_t idesc = l == FN_LAYERS - 1 ? tc::idesc_f16_f32(NET_TILE, NET_OUT)
+                                                               : tc::idesc_f16_f32(NET_TILE, FN_W);
+                    const uint32_t sbo = (uint32_t)(K / 8) * 128u;
+                    const uint32_t w_addr = ring + slot * FN_SLOT_BYTES;
+#pragma unroll
+                    for (int s = 0; s < 2; s++) {
+                        tc::mbar_wait(a_ready + s, s ? a_par1 : a_par0);
+                        if (s) a_par1 ^= 1; else a_par0 ^= 1;
+                        tc::fence_after_thread_sync();
+                        const uint32_t t_d = tmem_base + (uint32_t)(s * 256), t_a = t_d + 128;
+                        for (int ks = 0; ks < K / 16; ks++)
+                            tc::mma_f16_ts(t_d, t_a + ks * 8, tc::smem_desc(w_addr + ks * 256, 128, sbo), idesc,
+                                           ks > 0 ? 1u : 0u);
+                        tc::mma_commit(d_ready + s);
+                    }
+                    tc::mma_commit(w_empty + slot);
+                }
+            }
+        }
+    } else {
+        // ------------------------------------------------ weight loader
+        if (lane == 0) {
+            uint32_t cnt = 0;
+            for (long long pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
+#pragma unroll 1
+                for (int l = 0; l < FN_LAYERS; l++, cnt++) {
+                    const uint32_t slot = cnt % FN_RING, use = cnt / FN_RING;
+                    if (use > 0) tc::mbar_wait(w_empty + slot, (use - 1) & 1u);
+                    const uint32_t bytes = fn_layer_bytes(l);
+                    tc::mbar_arrive_expect_tx(w_full + slot, bytes);
+                    tc::bulk_g2s(smem + FnSmem::RING + slot * FN_SLOT_BYTES, packed + fn_layer_offset(l), bytes,
+                                 w_full + slot);
+                }
+            }
+        }
+    }
+    tc::fence_before_thread_sync();
+    __syncthreads();
+    tc::fence_after_thread_sync();
+    if (warp == 0) tc::tmem_dealloc<512>(tmem_base);
+}
+
+// ------------------------------------------------------------------------------------ host ABI
+extern "C" size_t rtxnerf_freqnet_param_count(void) { return (size_t)FN_PACKED_BYTES / 2; }
+
+extern "C" int rtxnerf_freqnet_pack(const uint16_t* d_weights, uint16_t* d_packed, void* stream)
+{
+    if (!d_weights || !d_packed) return RTXNERF_EINVAL;
+    if (((uintptr_t)d_weights & 15u) || ((uintptr_t)d_packed & 15u)) return RTXNERF_EINVAL;
+    freqnet_pack_kernel<<<64, 256, 0, (cudaStream_t)stream>>>(d_weights, reinterpret_cast<uint8_t*>(d_packed));
+    return rtx_launch_status();
+}
+
+static int freqnet_check(const rtxnerf_freqnet* net)
+{
+    if (!net || !net->weights_packed) return RTXNERF_EINVAL;
+    if (net->n_freq_xyz != FN_XYZ_FREQS || net->n_freq_dir != FN_DIR_FREQS || net->width != FN_W ||
+        net->n_hidden != FN_HIDDEN)
+        return RTXNERF_ECONFIG;
+    if (net->out_activation != 0 && net->out_activation != 1) return RTXNERF_ECONFIG;
+    if ((uintptr_t)net->weights_packed & 15u) return RTXNERF_EINVAL;
+    return RTXNERF_OK;
+}
+
+extern "C" int rtxnerf_freqnet_encode(const float* d_samples, int sample_stride, long long n, uint16_t* d_encoded,
+                                      void* stream)
+{
+    if (!d_samples || !d_encoded || n < 0 || sample_stride < 5) return RTXNERF_EINVAL;
+    if ((uintptr_t)d_encoded & 15u) return RTXNERF_EINVAL;
+    if (n == 0) return RTXNERF_OK;
+    freqnet_encode_kernel<<<(unsigned)((n + 127) / 128), 128, 0, (cudaStream_t)stream>>>(d_samples, sample_stride, n,
+                                                                                         d_encoded);
+    return rtx_launch_status();
+}
+
+extern "C" int rtxnerf_freqnet_forward(const rtxnerf_freqnet* net, const float* d_samples, int sample_stride,
+                                       const long long* d_count, long long count_scale, long long n_max,
+                                       uint16_t* d_out16, float* d_radiance4, void* stream)
+{
+    int rc = freqnet_check(net);
+    if (rc) return rc;
+    if (!d_samples || (!d_out16 && !d_radiance4) || n_max < 0 || sample_stride < 5 || count_scale < 1)
+        return RTXNERF_EINVAL;
+    if (n_max == 0) return RTXNERF_OK;
+    static bool attr = false;
+    if (!attr) {
+        RTX_CUDA_TRY(cudaFuncSetAttribute(freqnet_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          FnSmem::BYTES));
+        attr = true;
+    }
+    const long long pairs = ((n_max + NET_TILE - 1) / NET_TILE + 1) / 2;
+    const long long blocks = pairs < RTX_NUM_SMS ? pairs : RTX_NUM_SMS;   // one CTA per SM owns all 512 TMEM columns
+    freqnet_forward_kernel<<<(unsigned)blocks, FN_THREADS, FnSmem::BYTES, (cudaStream_t)stream>>>(
+        reinterpret_cast<const uint8_t*>(net->weights_packed), d_samples, sample_stride, net->out_activation, d_count,
+        count_scale, n_max, d_out16, d_radiance4);
+    return rtx_launch_status();
+}

@@ -128,6 +128,21 @@ class NetworkRadiance:
                              count_scale=r.S, impl=self.impl)
 
 
+class FrequencyNetworkRadiance:
+    """The reference's own network configuration (main.cu:47-68) as the radiance stage: Frequency
+    encoding + 8 x 128 MLP on the sampler's [N][5] buffer (api.FrequencyNetwork)."""
+    needs_cells = False
+    launches = 1
+    fusable = False
+
+    def __init__(self, network):
+        self.net = network
+
+    def __call__(self, r):
+        self.net.forward(None, r.samples, radiance=r.radiance, n=r.N_cap, d_count=r.hits.total_hits,
+                         count_scale=r.S)
+
+
 class Trainer:
     """One data-parallel training step of the reference's loop (main.cu:612-805) on this rank's
     rays: march -> sampler -> network forward (features kept) -> compositing -> L2 loss ->

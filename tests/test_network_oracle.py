@@ -59,3 +59,21 @@ def test_mlp_oracle_vs_numpy(orc):
     np.testing.assert_allclose(out16.astype(np.float64), o, atol=1e-3)
     assert np.array_equal(rad, out16[:, :4].astype(np.float32))
     assert w.size == 7168                        # SURVEY: 7 168 MLP parameters
+
+
+def test_frequency_encoding_oracle_properties(orc):
+    """Composite Frequency encoding of main.cu:47-61 restated: layout, padding, known values."""
+    s = np.array([[0.0, 0.5, -0.25, 1.0, 0.125], [0.3, -0.7, 0.9, 2.0, -3.0]], np.float32)
+    e = orc.frequency_encode(s).astype(np.float32)
+    assert e.shape == (2, 112) and np.all(e[:, 108:] == 1.0)
+    # x = 0: sin = 0, cos = 1 at every octave
+    assert np.all(e[0, 0:20:2] == 0.0) and np.all(e[0, 1:20:2] == 1.0)
+    # y = 0.5: sin(pi/2) = 1, cos = 0; next octave sin(pi) = 0, cos = -1; then cos = 1
+    assert e[0, 20] == 1.0 and e[0, 21] == 0.0 and e[0, 22] == 0.0 and e[0, 23] == -1.0 and e[0, 25] == 1.0
+    # z = -0.25: sin(-pi/4)
+    assert abs(e[0, 40] + np.sqrt(0.5)) < 1e-3 and abs(e[0, 41] - np.sqrt(0.5)) < 1e-3
+    # theta block starts at 60 with 12 frequencies, phi at 84
+    assert abs(e[0, 84] - np.sin(np.pi * 0.125)) < 1e-3 and abs(e[0, 85] - np.cos(np.pi * 0.125)) < 1e-3
+    # sin^2 + cos^2 = 1 within fp16 rounding everywhere
+    p = e[1, :108].reshape(54, 2)
+    assert np.all(np.abs((p ** 2).sum(1) - 1.0) < 3e-3)
