@@ -254,7 +254,8 @@ typedef struct rtxnerf_freqnet {
     int out_activation;              /* 0 none, 1 sigmoid */
 } rtxnerf_freqnet;
 
-size_t rtxnerf_freqnet_param_count(void);
+size_t rtxnerf_freqnet_param_count(void);    /* fp16 values in `weights` */
+size_t rtxnerf_freqnet_packed_count(void);   /* fp16 values in `weights_packed` (layer 0 padded to 128 inputs) */
 int rtxnerf_freqnet_pack(const uint16_t* d_weights, uint16_t* d_packed, void* stream);
 /* [n][sample_stride >= 5] fp32 rows (x,y,z,theta,phi) -> fp16 [n][112] */
 int rtxnerf_freqnet_encode(const float* d_samples, int sample_stride, long long n, uint16_t* d_encoded,

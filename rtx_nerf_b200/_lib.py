@@ -88,6 +88,7 @@ SIGNATURES = {
     "rtxnerf_render_rays_fused": (c_int, [C.POINTER(HashGrid), C.POINTER(Mlp), c_void_p, c_void_p, c_void_p, c_void_p,
                                           c_int, c_int, c_int, c_void_p, c_void_p]),
     "rtxnerf_freqnet_param_count": (c_size_t, []),
+    "rtxnerf_freqnet_packed_count": (c_size_t, []),
     "rtxnerf_freqnet_pack": (c_int, [c_void_p, c_void_p, c_void_p]),
     "rtxnerf_freqnet_encode": (c_int, [c_void_p, c_int, c_ll, c_void_p, c_void_p]),
     "rtxnerf_freqnet_forward": (c_int, [C.POINTER(FreqNet), c_void_p, c_int, c_void_p, c_ll, c_ll, c_void_p, c_void_p,

@@ -283,7 +283,7 @@ class FrequencyNetwork:
         if w.size != n:
             raise ValueError("FrequencyNetwork needs %d fp16 weights, got %d" % (n, w.size))
         self.weights = torch.as_tensor(w).to(device)
-        self.packed = torch.empty_like(self.weights)
+        self.packed = torch.empty(int(_lib.load().rtxnerf_freqnet_packed_count()), dtype=torch.float16, device=device)
         self.out_activation = int(out_activation)
         self.repack()
 

@@ -32,30 +32,36 @@
 #define FN_RING 4
 #define FN_SLOT_BYTES (FN_W * FN_W * 2)
 #define FN_THREADS 320
-#define FN_PACKED_BYTES (FN_W * FN_IN * 2 + (FN_HIDDEN - 1) * FN_W * FN_W * 2 + NET_OUT * FN_W * 2)
+#define FN_PARAMS (FN_W * FN_IN + (FN_HIDDEN - 1) * FN_W * FN_W + NET_OUT * FN_W)     // row-major fp16 values
+#define FN_PACKED_BYTES (FN_HIDDEN * FN_W * FN_W * 2 + NET_OUT * FN_W * 2)           // layer 0 padded to K = 128
 
-__host__ __device__ constexpr int fn_layer_k(int l) { return l == 0 ? FN_IN : FN_W; }
+__host__ __device__ constexpr int fn_layer_k(int l) { return l == 0 ? FN_IN : FN_W; }     // K of the row-major source
 __host__ __device__ constexpr int fn_layer_n(int l) { return l == FN_LAYERS - 1 ? NET_OUT : FN_W; }
-__host__ __device__ constexpr uint32_t fn_layer_bytes(int l) { return (uint32_t)(fn_layer_n(l) * fn_layer_k(l) * 2); }
-__host__ __device__ constexpr uint32_t fn_layer_offset(int l)
+__host__ __device__ constexpr uint32_t fn_layer_bytes(int l) { return (uint32_t)(fn_layer_n(l) * FN_W * 2); }
+__host__ __device__ constexpr uint32_t fn_layer_offset(int l) { return (uint32_t)(l * FN_W * FN_W * 2); }
+__host__ __device__ constexpr uint32_t fn_layer_src(int l)      // first fp16 of layer l in the row-major weights
 {
-    return l == 0 ? 0u : (uint32_t)(FN_W * FN_IN * 2 + (l - 1) * FN_W * FN_W * 2);
+    return l == 0 ? 0u : (uint32_t)(FN_W * FN_IN + (l - 1) * FN_W * FN_W);
 }
 
-// row-major [out][in] per layer -> the no-swizzle K-major core-matrix layout the MMA reads
-// (mlp_tile.cuh tile_chunk_off), layers concatenated: a ring slot is filled by ONE bulk copy.
+// row-major [out][in] per layer -> the K-major SWIZZLE_128B operand layout, layers concatenated
+// (a ring slot is filled by ONE bulk copy and read by the MMA as is):
+//   element (r, k) of an [N][128] layer at  (k/64)*(N*128) + (r/8)*1024 + (r%8)*128 + (((k%64)/8) ^ (r%8))*16 + (k%8)*2
+// i.e. two K-blocks of 64 (one 128-byte row each), 8-row swizzle atoms of 1 KB.  Layer 0's 112
+// inputs are zero-padded to 128.  (The no-swizzle core-matrix layout of mlp_tile.cuh ran the
+// M128 N128 K16 MMAs at ~40 % of their rate here.)
 __global__ void freqnet_pack_kernel(const uint16_t* __restrict__ w, uint8_t* __restrict__ packed)
 {
     const int total_chunks = FN_PACKED_BYTES / 16;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total_chunks; i += gridDim.x * blockDim.x) {
-        int l = 0;
-        while (l + 1 < FN_LAYERS && (uint32_t)i * 16u >= fn_layer_offset(l + 1)) l++;
-        const int K = fn_layer_k(l), chunks = K >> 3;
-        const int local = i - (int)(fn_layer_offset(l) / 16);
-        const int r = local / chunks, c = local - r * chunks;
-        const uint16_t* src = w + fn_layer_offset(l) / 2 + (size_t)r * K + c * 8;   // row-major offsets coincide
-        *reinterpret_cast<uint4*>(packed + fn_layer_offset(l) + tile_chunk_off(r, c, K)) =
-            *reinterpret_cast<const uint4*>(src);
+        const int l = min(i / (FN_W * FN_W * 2 / 16), FN_LAYERS - 1);
+        const int N = fn_layer_n(l), K = fn_layer_k(l);
+        const int local = i - (int)(fn_layer_offset(l) / 16);      // chunk index (r, c) in [N][16 chunks of 8]
+        const int r = local >> 4, c = local & 15;
+        uint4 v = make_uint4(0u, 0u, 0u, 0u);
+        if (c * 8 < K) v = *reinterpret_cast<const uint4*>(w + fn_layer_src(l) + (size_t)r * K + c * 8);
+        const uint32_t off = (uint32_t)((c >> 3) * (N * 128) + (r >> 3) * 1024 + (r & 7) * 128 + (((c & 7) ^ (r & 7)) << 4));
+        *reinterpret_cast<uint4*>(packed + fn_layer_offset(l) + off) = v;
     }
 }
 
@@ -87,19 +93,19 @@ __device__ __forceinline__ void frequency_row(const float* __restrict__ p, bool 
             if (nc == 16) { sink(base, col); base += 16; nc = 0; }
         }
     }
-    // 54 columns so far: 6 in col[]; two columns of ones complete the last 8
+    // 54 columns so far: 6 in col[]; two columns of ones complete the 112 features, eight
+    // columns of zeros pad the row to K = 128 for the tensor core (the weights there are zero)
     col[6] = valid ? 0x3c003c00u : 0u;
     col[7] = col[6];
-    uint32_t last[8];
 #pragma unroll
-    for (int i = 0; i < 8; i++) last[i] = col[i];
-    sink.tail(base, last);
+    for (int i = 8; i < 16; i++) col[i] = 0u;
+    sink.tail(base, col);
 }
 
 struct TmemRowSink {
     uint32_t taddr;   // this thread's lane row, first A column
     __device__ __forceinline__ void operator()(int base, const uint32_t (&c)[16]) const { tc::tmem_st_x16(taddr + base, c); }
-    __device__ __forceinline__ void tail(int base, const uint32_t (&c)[8]) const { tc::tmem_st_x8(taddr + base, c); }
+    __device__ __forceinline__ void tail(int base, const uint32_t (&c)[16]) const { tc::tmem_st_x16(taddr + base, c); }
 };
 struct GlobalRowSink {
     uint32_t* row;    // [56] packed columns of this sample, or nullptr
@@ -109,7 +115,7 @@ struct GlobalRowSink {
         for (int i = 0; i < 4; i++)
             reinterpret_cast<uint4*>(row + base)[i] = make_uint4(c[4 * i], c[4 * i + 1], c[4 * i + 2], c[4 * i + 3]);
     }
-    __device__ __forceinline__ void tail(int base, const uint32_t (&c)[8]) const
+    __device__ __forceinline__ void tail(int base, const uint32_t (&c)[16]) const   // the 112 real features only
     {
 #pragma unroll
         for (int i = 0; i < 2; i++)
@@ -128,10 +134,10 @@ __global__ void freqnet_encode_kernel(const float* __restrict__ samples, int str
 }
 
 struct FnSmem {
-    static constexpr int RING = 0;                                   // FN_RING slots of 32 KB
+    static constexpr int RING = 0;                                   // FN_RING slots of 32 KB, 1 KB-aligned
     static constexpr int BAR = RING + FN_RING * FN_SLOT_BYTES;       // w_full[R], w_empty[R], a_ready[2], d_ready[2]
     static constexpr int TMEM_SLOT = BAR + 8 * (2 * FN_RING + 4);
-    static constexpr int BYTES = TMEM_SLOT + 16;
+    static constexpr int BYTES = TMEM_SLOT + 16 + 1024;             // + slack for the 1 KB alignment
 };
 
 // hidden-layer epilogue of one row: 128 fp32 accumulator columns -> ReLU -> fp16 -> 64 A columns
@@ -158,7 +164,8 @@ freqnet_forward_kernel(const uint8_t* __restrict__ packed, const float* __restri
                        int out_activation, const long long* __restrict__ d_count, long long count_scale,
                        long long n_max, uint16_t* __restrict__ out16, float* __restrict__ radiance4)
 {
-    extern __shared__ __align__(128) uint8_t smem[];
+    extern __shared__ __align__(128) uint8_t smem_raw[];
+    uint8_t* smem = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);   // swizzle atoms are 1 KB
     uint64_t* w_full = reinterpret_cast<uint64_t*>(smem + FnSmem::BAR);
     uint64_t* w_empty = w_full + FN_RING;
     uint64_t* a_ready = w_empty + FN_RING;
@@ -233,10 +240,9 @@ freqnet_forward_kernel(const uint8_t* __restrict__ packed, const float* __restri
                 for (int l = 0; l < FN_LAYERS; l++, cnt++) {
                     const uint32_t slot = cnt % FN_RING;
                     tc::mbar_wait(w_full + slot, (cnt / FN_RING) & 1u);
-                    const int K = fn_layer_k(l);
                     const uint32_t idesc = l == FN_LAYERS - 1 ? tc::idesc_f16_f32(NET_TILE, NET_OUT)
                                                                : tc::idesc_f16_f32(NET_TILE, FN_W);
-                    const uint32_t sbo = (uint32_t)(K / 8) * 128u;
+                    const uint32_t kb_stride = (uint32_t)fn_layer_n(l) * 128u;     // second K-block of 64
                     const uint32_t w_addr = ring + slot * FN_SLOT_BYTES;
 #pragma unroll
                     for (int s = 0; s < 2; s++) {
@@ -244,8 +250,10 @@ freqnet_forward_kernel(const uint8_t* __restrict__ packed, const float* __restri
                         if (s) a_par1 ^= 1; else a_par0 ^= 1;
                         tc::fence_after_thread_sync();
                         const uint32_t t_d = tmem_base + (uint32_t)(s * 256), t_a = t_d + 128;
-                        for (int ks = 0; ks < K / 16; ks++)
-                            tc::mma_f16_ts(t_d, t_a + ks * 8, tc::smem_desc(w_addr + ks * 256, 128, sbo), idesc,
+#pragma unroll
+                        for (int ks = 0; ks < FN_W / 16; ks++)
+                            tc::mma_f16_ts(t_d, t_a + ks * 8,
+                                           tc::smem_desc_sw128(w_addr + (ks >> 2) * kb_stride + (ks & 3) * 32), idesc,
                                            ks > 0 ? 1u : 0u);
                         tc::mma_commit(d_ready + s);
                     }
@@ -277,7 +285,8 @@ freqnet_forward_kernel(const uint8_t* __restrict__ packed, const float* __restri
 }
 
 // ------------------------------------------------------------------------------------ host ABI
-extern "C" size_t rtxnerf_freqnet_param_count(void) { return (size_t)FN_PACKED_BYTES / 2; }
+extern "C" size_t rtxnerf_freqnet_param_count(void) { return (size_t)FN_PARAMS; }
+extern "C" size_t rtxnerf_freqnet_packed_count(void) { return (size_t)FN_PACKED_BYTES / 2; }
 
 extern "C" int rtxnerf_freqnet_pack(const uint16_t* d_weights, uint16_t* d_packed, void* stream)
 {

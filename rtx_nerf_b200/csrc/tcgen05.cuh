@@ -65,6 +65,20 @@ __device__ __forceinline__ uint64_t smem_desc(uint32_t saddr, uint32_t lbo_bytes
     d |= (uint64_t)1 << 46;
     return d;
 }
+// K-major SWIZZLE_128B operand: rows of 128 bytes (64 fp16 of K), 8-row atoms of 1 KB whose
+// 16-byte chunks are XOR-ed with the row index; SBO = 1024 (next 8 rows), LBO unused, layout
+// type 2 at [61,64).  The tile base must be 1 KB-aligned; a K=16 slice inside the 128-byte row
+// is addressed by adding 32 bytes to the start address.
+__device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t saddr)
+{
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr & 0x3FFFFu) >> 4);
+    d |= (uint64_t)1 << 16;
+    d |= (uint64_t)(1024u >> 4) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)2 << 61;
+    return d;
+}
 // Instruction descriptor for kind::f16: fp16 A/B (format 0), fp32 accumulate (c_format 1 at
 // bits [4,6)), both operands K-major, N>>3 at [17,23), M>>4 at [24,29).
 __host__ __device__ constexpr uint32_t idesc_f16_f32(int M, int N)
