@@ -14,6 +14,10 @@ NVCC_FLAGS = ["-std=c++17", "-O3", "-gencode", "arch=compute_100a,code=sm_100a",
               "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr", "-Xptxas", "-v"]
 
 
+if os.environ.get("FN_TRACE") == "1":     # development: role timeline of network_freq.cu (scripts/freqnet_trace.py)
+    NVCC_FLAGS.append("-DFN_TRACE")
+
+
 def sources():
     return sorted(glob.glob(os.path.join(CSRC, "*.cu")))
 

@@ -13,13 +13,16 @@
 //     M128 N128 K16 MMA reads 8 KB per 64 cycles — the whole 128 B/clk of the SM's shared
 //     memory — and the epilogue's stores would stall it; with A in TMEM shared memory only
 //     feeds B (the weights).
-//   * two tiles of 128 samples are in flight per SM (2 x (128 + 64) of the 512 TMEM columns):
-//     while the tensor core multiplies tile 0 by W_l, four warps run tile 1's epilogue.
-//   * the weights (256 KB, more than shared memory) are pre-packed once into the UMMA
-//     core-matrix layout and streamed from L2 layer by layer through a 4-slot ring with
-//     cp.async.bulk + mbarrier transaction counts; one load serves both tiles.
-//   * roles: warps 0-3 / 4-7 = encode + epilogue of tile slot 0 / 1 (TMEM lane quarters),
-//     warp 8 = MMA issue (one thread), warp 9 = weight loader (one thread).
+//   * two tiles of 128 samples are in flight per SM (2 x (128 accumulator + 64 hidden-operand +
+//     64 encoded-operand) = all 512 TMEM columns): while the tensor core multiplies tile 0 by
+//     W_l, four warps run tile 1's epilogue, and eight more warps encode the NEXT pair of tiles
+//     straight into TMEM, so the MUFU-bound encoding (108 sin/cos per row) is off the layer chain.
+//   * the weights (256 KB, more than shared memory) are pre-packed once into the K-major
+//     SWIZZLE_128B operand layout and streamed from L2 layer by layer through a 4-slot ring
+//     with cp.async.bulk + mbarrier transaction counts; one load serves both tiles.
+//   * one tcgen05.commit per layer-tile and nothing else on the issuing thread: a commit costs
+//     it ~200 cycles, so ring slots are released by a plain mbarrier arrive from the epilogue.
+// Measured (B200, 40.96 M rows): see DESIGN.md 4.7 / profiles/r01_e_freqnet_*.
 #include "common.cuh"
 #include "mlp_tile.cuh"
 
@@ -31,7 +34,7 @@
 #define FN_LAYERS 9          // 112->128, 7 x 128->128, 128->16
 #define FN_RING 4
 #define FN_SLOT_BYTES (FN_W * FN_W * 2)
-#define FN_THREADS 320
+#define FN_THREADS 576
 #define FN_PARAMS (FN_W * FN_IN + (FN_HIDDEN - 1) * FN_W * FN_W + NET_OUT * FN_W)     // row-major fp16 values
 #define FN_PACKED_BYTES (FN_HIDDEN * FN_W * FN_W * 2 + NET_OUT * FN_W * 2)           // layer 0 padded to K = 128
 
@@ -133,12 +136,32 @@ __global__ void freqnet_encode_kernel(const float* __restrict__ samples, int str
     frequency_row(samples + s * stride, true, sink);
 }
 
+#ifdef FN_TRACE
+// development trace: clock64 stamps of CTA 0 (role 0/1 = epilogue of slot 0/1, role 2 = MMA thread)
+__device__ long long fn_trace[3 * 1024];
+__device__ __forceinline__ void fn_mark(int role, int& idx)
+{
+    if (blockIdx.x == 0 && idx < 1024) fn_trace[role * 1024 + idx] = clock64();
+    idx++;
+}
+extern "C" int rtxnerf_debug_freqnet_trace(long long* host_out)
+{
+    return (int)cudaMemcpyFromSymbol(host_out, fn_trace, sizeof(fn_trace));
+}
+#else
+__device__ __forceinline__ void fn_mark(int, int&) {}
+#endif
+
 struct FnSmem {
     static constexpr int RING = 0;                                   // FN_RING slots of 32 KB, 1 KB-aligned
-    static constexpr int BAR = RING + FN_RING * FN_SLOT_BYTES;       // w_full[R], w_empty[R], a_ready[2], d_ready[2]
-    static constexpr int TMEM_SLOT = BAR + 8 * (2 * FN_RING + 4);
+    static constexpr int BAR = RING + FN_RING * FN_SLOT_BYTES;       // see FnBars
+    static constexpr int TMEM_SLOT = BAR + 8 * (2 * FN_RING + 8);
     static constexpr int BYTES = TMEM_SLOT + 16 + 1024;             // + slack for the 1 KB alignment
 };
+// TMEM columns of tile slot s (base s*256): accumulators, hidden-layer A operand, encoded A operand
+#define FN_COL_D 0
+#define FN_COL_AH 128
+#define FN_COL_AE 192
 
 // hidden-layer epilogue of one row: 128 fp32 accumulator columns -> ReLU -> fp16 -> 64 A columns
 __device__ __forceinline__ void fn_hidden_epilogue(uint32_t t_d, uint32_t t_a)
@@ -159,6 +182,15 @@ __device__ __forceinline__ void fn_hidden_epilogue(uint32_t t_d, uint32_t t_a)
     }
 }
 
+// Roles (18 warps): 0-3 / 4-7 epilogue of tile slot 0 / 1, 8-11 / 12-15 encoder of slot 0 / 1
+// (warp % 4 = TMEM lane quarter in both), 16 MMA issue, 17 weight loader.
+// Hand-offs (mbarriers): enc_ready[s] encoder -> MMA (layer-0 operand written), enc_free[s]
+// epilogue -> encoder (layer-0 MMA of the previous tile has completed: its operand may be
+// overwritten), a_ready[s] epilogue -> MMA (next hidden operand written), d_ready[s] MMA ->
+// epilogue (tcgen05.commit: accumulators complete), w_full[k] loader -> MMA (bulk copy landed),
+// w_empty[k] slot-1 epilogue -> loader (the layer's MMAs of BOTH tiles have completed: the tensor
+// pipe runs in order, so tile 1's completion covers tile 0).  The only tcgen05.commit per
+// layer-tile is d_ready: a commit stalls the issuing thread for ~200 cycles.
 __global__ void __launch_bounds__(FN_THREADS, 1)
 freqnet_forward_kernel(const uint8_t* __restrict__ packed, const float* __restrict__ samples, int stride,
                        int out_activation, const long long* __restrict__ d_count, long long count_scale,
@@ -170,6 +202,8 @@ freqnet_forward_kernel(const uint8_t* __restrict__ packed, const float* __restri
     uint64_t* w_empty = w_full + FN_RING;
     uint64_t* a_ready = w_empty + FN_RING;
     uint64_t* d_ready = a_ready + 2;
+    uint64_t* enc_ready = d_ready + 2;
+    uint64_t* enc_free = enc_ready + 2;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + FnSmem::TMEM_SLOT);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
@@ -181,6 +215,8 @@ freqnet_forward_kernel(const uint8_t* __restrict__ packed, const float* __restri
         for (int i = 0; i < 2; i++) {
             tc::mbar_init(a_ready + i, NET_TILE);
             tc::mbar_init(d_ready + i, 1);
+            tc::mbar_init(enc_ready + i, NET_TILE);
+            tc::mbar_init(enc_free + i, 1);
         }
         tc::fence_mbar_init();
     }
@@ -199,41 +235,68 @@ freqnet_forward_kernel(const uint8_t* __restrict__ packed, const float* __restri
     const long long n_pairs = (n_tiles + 1) / 2;
 
     if (warp < 8) {
-        // ------------------------------------------------ encode + epilogue group of tile slot s
+        // ------------------------------------------------ epilogue group of tile slot s
         const int s = warp >> 2, wk = warp & 3;
-        const uint32_t t_d = tmem_base + (uint32_t)(s * 256) + ((uint32_t)(wk * 32) << 16);
-        const uint32_t t_a = t_d + 128;
+        const uint32_t t_d = tmem_base + (uint32_t)(s * 256 + FN_COL_D) + ((uint32_t)(wk * 32) << 16);
+        const uint32_t t_a = t_d + FN_COL_AH;
         const int row_in_tile = wk * 32 + lane;
-        uint32_t d_par = 0;
+        const bool leader = wk == 0 && lane == 0;
+        uint32_t d_par = 0, cnt = 0;
+        int tr = 0;
         for (long long pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
             const long long row = (pair * 2 + s) * NET_TILE + row_in_tile;
-            const bool valid = row < n;
-            TmemRowSink sink{t_a};
-            frequency_row(samples + (valid ? row : 0) * stride, valid, sink);
-            tc::tmem_st_wait();
-            tc::fence_before_thread_sync();
-            tc::mbar_arrive(a_ready + s);
-            for (int l = 0; l < FN_HIDDEN; l++) {
+            for (int l = 0; l < FN_HIDDEN; l++, cnt++) {
                 tc::mbar_wait(d_ready + s, d_par);
                 d_par ^= 1;
+                if (leader) {
+                    fn_mark(s, tr);                               // accumulators seen
+                    if (l == 0) tc::mbar_arrive(enc_free + s);    // the encoded operand has been consumed
+                    if (s == 1) tc::mbar_arrive(w_empty + cnt % FN_RING);
+                }
                 tc::fence_after_thread_sync();
                 fn_hidden_epilogue(t_d, t_a);
                 tc::tmem_st_wait();
                 tc::fence_before_thread_sync();
                 tc::mbar_arrive(a_ready + s);
+                if (leader) fn_mark(s, tr);                       // next operand published
             }
             tc::mbar_wait(d_ready + s, d_par);
             d_par ^= 1;
+            if (leader && s == 1) tc::mbar_arrive(w_empty + cnt % FN_RING);
+            cnt++;
             tc::fence_after_thread_sync();
             uint32_t r[16];
             output_row_load(t_d, r);
             tc::fence_before_thread_sync();
-            if (valid) output_row_store(r, out_activation, row, out16, radiance4);
+            if (row < n) output_row_store(r, out_activation, row, out16, radiance4);
         }
-    } else if (warp == 8) {
+    } else if (warp < 16) {
+        // ------------------------------------------------ encoder group of tile slot s
+        const int s = (warp - 8) >> 2, wk = warp & 3;
+        const uint32_t t_e = tmem_base + (uint32_t)(s * 256 + FN_COL_AE) + ((uint32_t)(wk * 32) << 16);
+        const int row_in_tile = wk * 32 + lane;
+        uint32_t f_par = 0;
+        bool first = true;
+        for (long long pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
+            const long long row = (pair * 2 + s) * NET_TILE + row_in_tile;
+            const bool valid = row < n;
+            if (!first) {
+                tc::mbar_wait(enc_free + s, f_par);
+                f_par ^= 1;
+                tc::fence_after_thread_sync();
+            }
+            first = false;
+            TmemRowSink sink{t_e};
+            frequency_row(samples + (valid ? row : 0) * stride, valid, sink);
+            tc::tmem_st_wait();
+            tc::fence_before_thread_sync();
+            tc::mbar_arrive(enc_ready + s);
+        }
+    } else if (warp == 16) {
         // ------------------------------------------------ MMA issue
         if (lane == 0) {
-            uint32_t cnt = 0, a_par0 = 0, a_par1 = 0;
+            uint32_t cnt = 0, a_par0 = 0, a_par1 = 0, e_par = 0;
+            int tr = 0;
             const uint32_t ring = tc::smem_u32(smem + FnSmem::RING);
             for (long long pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
 #pragma unroll 1
@@ -246,18 +309,25 @@ freqnet_forward_kernel(const uint8_t* __restrict__ packed, const float* __restri
                     const uint32_t w_addr = ring + slot * FN_SLOT_BYTES;
 #pragma unroll
                     for (int s = 0; s < 2; s++) {
-                        tc::mbar_wait(a_ready + s, s ? a_par1 : a_par0);
-                        if (s) a_par1 ^= 1; else a_par0 ^= 1;
+                        if (l == 0) {
+                            tc::mbar_wait(enc_ready + s, e_par);
+                        } else {
+                            tc::mbar_wait(a_ready + s, s ? a_par1 : a_par0);
+                            if (s) a_par1 ^= 1; else a_par0 ^= 1;
+                        }
                         tc::fence_after_thread_sync();
-                        const uint32_t t_d = tmem_base + (uint32_t)(s * 256), t_a = t_d + 128;
+                        fn_mark(2, tr);                       // per (l, s): operand seen
+                        const uint32_t t_d = tmem_base + (uint32_t)(s * 256 + FN_COL_D);
+                        const uint32_t t_a = tmem_base + (uint32_t)(s * 256 + (l == 0 ? FN_COL_AE : FN_COL_AH));
 #pragma unroll
                         for (int ks = 0; ks < FN_W / 16; ks++)
                             tc::mma_f16_ts(t_d, t_a + ks * 8,
                                            tc::smem_desc_sw128(w_addr + (ks >> 2) * kb_stride + (ks & 3) * 32), idesc,
                                            ks > 0 ? 1u : 0u);
                         tc::mma_commit(d_ready + s);
+                        fn_mark(2, tr);                       // per (l, s): MMAs issued + committed
                     }
-                    tc::mma_commit(w_empty + slot);
+                    if (l == 0) e_par ^= 1;
                 }
             }
         }
