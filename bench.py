@@ -246,6 +246,34 @@ def run_ours(args):
     e2e_s = time.perf_counter() - t0
     clock_summary = clocks.summary() if clocks else None
 
+    # ---- the same view through the reference's OWN network configuration (main.cu:47-68:
+    # Frequency encoding + 8 x 128 FullyFusedMLP), staged path; rank 0 only, short run
+    refnet = None
+    if not args.no_refnet and rank == 0:
+        fnet = api.FrequencyNetwork(synth.mlp_weights(112, 128, 8, 16, seed=4))
+        r2 = pipeline.ViewRenderer(grid, W, H, focal, W / H, S, HM, pipeline.FrequencyNetworkRadiance(fnet))
+        for k in range(2):
+            r2.render_device(poses_dev[k])
+        torch.cuda.synchronize()
+        n2 = 5
+        ev2 = [[torch.cuda.Event(enable_timing=True) for _ in range(5)] for _ in range(n2)]
+        for k in range(n2):
+            r2.pose_dev.copy_(poses_dev[args.warmup + k], non_blocking=True)
+            ev2[k][0].record()
+            for i, (_, fn) in enumerate(r2.stages(fused=False)):
+                fn()
+                ev2[k][i + 1].record()
+        torch.cuda.synchronize()
+        ms2 = [float(np.mean([ev2[k][i].elapsed_time(ev2[k][i + 1]) for k in range(n2)])) for i in range(4)]
+        n_s2 = float(r2.hits.total_hits.item()) * S
+        tf2 = 262144.0 * n_s2 / (ms2[2] * 1e-3) / 1e12
+        refnet = dict(workload="configs[1] view with the reference's literal network: Frequency(10 / 12 frequencies) "
+                               "-> 8 x 128 ReLU -> 16 (sigmoid), fp16, 262144 FLOP/sample; staged path",
+                      ms_per_view=sum(ms2), rays_per_s=W * H / (sum(ms2) * 1e-3), samples_per_s=n_s2 / (sum(ms2) * 1e-3),
+                      network_ms=ms2[2], network_tflops=tf2, peak_tflops=pk["tf"], frac_of_peak=tf2 / pk["tf"],
+                      stages_ms=dict(march=ms2[0], sampler=ms2[1], network=ms2[2], composite=ms2[3]))
+        del r2, fnet
+
     # ---- training step (BASELINE configs[3]): 2^18 rays x (S=4, H_max=32), fwd + bwd + Adam,
     # NCCL all-reduce of the flat fp32 gradient buffer when N > 1; a short run, reported beside
     # the headline
@@ -320,8 +348,13 @@ def run_ours(args):
                 stages[nme] = dict(ms=ms, bound="hbm", achieved=gb, peak=pk["hbm"], unit="GB/s", frac=gb / pk["hbm"])
         dom = max(stages, key=lambda k: stages[k]["ms"])
         d = stages[dom]
+        # dram bytes per launch of the dominant kernel from the committed ncu --set full capture
+        traffic = None
+        tpath = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+        if os.path.exists(tpath):
+            traffic = json.load(open(tpath)).get(dom)
         roofline = dict(kernel=dom, bound=d["bound"], achieved=d["achieved"], peak=d["peak"], unit=d["unit"],
-                        frac=d["frac"], traffic=None, peak_source=pk["src"],
+                        frac=d["frac"], traffic=traffic, peak_source=pk["src"],
                         note="achieved = algorithmic work per launch (SURVEY 8d) / mean CUDA-event duration of that "
                              "stage inside the timed region; kernel share of the step = %.2f" % (d["ms"] / sum(stage_ms)))
         line = dict(metric="rays/s", value=value, unit="rays/s", n_gpus=world, steps=args.steps, warmup=args.warmup,
@@ -334,6 +367,8 @@ def run_ours(args):
                     e2e=dict(value=rays_all / (e2e_ms * 1e-3), unit="rays/s", h2d_bytes_per_step=64,
                              d2h_bytes_per_step=R * 12, ms_per_step=e2e_ms / args.steps),
                     gpu_launches=launches, roofline=roofline, stages=stages, clocks=clock_summary)
+        if refnet:
+            line["reference_network"] = refnet
         if train:
             line["train_step"] = dict(
                 workload="configs[3]: 2^18 rays per GPU per step, S=4 x H_max=32 (128 samples/ray), network fwd+bwd, "
@@ -363,6 +398,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     ap.add_argument("--no-train", action="store_true", help="skip the training-step leg (profiling runs)")
+    ap.add_argument("--no-refnet", action="store_true", help="skip the Frequency + 8x128 network leg")
     ap.add_argument("--spinup", type=float, default=0.5, help="seconds of untimed load before the timed steps")
     ap.add_argument("--staged", action="store_true",
                     help="render through the separate sampler / network / compositing entry points instead of the "
