@@ -253,12 +253,12 @@ def run_ours(args):
         fnet = api.FrequencyNetwork(synth.mlp_weights(112, 128, 8, 16, seed=4))
         r2 = pipeline.ViewRenderer(grid, W, H, focal, W / H, S, HM, pipeline.FrequencyNetworkRadiance(fnet))
         for k in range(2):
-            r2.render_device(poses_dev[k])
+            r2.render_device(poses_dev[k % len(poses_dev)])
         torch.cuda.synchronize()
         n2 = 5
         ev2 = [[torch.cuda.Event(enable_timing=True) for _ in range(5)] for _ in range(n2)]
         for k in range(n2):
-            r2.pose_dev.copy_(poses_dev[args.warmup + k], non_blocking=True)
+            r2.pose_dev.copy_(poses_dev[(args.warmup + k) % len(poses_dev)], non_blocking=True)
             ev2[k][0].record()
             for i, (_, fn) in enumerate(r2.stages(fused=False)):
                 fn()

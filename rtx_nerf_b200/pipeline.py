@@ -38,7 +38,7 @@ class ViewRenderer:
         self.pose_pinned = torch.empty(16, dtype=torch.float32).pin_memory()
         self.pixels_pinned = torch.empty((self.R, 3), dtype=torch.float32).pin_memory()
         march = 1 if max_hits <= 32 else 3
-        self.launches_per_view = march + 1 if self.can_fuse else march + 1 + radiance.launches + 1
+        self.launches_per_view = (march + 1) if self.can_fuse else (march + 1 + radiance.launches + 1)
 
     # --- stages (all asynchronous on the current stream) -------------------------------
     def stage_march(self):
