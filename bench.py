@@ -218,10 +218,20 @@ def run_ours(args):
     # untimed clock spin-up: a B200 coming out of idle needs a few hundred ms of load to reach
     # its steady SM clock; without it the first process on a fresh box measures the ramp
     t_spin = time.perf_counter()
-    while time.perf_counter() - t_spin < args.spinup:
+    prev = None
+    while True:
+        a_ev, b_ev = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a_ev.record()
         for _ in range(8):
             graph.replay()
+        b_ev.record()
         torch.cuda.synchronize()
+        cur = a_ev.elapsed_time(b_ev)
+        el = time.perf_counter() - t_spin
+        # steady = two consecutive batches within 2 %; never less than --spinup, never more than 6 s
+        if el >= args.spinup and (args.spinup == 0 or el > 6.0 or (prev is not None and abs(cur - prev) < 0.02 * prev)):
+            break
+        prev = cur
     hits_total = torch.zeros(1, dtype=torch.int64, device="cuda")
     barrier()
     t_start = torch.cuda.Event(enable_timing=True)

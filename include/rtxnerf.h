@@ -62,6 +62,24 @@ int rtxnerf_grid_resolution(const rtxnerf_grid* g);
  * main.cu:399,492 stores in Params.aabb); built lazily, owned by the grid. */
 int rtxnerf_grid_device_aabbs(rtxnerf_grid* g, float** d_aabb6_out);
 
+/* Device-side rebuild from densities (the reference has only the static make_grid
+ * and its "TODO: make this a CUDA kernel", main.cu:153).
+ *   rtxnerf_grid_cell_samples: [G^3][5] fp32 rows (x,y,z = cell centre, theta = phi = 0) in
+ *     primitive order — the rows to run the network on;
+ *   rtxnerf_grid_update_from_density: sigma of cell p at d_sigma[p*sigma_stride] (stride 4 on the
+ *     network's [n][4] radiance buffer, +3 offset applied by the caller);
+ *     d_ema != NULL: ema = max(ema*decay, sigma) (instant-ngp's rule) else ema = sigma;
+ *     cell occupied iff ema > threshold.  Asynchronous; the next march sees the new bits.
+ *   rtxnerf_grid_read_bits: synchronous copy of the bitfield to the host. */
+int rtxnerf_grid_cell_samples(int G, float* d_rows5, void* stream);
+int rtxnerf_grid_update_from_density(rtxnerf_grid* g, const float* d_sigma, int sigma_stride, float decay,
+                                     float* d_ema, float threshold, void* stream);
+int rtxnerf_grid_read_bits(const rtxnerf_grid* g, uint32_t* bits_host);
+
+/* Headless image output (stb_image_write is vendored but unused, main.cu:19-21):
+ * fp32 RGB [height][width][3] on the HOST, clamped to [0,1] -> binary PPM (P6). */
+int rtxnerf_write_ppm(const char* path, const float* pixels_host, int width, int height);
+
 /* ------------------------------------------------------------------------------------
  * Ray march — replaces optixLaunch(pipeline_ray_march, ...) (main.cu:506-508) and the
  * device programs rtx/src/optixPrograms.cu:43-248.
@@ -144,6 +162,17 @@ int rtxnerf_launch_sampler(const float* d_start_points, const float* d_end_point
                            int batch_size, int grid_res, const int* d_num_hits,
                            const int* d_indices, int sample_type, int samples_per_segment,
                            void* stream);
+
+/* Same, with counter-based random draws for the STRATIFIED_JITTERING / UNIFORM modes (SURVEY 8
+ * f4): seed != 0 replaces the reference's by-value default-seeded thrust::minstd_rand
+ * (sampler.cu:25,117 — every thread draws the identical sequence and every launch repeats it)
+ * by u = splitmix64(seed, global sample index) >> 40 scaled to [0,1), t = fma(u, b - a, a);
+ * seed == 0 is rtxnerf_launch_sampler.  REGULAR mode ignores the seed. */
+int rtxnerf_launch_sampler_seeded(const float* d_start_points, const float* d_end_points,
+                                  const float* d_view_dirs, float* d_t_vals, float* d_sampled_points,
+                                  int batch_size, int grid_res, const int* d_num_hits,
+                                  const int* d_indices, int sample_type, int samples_per_segment,
+                                  unsigned long long seed, void* stream);
 
 /* ------------------------------------------------------------------------------------
  * Volume rendering — replaces launch_volrender_cuda / launch_volrender_backward_cuda

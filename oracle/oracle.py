@@ -183,7 +183,8 @@ def compact_hits(num_hits, indices, arr_size, dense, comps):
 
 
 # --------------------------------------------------------------------------- sampler / compositing
-def sampler(start_points, end_points, view_dirs, num_hits, indices, S=32, sample_type=0, nthreads=None):
+def sampler(start_points, end_points, view_dirs, num_hits, indices, S=32, sample_type=0, nthreads=None, seed=0):
+    """seed = 0: the reference's own draws (sampler.cu:25,117); seed != 0: counter-based draws (f4)."""
     start_points = np.ascontiguousarray(start_points, np.float32)
     end_points = np.ascontiguousarray(end_points, np.float32)
     view_dirs = np.ascontiguousarray(view_dirs, np.float32)
@@ -192,10 +193,10 @@ def sampler(start_points, end_points, view_dirs, num_hits, indices, S=32, sample
     N = int(num_hits.sum()) * S
     samples = np.empty((N, 5), np.float32)
     t_vals = np.empty(N, np.float32)
-    lib().orc_sampler(_ptr(start_points, _f32p), _ptr(end_points, _f32p), _ptr(view_dirs, _f32p),
-                      _ptr(t_vals, _f32p), _ptr(samples, _f32p), C.c_int(num_hits.size),
-                      _ptr(num_hits, _i32p), _ptr(indices, _i32p), C.c_int(S), C.c_int(sample_type),
-                      C.c_int(nthreads or default_threads()))
+    lib().orc_sampler_seeded(_ptr(start_points, _f32p), _ptr(end_points, _f32p), _ptr(view_dirs, _f32p),
+                             _ptr(t_vals, _f32p), _ptr(samples, _f32p), C.c_int(num_hits.size),
+                             _ptr(num_hits, _i32p), _ptr(indices, _i32p), C.c_int(S), C.c_int(sample_type),
+                             C.c_ulonglong(seed), C.c_int(nthreads or default_threads()))
     return samples, t_vals
 
 

@@ -378,10 +378,37 @@ static inline float uniform_real(minstd* g, float a, float b)
     return fmaf(result, b - a, a);
 }
 
+/* Counter-based uniform draw in [0,1) for the seeded sampling modes: splitmix64 of
+ * (seed, global sample index), top 24 bits.  Unlike the reference's by-value minstd_rand
+ * (sampler.cu:25,117: every thread draws the same sequence) each sample gets its own draw and a
+ * launch is reproducible from (seed, index) alone. */
+float orc_counter_uniform(unsigned long long seed, unsigned long long index)
+{
+    unsigned long long z = seed + (index + 1ull) * 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    z = z ^ (z >> 31);
+    return (float)(z >> 40) * (1.0f / 16777216.0f);
+}
+
+void orc_sampler_seeded(const float* start_points, const float* end_points, const float* view_dirs,
+                        float* t_vals, float* samples, int batch_size, const int* num_hits,
+                        const int* indices, int S, int sample_type, unsigned long long seed, int nthreads);
+
 /* sampler/sampler.cu:14-103 */
 void orc_sampler(const float* start_points, const float* end_points, const float* view_dirs,
                  float* t_vals, float* samples, int batch_size, const int* num_hits,
                  const int* indices, int S, int sample_type, int nthreads)
+{
+    orc_sampler_seeded(start_points, end_points, view_dirs, t_vals, samples, batch_size, num_hits, indices, S,
+                       sample_type, 0ull, nthreads);
+}
+
+/* seed == 0: the reference's own draws (by-value default-seeded minstd_rand); seed != 0: the
+ * same modes with counter-based draws, t = fma(u, b - a, a). */
+void orc_sampler_seeded(const float* start_points, const float* end_points, const float* view_dirs,
+                        float* t_vals, float* samples, int batch_size, const int* num_hits,
+                        const int* indices, int S, int sample_type, unsigned long long seed, int nthreads)
 {
     const float inv_s = 1.0f / (float)S; /* sampler.cu:50,65 */
 #pragma omp parallel for schedule(dynamic, 256) num_threads(nthreads > 0 ? nthreads : 1)
@@ -404,10 +431,11 @@ void orc_sampler(const float* start_points, const float* end_points, const float
                     t_initial += inv_s;
                     t_vals[n] = t_initial;
                 } else if (sample_type == 2) { /* :68-81 */
-                    t = uniform_real(&rng, 0.0f, 1.0f);
+                    t = seed ? orc_counter_uniform(seed, n) : uniform_real(&rng, 0.0f, 1.0f);
                     t_vals[n] = t_initial;
                 } else { /* :82-99 */
-                    t = uniform_real(&rng, t_initial, t_final);
+                    t = seed ? fmaf(orc_counter_uniform(seed, n), t_final - t_initial, t_initial)
+                             : uniform_real(&rng, t_initial, t_final);
                     t_vals[n] = t_initial;
                     t_initial = t_final;
                     t_final += inv_s;

@@ -90,6 +90,10 @@ void orc_compact_hits(const int* num_hits, const int* indices, int n_rays, int a
 /* sampler/sampler.cu:14-103 with NUM_SAMPLES_PER_SEGMENT = S (reference: 32).
  * sample_type: 0 REGULAR, 1 STRATIFIED_JITTERING, 2 UNIFORM (sampler.h:5-9).
  * samples [N][5] = x,y,z,theta,phi;  t_vals [N];  N = S * sum(num_hits). */
+float orc_counter_uniform(unsigned long long seed, unsigned long long index);
+void orc_sampler_seeded(const float* start_points, const float* end_points, const float* view_dirs,
+                        float* t_vals, float* samples, int batch_size, const int* num_hits,
+                        const int* indices, int S, int sample_type, unsigned long long seed, int nthreads);
 void orc_sampler(const float* start_points, const float* end_points, const float* view_dirs,
                  float* t_vals, float* samples, int batch_size,
                  const int* num_hits, const int* indices, int S, int sample_type,

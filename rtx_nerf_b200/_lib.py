@@ -68,12 +68,18 @@ SIGNATURES = {
     "rtxnerf_grid_destroy": (c_int, [c_void_p]),
     "rtxnerf_grid_resolution": (c_int, [c_void_p]),
     "rtxnerf_grid_device_aabbs": (c_int, [c_void_p, C.POINTER(c_void_p)]),
+    "rtxnerf_grid_cell_samples": (c_int, [c_int, c_void_p, c_void_p]),
+    "rtxnerf_grid_update_from_density": (c_int, [c_void_p, c_void_p, c_int, c_float, c_void_p, c_float, c_void_p]),
+    "rtxnerf_grid_read_bits": (c_int, [c_void_p, c_void_p]),
+    "rtxnerf_write_ppm": (c_int, [C.c_char_p, c_void_p, c_int, c_int]),
     "rtxnerf_ray_march_dense": (c_int, [C.POINTER(Params), c_void_p]),
     "rtxnerf_ray_march_workspace_bytes": (c_size_t, [c_ll]),
     "rtxnerf_ray_march_csr": (c_int, [c_void_p, C.POINTER(Camera), c_ll, c_ll, c_int, C.POINTER(Hits),
                                       c_void_p, c_size_t, c_void_p]),
     "rtxnerf_launch_sampler": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,
                                        c_void_p, c_void_p, c_int, c_int, c_void_p]),
+    "rtxnerf_launch_sampler_seeded": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,
+                                              c_void_p, c_void_p, c_int, c_int, C.c_ulonglong, c_void_p]),
     "rtxnerf_launch_volrender": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,
                                          c_void_p, c_void_p]),
     "rtxnerf_launch_volrender_backward": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,

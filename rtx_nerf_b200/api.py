@@ -43,18 +43,20 @@ def _chk_dev(t, dtype, name):
 # ----------------------------------------------------------------------------- sampler
 def launchSampler(d_start_points, d_end_points, d_view_dirs, d_t_vals, d_sampled_points, batch_size,
                   grid_res, d_num_hits, d_indices, sample_type=SAMPLING_REGULAR, stream=None,
-                  samples_per_segment=NUM_SAMPLES_PER_SEGMENT):
-    """sampler/sampler.h:19-30.  Asynchronous on `stream`."""
+                  samples_per_segment=NUM_SAMPLES_PER_SEGMENT, seed=0):
+    """sampler/sampler.h:19-30.  Asynchronous on `stream`.  seed != 0: counter-based draws for the
+    STRATIFIED_JITTERING / UNIFORM modes instead of the reference's repeated minstd sequence."""
     for t, dt, n in ((d_start_points, torch.float32, "d_start_points"), (d_end_points, torch.float32, "d_end_points"),
                      (d_view_dirs, torch.float32, "d_view_dirs"), (d_t_vals, torch.float32, "d_t_vals"),
                      (d_sampled_points, torch.float32, "d_sampled_points"), (d_num_hits, torch.int32, "d_num_hits"),
                      (d_indices, torch.int32, "d_indices")):
         _chk_dev(t, dt, n)
     lib = _lib.load()
-    _lib.check(lib.rtxnerf_launch_sampler(_p(d_start_points), _p(d_end_points), _p(d_view_dirs), _p(d_t_vals),
-                                          _p(d_sampled_points), int(batch_size), int(grid_res), _p(d_num_hits),
-                                          _p(d_indices), int(sample_type), int(samples_per_segment),
-                                          _stream_ptr(stream)), "launchSampler")
+    _lib.check(lib.rtxnerf_launch_sampler_seeded(_p(d_start_points), _p(d_end_points), _p(d_view_dirs),
+                                                 _p(d_t_vals), _p(d_sampled_points), int(batch_size), int(grid_res),
+                                                 _p(d_num_hits), _p(d_indices), int(sample_type),
+                                                 int(samples_per_segment), int(seed), _stream_ptr(stream)),
+               "launchSampler")
     _lib.count_launches(1 if batch_size > 0 else 0)
 
 
@@ -145,6 +147,31 @@ class OccupancyGrid:
         bits = np.ascontiguousarray(occ_bits, np.uint32)
         _lib.check(_lib.load().rtxnerf_grid_update(self._h, bits.ctypes.data_as(C.c_void_p), _stream_ptr(stream)),
                    "grid_update")
+
+    def cell_samples(self, rows=None, stream=None):
+        """[G^3][5] fp32 rows at the cell centres, primitive order: the network's input for an update."""
+        if rows is None:
+            rows = torch.empty((self.G ** 3, 5), dtype=torch.float32, device="cuda")
+        _lib.check(_lib.load().rtxnerf_grid_cell_samples(int(self.G), _p(rows), _stream_ptr(stream)), "grid_cell_samples")
+        return rows
+
+    def update_from_density(self, sigma, threshold, decay=0.0, ema=None, stream=None):
+        """Device-side rebuild: sigma is a float tensor whose element [p*stride] is the
+        density of cell p — a [G^3] vector or the [:, 3] column view of the network's [G^3][4]
+        radiance.  ema: optional [G^3] running maximum, ema = max(ema*decay, sigma)."""
+        if sigma.dtype != torch.float32 or not sigma.is_cuda:
+            raise TypeError("sigma must be a float32 CUDA tensor")
+        stride = sigma.stride(0) if sigma.dim() == 1 else None
+        if stride is None or sigma.shape[0] != self.G ** 3:
+            raise ValueError("sigma must be a 1-D (possibly strided) view of G^3 densities")
+        _lib.check(_lib.load().rtxnerf_grid_update_from_density(self._h, sigma.data_ptr(), int(stride), float(decay),
+                                                                _p(ema), float(threshold), _stream_ptr(stream)),
+                   "grid_update_from_density")
+
+    def read_bits(self):
+        out = np.empty((self.G ** 3 + 31) // 32, np.uint32)
+        _lib.check(_lib.load().rtxnerf_grid_read_bits(self._h, out.ctypes.data_as(C.c_void_p)), "grid_read_bits")
+        return out
 
     def device_aabbs(self):
         p = C.c_void_p()
@@ -264,6 +291,16 @@ def cell_radiance(hit_cells, total_hits, capacity_hits, samples_per_segment, cel
 # ----------------------------------------------------------------------------- network
 IMPL_TCGEN05 = 0
 IMPL_SIMT = 1
+
+
+def write_ppm(path, pixels, width, height):
+    """Headless image output: [height*width][3] fp32 RGB (host or device) -> binary PPM."""
+    px = pixels.detach().cpu().numpy() if hasattr(pixels, "detach") else np.asarray(pixels)
+    px = np.ascontiguousarray(px, np.float32).reshape(-1)
+    if px.size != width * height * 3:
+        raise ValueError("pixels must hold width*height RGB triples")
+    _lib.check(_lib.load().rtxnerf_write_ppm(str(path).encode(), px.ctypes.data_as(C.c_void_p), int(width), int(height)),
+               "write_ppm")
 
 
 class FrequencyNetwork:

@@ -9,6 +9,14 @@
 
 #define RTX_NUM_SMS 148  // B200: 2 dies x 74 SMs; grids are sized in multiples of this
 
+// the occupancy grid behind the opaque rtxnerf_grid handle (march.cu, grid_update.cu)
+struct rtxnerf_grid {
+    int G;
+    size_t n_words;
+    uint32_t* d_bits;   // G^3 bits, bit (p&31) of word (p>>5), p = (x*G+y)*G+z
+    float* d_aabb;      // lazily built make_grid list (compat with Params.aabb)
+};
+
 #define RTX_CUDA_TRY(expr)                      \
     do {                                        \
         cudaError_t _e = (expr);                \

@@ -23,13 +23,6 @@
 #include <new>
 #include <vector>
 
-struct rtxnerf_grid {
-    int G;
-    size_t n_words;
-    uint32_t* d_bits;   // G^3 bits, bit (p&31) of word (p>>5), p = (x*G+y)*G+z
-    float* d_aabb;      // lazily built make_grid list (compat with Params.aabb)
-};
-
 #define RAY_TMAX 102.0f              // optixPrograms.cu:80: (max.z - min.z) + 100
 #define CLAMP_EPS 9.99999997e-07f    // (float)1e-6: for float t, (double)t > 1e-6  <=>  t > (float)1e-6
 #define MARCH_BLOCK 128

@@ -36,6 +36,18 @@ __device__ __forceinline__ float uniform_real(uint32_t draw_index, float a, floa
     return rn_fma(r, rn_sub(b, a), a);
 }
 
+// Counter-based draw in [0,1) for the seeded modes (oracle: orc_counter_uniform):
+// splitmix64 of (seed, global sample index), top 24 bits.  Every sample has its own draw and a
+// launch is reproducible from (seed, index) alone.
+__device__ __forceinline__ float counter_uniform(unsigned long long seed, unsigned long long index)
+{
+    unsigned long long z = seed + (index + 1ull) * 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    z = z ^ (z >> 31);
+    return (float)(z >> 40) * (1.0f / 16777216.0f);
+}
+
 // i repeated additions of inv_s starting from `from` (sampler.cu:65,97: t += 1.0f/S)
 __device__ __forceinline__ float accumulate_steps(float from, float inv_s, int i, bool exact_pow2)
 {
@@ -49,7 +61,7 @@ __global__ void __launch_bounds__(SAMPLER_WARPS * 32)
 sampler_kernel(const float* __restrict__ start_points, const float* __restrict__ end_points,
                const float* __restrict__ view_dirs, float* __restrict__ t_vals, float* __restrict__ samples,
                int batch_size, const int* __restrict__ num_hits, const int* __restrict__ indices, int S,
-               int sample_type)
+               int sample_type, unsigned long long seed)
 {
     __shared__ __align__(16) float tile[SAMPLER_WARPS][160];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -80,14 +92,16 @@ sampler_kernel(const float* __restrict__ start_points, const float* __restrict__
                     t = accumulate_steps(0.0f, inv_s, i, pow2);
                     tv = rn_add(t, inv_s);
                 } else if (sample_type == 2) {           // UNIFORM :68-81 (t_vals stays t_initial = 0)
-                    t = uniform_real((uint32_t)(q + 1), 0.0f, 1.0f);
+                    t = seed ? counter_uniform(seed, (unsigned long long)(out0 + q))
+                             : uniform_real((uint32_t)(q + 1), 0.0f, 1.0f);
                     tv = 0.0f;
                 } else {                                 // STRATIFIED_JITTERING :82-99
                     float t0 = accumulate_steps(0.0f, inv_s, i, pow2);   // t_initial after i steps
                     float t1 = accumulate_steps(inv_s, inv_s, i, pow2);  // t_final after i steps
                     // t_initial = t_final (i>0) : after the first step t_initial carries t_final's value
                     if (i > 0) t0 = accumulate_steps(inv_s, inv_s, i - 1, pow2);
-                    t = uniform_real((uint32_t)(q + 1), t0, t1);
+                    t = seed ? rn_fma(counter_uniform(seed, (unsigned long long)(out0 + q)), rn_sub(t1, t0), t0)
+                             : uniform_real((uint32_t)(q + 1), t0, t1);
                     tv = t0;
                 }
                 sx = rn_fma(t, dx, ax);                  // :57-59 (fma under nvcc -fmad)
@@ -123,6 +137,17 @@ extern "C" int rtxnerf_launch_sampler(const float* d_start_points, const float* 
                                       int batch_size, int grid_res, const int* d_num_hits, const int* d_indices,
                                       int sample_type, int samples_per_segment, void* stream)
 {
+    return rtxnerf_launch_sampler_seeded(d_start_points, d_end_points, d_view_dirs, d_t_vals, d_sampled_points,
+                                         batch_size, grid_res, d_num_hits, d_indices, sample_type,
+                                         samples_per_segment, 0ull, stream);
+}
+
+extern "C" int rtxnerf_launch_sampler_seeded(const float* d_start_points, const float* d_end_points,
+                                             const float* d_view_dirs, float* d_t_vals, float* d_sampled_points,
+                                             int batch_size, int grid_res, const int* d_num_hits,
+                                             const int* d_indices, int sample_type, int samples_per_segment,
+                                             unsigned long long seed, void* stream)
+{
     (void)grid_res;  // unused by the reference too (sampler.cu:19)
     if (!d_start_points || !d_end_points || !d_view_dirs || !d_t_vals || !d_sampled_points || !d_num_hits ||
         !d_indices)
@@ -134,6 +159,6 @@ extern "C" int rtxnerf_launch_sampler(const float* d_start_points, const float* 
     if (blocks > max_blocks) blocks = max_blocks;
     sampler_kernel<<<(unsigned)blocks, SAMPLER_WARPS * 32, 0, (cudaStream_t)stream>>>(
         d_start_points, d_end_points, d_view_dirs, d_t_vals, d_sampled_points, batch_size, d_num_hits, d_indices,
-        samples_per_segment, sample_type);
+        samples_per_segment, sample_type, seed);
     return rtx_launch_status();
 }

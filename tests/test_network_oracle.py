@@ -77,3 +77,30 @@ def test_frequency_encoding_oracle_properties(orc):
     # sin^2 + cos^2 = 1 within fp16 rounding everywhere
     p = e[1, :108].reshape(54, 2)
     assert np.all(np.abs((p ** 2).sum(1) - 1.0) < 3e-3)
+
+
+def test_seeded_sampler_oracle_properties(orc):
+    """Counter-based modes: stratified draws stay inside their stratum, uniform draws in
+    [0,1), draws differ between rays and seeds, seed 0 reproduces the reference's repeated sequence."""
+    rng = np.random.default_rng(0)
+    nh = np.array([3, 0, 3, 2], np.int32)
+    idx = np.array([0, 3, 3, 6], np.int32)
+    sp = rng.uniform(-1, 1, (8, 3)).astype(np.float32)
+    ep = sp + np.float32(0.01)
+    vd = np.zeros((4, 2), np.float32)
+    S = 8
+    s7, t7 = orc.sampler(sp, ep, vd, nh, idx, S, 1, seed=7)
+    t = ((s7[:, 0] - np.repeat(sp[:, 0], S)) / np.float32(0.01)).reshape(8, S)
+    lo = np.arange(S, dtype=np.float32) / S
+    assert np.all(t >= lo - 1e-3) and np.all(t <= lo + 1.0 / S + 1e-3)
+    assert np.array_equal(t7.reshape(8, S), np.tile(lo, (8, 1)))              # t_vals = stratum start (sampler.cu:96)
+    s8, _ = orc.sampler(sp, ep, vd, nh, idx, S, 1, seed=8)
+    assert not np.array_equal(s7, s8)
+    u, tu = orc.sampler(sp, ep, vd, nh, idx, S, 2, seed=7)
+    tt = (u[:, 0] - np.repeat(sp[:, 0], S)) / np.float32(0.01)
+    assert np.all(tt > -1e-3) and np.all(tt < 1 + 1e-3) and np.all(tu == 0)    # UNIFORM stores t_initial = 0 (Q12)
+    # seed 0 = the reference: rays 0 and 2 (same hit count) draw the identical sequence (Q14)
+    s0, _ = orc.sampler(sp, ep, vd, nh, idx, S, 1, seed=0)
+    t0 = ((s0[:, 0] - np.repeat(sp[:, 0], S)) / np.float32(0.01)).reshape(8, S)
+    assert np.allclose(t0[0:3], t0[3:6], atol=2e-3)
+    assert not np.allclose(t[0:3], t[3:6], atol=2e-3)
