@@ -346,6 +346,44 @@ hashgrid_backward_kernel(Levels lv, const float* __restrict__ samples, int strid
                     v[2 * c] = pt.w[c] * gl.x;
                     v[2 * c + 1] = pt.w[c] * gl.y;
                 }
+                if (heads == 1u) {
+                    // the whole warp sits in ONE cell (coarse levels): reduce-scatter instead of 5 x 16
+                    // butterflies.  Two halving rounds leave each lane one x-pair quad (4 values), three
+                    // plain rounds finish it: 24 shuffles instead of 80, and ONE 16-byte reduction per quad.
+                    const bool b4 = lane & 16, b3 = lane & 8;
+                    float h8[8];
+#pragma unroll
+                    for (int i = 0; i < 8; i++) {
+                        const float mine = b4 ? v[8 + i] : v[i], send = b4 ? v[i] : v[8 + i];
+                        h8[i] = mine + __shfl_xor_sync(FULL, send, 16);
+                    }
+                    float q4[4];
+#pragma unroll
+                    for (int i = 0; i < 4; i++) {
+                        const float mine = b3 ? h8[4 + i] : h8[i], send = b3 ? h8[i] : h8[4 + i];
+                        q4[i] = mine + __shfl_xor_sync(FULL, send, 8);
+                    }
+#pragma unroll
+                    for (int d = 4; d; d >>= 1)
+#pragma unroll
+                        for (int i = 0; i < 4; i++) q4[i] += __shfl_xor_sync(FULL, q4[i], d);
+                    if ((lane & 7) == 0) {       // lanes 0, 8, 16, 24 hold quads 0, 1, 2, 3 (qd = 2*b4 + b3)
+                        const int qd = lane >> 3;
+                        const uint32_t i0 = qd == 0 ? pt.idx[0] : qd == 1 ? pt.idx[2] : qd == 2 ? pt.idx[4] : pt.idx[6];
+                        const uint32_t i1 = qd == 0 ? pt.idx[1] : qd == 1 ? pt.idx[3] : qd == 2 ? pt.idx[5] : pt.idx[7];
+                        float2* gt = reinterpret_cast<float2*>(grad_table) + lv.offset[l];
+                        const float2 a = make_float2(q4[0], q4[1]), b = make_float2(q4[2], q4[3]);
+                        if ((i0 ^ i1) == 1u) {
+                            const bool odd = i0 & 1u;
+                            atomicAdd(reinterpret_cast<float4*>(gt + (i0 & ~1u)),
+                                      odd ? make_float4(b.x, b.y, a.x, a.y) : make_float4(a.x, a.y, b.x, b.y));
+                        } else {
+                            atomicAdd(gt + i0, a);
+                            atomicAdd(gt + i1, b);
+                        }
+                    }
+                    continue;
+                }
                 // lanes i and i+d are in the same run iff no head in (i, i+d]
                 const unsigned after = lane < 31 ? (heads >> (lane + 1)) : 1u;
 #pragma unroll

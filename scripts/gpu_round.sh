@@ -11,6 +11,8 @@ timeout 600 python bench.py > $O/bench.json 2> $O/bench.err; echo "bench rc=$?" 
 timeout 300 python bench.py --impl reference --steps 3 --warmup 1 > $O/bench_ref.json 2> $O/bench_ref.err; echo "ref rc=$?" | tee -a $O/rc.txt
 timeout 300 python scripts/stage_bench.py > $O/stage_bench.txt 2>&1
 timeout 300 python scripts/train_bench.py > $O/train_bench.txt 2>&1
+timeout 300 python scripts/ref_kernels_bench.py --json $O/ref_kernels.json > $O/ref_kernels.txt 2>&1; echo "ref-kernels rc=$?" | tee -a $O/rc.txt
+timeout 300 python scripts/freqnet_bench.py > $O/freqnet_bench.txt 2>&1
 if [ "$2" != "noprof" ]; then
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/launches.csv \
   python bench.py --steps 2 --warmup 3 --no-cpu --spinup 0 > $O/ncu_launch.log 2>&1; echo "ncu-list rc=$?" | tee -a $O/rc.txt
@@ -22,4 +24,4 @@ timeout 900 ncu --set full --clock-control none --import-source on -s 12 -c 4 -o
 timeout 900 ncu --set full --clock-control none --import-source on -s 24 -c 14 -o $O/train_full -f \
   python scripts/train_bench.py --steps 1 > $O/ncu_train.log 2>&1; echo "ncu-train rc=$?" | tee -a $O/rc.txt
 fi
-tail -3 $O/pytest.log; cat $O/smoke.log | tail -2; cat $O/bench.json | cut -c1-600; cat $O/stage_bench.txt; cat $O/train_bench.txt
+tail -3 $O/pytest.log; cat $O/smoke.log | tail -2; cat $O/bench.json | cut -c1-600; cat $O/stage_bench.txt; cat $O/train_bench.txt; cat $O/ref_kernels.txt; tail -3 $O/freqnet_bench.txt
