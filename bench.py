@@ -43,34 +43,47 @@ def peaks():
 
 
 class ClockSampler(threading.Thread):
-    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md)."""
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md: ONE
+    `nvidia-smi -lms 200` process, started before and killed after — spawning a fresh nvidia-smi
+    per sample re-initialises NVML over all GPUs of the box and perturbs the run it watches)."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
         super().__init__(daemon=True)
-        self.index, self.rows, self.stop_flag = index, [], False
+        self.index, self.rows, self.proc = index, [], None
 
     def run(self):
-        while not self.stop_flag:
-            try:
-                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
-                f = [x.strip() for x in out.strip().split(",")]
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            for line in self.proc.stdout:
+                f = [x.strip() for x in line.strip().split(",")]
                 if len(f) >= 6:
                     self.rows.append(f)
-            except Exception:
-                pass
-            time.sleep(0.1)
+        except Exception:
+            pass
 
     def summary(self):
-        self.stop_flag = True
-        if not self.rows:
+        if self.proc is not None:
+            try:
+                self.proc.terminate()          # the exact process started above
+                self.proc.wait(timeout=5)
+            except Exception:
+                pass
+        rows = []
+        for r in list(self.rows):
+            try:
+                rows.append((float(r[0]), float(r[1]), r[2:6]))
+            except ValueError:
+                pass
+        if not rows:
             return dict(sm_mhz=None, sm_max_mhz=None, reasons=["unsampled"])
-        sm = sorted(float(r[0]) for r in self.rows)
+        sm = sorted(r[0] for r in rows)
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = [n for i, n in enumerate(names) if any(r[2 + i].lower().startswith("active") for r in self.rows)]
-        return dict(sm_mhz=sm[len(sm) // 2], sm_max_mhz=float(self.rows[0][1]), reasons=reasons, samples=len(sm))
+        reasons = [n for i, n in enumerate(names) if any(r[2][i].lower().startswith("active") for r in rows)]
+        return dict(sm_mhz=sm[len(sm) // 2], sm_min_mhz=sm[0], sm_max_mhz=rows[0][1], reasons=reasons, samples=len(sm))
 
 
 def scene():
@@ -215,24 +228,31 @@ def run_ours(args):
             fn()
     launches_per_step = _lib.kernel_launches() - launches0
     graph.replay()
-    # untimed clock spin-up: a B200 coming out of idle needs a few hundred ms of load to reach
-    # its steady SM clock; without it the first process on a fresh box measures the ramp
+    # untimed clock spin-up: a B200 coming out of idle needs up to a second or two of load to reach
+    # its steady SM clock; without it the first process on a cold GPU measures the ramp.  Each
+    # batch is a rehearsal of the timed loop (same K poses), so consecutive batches are comparable:
+    # steady = two consecutive batches within 1.5 %, never less than --spinup s, never more than 8 s.
     t_spin = time.perf_counter()
     prev = None
+    n_spin = 0
+    hits_total = torch.zeros(1, dtype=torch.int64, device="cuda")
     while True:
+        n_spin += 1
         a_ev, b_ev = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a_ev.record()
-        for _ in range(8):
+        for k in range(args.steps):
+            r.pose_dev.copy_(poses_dev[args.warmup + k], non_blocking=True)
             graph.replay()
+            hits_total += r.hits.total_hits     # also loads this op's kernel before the timed region
         b_ev.record()
         torch.cuda.synchronize()
         cur = a_ev.elapsed_time(b_ev)
         el = time.perf_counter() - t_spin
-        # steady = two consecutive batches within 2 %; never less than --spinup, never more than 6 s
-        if el >= args.spinup and (args.spinup == 0 or el > 6.0 or (prev is not None and abs(cur - prev) < 0.02 * prev)):
+        if el >= args.spinup and (args.spinup == 0 or el > 8.0 or (prev is not None and abs(cur - prev) < 0.015 * prev)):
             break
         prev = cur
-    hits_total = torch.zeros(1, dtype=torch.int64, device="cuda")
+    spin_info = dict(seconds=round(el, 3), rehearsals=n_spin, last_ms_per_view=cur / args.steps)
+    hits_total.zero_()
     barrier()
     t_start = torch.cuda.Event(enable_timing=True)
     t_end = torch.cuda.Event(enable_timing=True)
@@ -248,12 +268,24 @@ def run_ours(args):
     hits = int(hits_total.item())
 
     # ---- e2e: the user's call, host pose in / host pixels out every step
+    # (ViewRenderer.render_views_host: the batch-of-views call of configs[2]; every step copies its
+    # 64-byte pose host->device from pinned memory and its 7.68 MB of pixels device->host, the
+    # latter on a copy stream under the next view's kernels.  The one-view synchronous call
+    # render_host is timed beside it.)
+    e2e_poses = [my_poses[args.warmup + k] for k in range(args.steps)]
+    e2e_out = torch.empty((args.steps, r.R, 3), dtype=torch.float32, pin_memory=True)
+    r.render_views_host(e2e_poses[:2], out=e2e_out[:2], fused=not args.staged)      # untimed: stream + buffers
     barrier()
+    t0 = time.perf_counter()
+    r.render_views_host(e2e_poses, out=e2e_out, fused=not args.staged)
+    barrier()
+    e2e_s = time.perf_counter() - t0
     t0 = time.perf_counter()
     for k in range(args.steps):
         r.render_host(my_poses[args.warmup + k], fused=not args.staged)
-    barrier()
-    e2e_s = time.perf_counter() - t0
+    e2e_sync_ms = (time.perf_counter() - t0) * 1e3 / args.steps
+    if not np.array_equal(e2e_out[args.steps - 1].numpy(), r.pixels_pinned.numpy()):
+        raise RuntimeError("render_views_host and render_host disagree on the last view")
     clock_summary = clocks.summary() if clocks else None
 
     # ---- the same view through the reference's OWN network configuration (main.cu:47-68:
@@ -314,15 +346,34 @@ def run_ours(args):
             tr.optimizer_step()
         b.record()
         barrier()
-        ar_ms = c.elapsed_time(d)   # the last step's collective
-        train = dict(ms=a.elapsed_time(b) / t_steps, allreduce_ms=ar_ms, rays=TR,
+        ar_ms = c.elapsed_time(d)   # the last step's collective, INCLUDING the wait for the slowest rank's backward
+        ar_alone = 0.0
+        if world > 1:               # the collective alone: all ranks enter together, 5 back-to-back calls
+            barrier()
+            c.record()
+            for _ in range(5):
+                tr.allreduce()
+            d.record()
+            barrier()
+            ar_alone = c.elapsed_time(d) / 5
+        train = dict(ms=a.elapsed_time(b) / t_steps, allreduce_ms=ar_ms, allreduce_alone_ms=ar_alone, rays=TR,
                      samples=float(tr.view.hits.total_hits.item()) * TS, grad_bytes=tr.grads.numel() * 4,
                      launches_per_step=tr.launches_per_step, loss=float(tr.loss_sum.item()) / (t_warm + t_steps))
 
     # ---- max over ranks
     tv = [train["ms"], train["allreduce_ms"], train["samples"]] if train else [0.0, 0.0, 0.0]
+    ar_alone_all = 0.0
+    if train and world > 1:
+        t_ar = torch.tensor([train["allreduce_alone_ms"]], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t_ar, op=dist.ReduceOp.MAX)
+        ar_alone_all = float(t_ar[0])
     vals = torch.tensor([ms_total, e2e_s * 1e3, float(hits)] + tv + stage_ms, dtype=torch.float64, device="cuda")
+    per_rank = [[ms_total / args.steps, spin_info["last_ms_per_view"]]]
     if world > 1:
+        mine = torch.tensor(per_rank[0], dtype=torch.float64, device="cuda")
+        allr = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(allr, mine)
+        per_rank = [[float(x) for x in t] for t in allr]
         mx = vals.clone()
         dist.all_reduce(mx, op=dist.ReduceOp.MAX)
         sm = vals.clone()
@@ -375,8 +426,11 @@ def run_ours(args):
                     samples_per_s=samples_all / (ms_total * 1e-3),
                     rays_per_step_per_gpu=R, samples_per_step_per_gpu=Ns,
                     e2e=dict(value=rays_all / (e2e_ms * 1e-3), unit="rays/s", h2d_bytes_per_step=64,
-                             d2h_bytes_per_step=R * 12, ms_per_step=e2e_ms / args.steps),
-                    gpu_launches=launches, roofline=roofline, stages=stages, clocks=clock_summary)
+                             d2h_bytes_per_step=R * 12, ms_per_step=e2e_ms / args.steps,
+                             call="ViewRenderer.render_views_host (K views, D2H of view k under view k+1)",
+                             one_view_sync_call_ms=e2e_sync_ms),
+                    gpu_launches=launches, roofline=roofline, stages=stages, clocks=clock_summary, spinup=spin_info,
+                    per_rank_ms=dict(timed=[round(x[0], 4) for x in per_rank], last_rehearsal=[round(x[1], 4) for x in per_rank]))
         if refnet:
             line["reference_network"] = refnet
         if train:
@@ -384,7 +438,7 @@ def run_ours(args):
                 workload="configs[3]: 2^18 rays per GPU per step, S=4 x H_max=32 (128 samples/ray), network fwd+bwd, "
                          "compositing fwd+bwd, L2 loss, Adam; NCCL all-reduce(sum) of the fp32 gradient buffer",
                 ms_per_step=train["ms"], rays_per_s=train["rays"] * world / (train["ms"] * 1e-3),
-                samples_per_s=train["samples_all"] / (train["ms"] * 1e-3), allreduce_ms=train["allreduce_ms"],
+                samples_per_s=train["samples_all"] / (train["ms"] * 1e-3), allreduce_ms=train["allreduce_ms"], allreduce_alone_ms=ar_alone_all,
                 allreduce_bytes=train["grad_bytes"], launches_per_step=train["launches_per_step"],
                 mean_loss=train["loss"], scaling="weak")
         if world == 1 and not args.no_cpu:
@@ -409,7 +463,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     ap.add_argument("--no-train", action="store_true", help="skip the training-step leg (profiling runs)")
     ap.add_argument("--no-refnet", action="store_true", help="skip the Frequency + 8x128 network leg")
-    ap.add_argument("--spinup", type=float, default=0.5, help="seconds of untimed load before the timed steps")
+    ap.add_argument("--spinup", type=float, default=1.5, help="seconds of untimed load before the timed steps")
     ap.add_argument("--staged", action="store_true",
                     help="render through the separate sampler / network / compositing entry points instead of the "
                          "fused kernel")

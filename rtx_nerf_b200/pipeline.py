@@ -93,6 +93,45 @@ class ViewRenderer:
         torch.cuda.current_stream().synchronize()
         return self.pixels_pinned
 
+    def render_views_host(self, poses_host, out=None, fused=None):
+        """Batch render (BASELINE configs[2], the reference's per-view loop main.cu:560-790): host
+        poses in, host pixels out for every view.  The device->host copy of view k runs on a copy
+        stream under the kernels of view k+1 (two device pixel buffers); returns the pinned
+        [n_views][R][3] buffer after the last copy has landed."""
+        n = len(poses_host)
+        if out is None:
+            out = torch.empty((n, self.R, 3), dtype=torch.float32, pin_memory=True)
+        if tuple(out.shape) != (n, self.R, 3) or out.dtype != torch.float32 or not out.is_pinned():
+            raise ValueError("render_views_host: out must be a pinned float32 [n_views][R][3] tensor")
+        if getattr(self, "_copy_stream", None) is None:
+            self._copy_stream = torch.cuda.Stream()
+            self._pixels_alt = torch.empty_like(self.pixels)
+        poses_pinned = torch.empty((n, 16), dtype=torch.float32, pin_memory=True)
+        poses_pinned.copy_(torch.as_tensor(np.asarray(poses_host, np.float32).reshape(n, 16)))
+        main = torch.cuda.current_stream()
+        bufs = [self.pixels, self._pixels_alt]
+        copied = [None, None]
+        try:
+            for k in range(n):
+                b = k & 1
+                if copied[b] is not None:
+                    main.wait_event(copied[b])          # this pixel buffer has left the device
+                self.pixels = bufs[b]
+                self.pose_dev.copy_(poses_pinned[k], non_blocking=True)
+                self.render_device(fused=fused)
+                rendered = torch.cuda.Event()
+                rendered.record(main)
+                self._copy_stream.wait_event(rendered)
+                with torch.cuda.stream(self._copy_stream):
+                    out[k].copy_(bufs[b], non_blocking=True)
+                    copied[b] = torch.cuda.Event()
+                    copied[b].record(self._copy_stream)
+        finally:
+            self.pixels = bufs[0]
+        self._copy_stream.synchronize()
+        main.synchronize()
+        return out
+
     def total_hits(self):
         return int(self.hits.total_hits.item())
 

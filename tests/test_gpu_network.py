@@ -185,3 +185,29 @@ def test_ray_coherent_schedule_matches_flat_kernel(cuda_api, n_rays, S):
     net.forward_rays(None, ds, _t(nh), _t(idx), n_rays, S, radiance=ray4b)
     torch.cuda.synchronize()
     assert np.array_equal(ray4b.cpu().numpy()[:n], flat4.cpu().numpy()[:n])
+
+
+def test_batch_render_views_host_matches_single_view_calls(cuda_api):
+    """ViewRenderer.render_views_host (configs[2]: a batch of views, the device->host copy of view k
+    under the kernels of view k+1) returns exactly what render_host returns view by view, for the
+    fused and the staged path, and leaves the renderer's pixel buffer where it was."""
+    import torch
+    from rtx_nerf_b200 import api, pipeline
+    G, W, H, S, HM = 64, 96, 80, 4, 16
+    occ = synth.occupancy_lego(G)
+    lv = synth.hashgrid_levels()
+    net = api.Network(lv, synth.hashgrid_table(lv, seed=1), synth.mlp_weights(seed=2))
+    grid = api.OccupancyGrid.from_occupancy(occ, G)
+    r = pipeline.ViewRenderer(grid, W, H, synth.focal_length(), W / H, S, HM, pipeline.NetworkRadiance(net))
+    poses = synth.poses(5, seed=21)
+    for fused in (True, False):
+        single = [r.render_host(p, fused=fused).clone() for p in poses]
+        before = r.pixels.data_ptr()
+        out = r.render_views_host(poses, fused=fused)
+        assert r.pixels.data_ptr() == before
+        assert tuple(out.shape) == (5, W * H, 3) and out.is_pinned()
+        for k in range(5):
+            assert torch.equal(out[k], single[k]), "view %d differs (fused=%s)" % (k, fused)
+    assert any(float(s.abs().max()) > 0 for s in single)
+    with pytest.raises(ValueError):
+        r.render_views_host(poses, out=torch.empty((5, W * H, 3)))
