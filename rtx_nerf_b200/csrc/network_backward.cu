@@ -515,7 +515,7 @@ extern "C" int rtxnerf_l2_loss(const float* d_pred, const float* d_target, long 
     if (blocks > RTX_NUM_SMS * 8) blocks = RTX_NUM_SMS * 8;
     l2_loss_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(d_pred, d_target, n, loss_scale, d_values,
                                                                       reinterpret_cast<__half*>(d_gradients), d_loss_sum);
-    return rtx_launch_status(2);
+    return rtx_launch_status();
 }
 
 extern "C" int rtxnerf_adam_step(long long n, float* d_master, uint16_t* d_params, float* d_grads, float* d_m1,
