@@ -18,6 +18,11 @@ if os.environ.get("FN_TRACE") == "1":     # development: role timeline of networ
     NVCC_FLAGS.append("-DFN_TRACE")
 
 
+for _k in ("FN_EPI_WARPS", "FN_ENC_WARPS"):   # development: role layout of network_freq.cu
+    if os.environ.get(_k):
+        NVCC_FLAGS.append("-D%s=%d" % (_k, int(os.environ[_k])))
+
+
 def sources():
     return sorted(glob.glob(os.path.join(CSRC, "*.cu")))
 

@@ -34,7 +34,19 @@
 #define FN_LAYERS 9          // 112->128, 7 x 128->128, 128->16
 #define FN_RING 4
 #define FN_SLOT_BYTES (FN_W * FN_W * 2)
-#define FN_THREADS 576
+// Role layout (measured at 40.96 M rows, best of 10): 4 epilogue warps per slot + 4 encoder warps per slot
+// 7.94 ms; 8 + 4 shared encoders 8.29 ms; 8 + 8 (72 registers, spills) 8.40 ms.
+#ifndef FN_EPI_WARPS
+#define FN_EPI_WARPS 4                          // epilogue warps per tile slot: 4, or 8 = two per TMEM lane quarter
+#endif
+#ifndef FN_ENC_WARPS
+#define FN_ENC_WARPS 8                          // encoder warps: 8 (4 per slot) or 4 (both slots, alternately)
+#endif
+#define FN_EPI_COLS (FN_W / (FN_EPI_WARPS / 4)) // accumulator columns one epilogue warp converts
+#define FN_WARP_ENC (2 * FN_EPI_WARPS)
+#define FN_WARP_MMA (FN_WARP_ENC + FN_ENC_WARPS)
+#define FN_WARP_LOAD (FN_WARP_MMA + 1)
+#define FN_THREADS ((FN_WARP_LOAD + 1) * 32)
 #define FN_PARAMS (FN_W * FN_IN + (FN_HIDDEN - 1) * FN_W * FN_W + NET_OUT * FN_W)     // row-major fp16 values
 #define FN_PACKED_BYTES (FN_HIDDEN * FN_W * FN_W * 2 + NET_OUT * FN_W * 2)           // layer 0 padded to K = 128
 
@@ -155,7 +167,7 @@ __device__ __forceinline__ void fn_mark(int, int&) {}
 struct FnSmem {
     static constexpr int RING = 0;                                   // FN_RING slots of 32 KB, 1 KB-aligned
     static constexpr int BAR = RING + FN_RING * FN_SLOT_BYTES;       // see FnBars
-    static constexpr int TMEM_SLOT = BAR + 8 * (2 * FN_RING + 8);
+    static constexpr int TMEM_SLOT = BAR + 8 * (2 * FN_RING + 10);
     static constexpr int BYTES = TMEM_SLOT + 16 + 1024;             // + slack for the 1 KB alignment
 };
 // TMEM columns of tile slot s (base s*256): accumulators, hidden-layer A operand, encoded A operand
@@ -164,10 +176,10 @@ struct FnSmem {
 #define FN_COL_AE 192
 
 // hidden-layer epilogue of one row: 128 fp32 accumulator columns -> ReLU -> fp16 -> 64 A columns
-__device__ __forceinline__ void fn_hidden_epilogue(uint32_t t_d, uint32_t t_a)
+__device__ __forceinline__ void fn_hidden_epilogue(uint32_t t_d, uint32_t t_a, int h_begin)
 {
 #pragma unroll
-    for (int h = 0; h < FN_W / 32; h++) {
+    for (int h = h_begin; h < h_begin + FN_EPI_COLS / 32; h++) {
         uint32_t r0[16], r1[16];
         tc::tmem_ld_x16(t_d + h * 32, r0);
         tc::tmem_ld_x16(t_d + h * 32 + 16, r1);
@@ -182,14 +194,16 @@ __device__ __forceinline__ void fn_hidden_epilogue(uint32_t t_d, uint32_t t_a)
     }
 }
 
-// Roles (18 warps): 0-3 / 4-7 epilogue of tile slot 0 / 1, 8-11 / 12-15 encoder of slot 0 / 1
-// (warp % 4 = TMEM lane quarter in both), 16 MMA issue, 17 weight loader.
+// Roles (18 warps by default): 0-3 / 4-7 epilogue of tile slot 0 / 1, 8-11 / 12-15 encoder of slot
+// 0 / 1 (warp % 4 = TMEM lane quarter everywhere), 16 MMA issue, 17 weight loader.
 // Hand-offs (mbarriers): enc_ready[s] encoder -> MMA (layer-0 operand written), enc_free[s]
 // epilogue -> encoder (layer-0 MMA of the previous tile has completed: its operand may be
 // overwritten), a_ready[s] epilogue -> MMA (next hidden operand written), d_ready[s] MMA ->
 // epilogue (tcgen05.commit: accumulators complete), w_full[k] loader -> MMA (bulk copy landed),
 // w_empty[k] slot-1 epilogue -> loader (the layer's MMAs of BOTH tiles have completed: the tensor
-// pipe runs in order, so tile 1's completion covers tile 0).  The only tcgen05.commit per
+// pipe runs in order, so tile 1's completion covers tile 0), o_free[s] epilogue -> MMA (the output
+// accumulators of the previous tile have been read: layer 0 of the next tile overwrites them, and
+// with the encoder running ahead nothing else orders the two).  The only tcgen05.commit per
 // layer-tile is d_ready: a commit stalls the issuing thread for ~200 cycles.
 __global__ void __launch_bounds__(FN_THREADS, 1)
 freqnet_forward_kernel(const uint8_t* __restrict__ packed, const float* __restrict__ samples, int stride,
@@ -204,6 +218,7 @@ freqnet_forward_kernel(const uint8_t* __restrict__ packed, const float* __restri
     uint64_t* d_ready = a_ready + 2;
     uint64_t* enc_ready = d_ready + 2;
     uint64_t* enc_free = enc_ready + 2;
+    uint64_t* o_free = enc_free + 2;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + FnSmem::TMEM_SLOT);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
@@ -213,10 +228,11 @@ freqnet_forward_kernel(const uint8_t* __restrict__ packed, const float* __restri
             tc::mbar_init(w_empty + i, 1);
         }
         for (int i = 0; i < 2; i++) {
-            tc::mbar_init(a_ready + i, NET_TILE);
+            tc::mbar_init(a_ready + i, FN_EPI_WARPS * 32);
             tc::mbar_init(d_ready + i, 1);
             tc::mbar_init(enc_ready + i, NET_TILE);
             tc::mbar_init(enc_free + i, 1);
+            tc::mbar_init(o_free + i, NET_TILE);
         }
         tc::fence_mbar_init();
     }
@@ -234,13 +250,14 @@ freqnet_forward_kernel(const uint8_t* __restrict__ packed, const float* __restri
     const long long n_tiles = (n + NET_TILE - 1) / NET_TILE;
     const long long n_pairs = (n_tiles + 1) / 2;
 
-    if (warp < 8) {
-        // ------------------------------------------------ epilogue group of tile slot s
-        const int s = warp >> 2, wk = warp & 3;
+    if (warp < FN_WARP_ENC) {
+        // ------------------------------------------------ epilogue group of tile slot s: warp & 3 = TMEM
+        // lane quarter, half = which 64 of the 128 accumulator columns this warp converts
+        const int s = warp / FN_EPI_WARPS, wk = warp & 3, half = FN_EPI_WARPS == 8 ? (warp >> 2) & 1 : 0;
         const uint32_t t_d = tmem_base + (uint32_t)(s * 256 + FN_COL_D) + ((uint32_t)(wk * 32) << 16);
         const uint32_t t_a = t_d + FN_COL_AH;
         const int row_in_tile = wk * 32 + lane;
-        const bool leader = wk == 0 && lane == 0;
+        const bool leader = wk == 0 && half == 0 && lane == 0;
         uint32_t d_par = 0, cnt = 0;
         int tr = 0;
         for (long long pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
@@ -254,7 +271,7 @@ freqnet_forward_kernel(const uint8_t* __restrict__ packed, const float* __restri
                     if (s == 1) tc::mbar_arrive(w_empty + cnt % FN_RING);
                 }
                 tc::fence_after_thread_sync();
-                fn_hidden_epilogue(t_d, t_a);
+                fn_hidden_epilogue(t_d, t_a, half * (FN_EPI_COLS / 32));
                 tc::tmem_st_wait();
                 tc::fence_before_thread_sync();
                 tc::mbar_arrive(a_ready + s);
@@ -265,37 +282,47 @@ freqnet_forward_kernel(const uint8_t* __restrict__ packed, const float* __restri
             if (leader && s == 1) tc::mbar_arrive(w_empty + cnt % FN_RING);
             cnt++;
             tc::fence_after_thread_sync();
-            uint32_t r[16];
-            output_row_load(t_d, r);
-            tc::fence_before_thread_sync();
-            if (row < n) output_row_store(r, out_activation, row, out16, radiance4);
+            if (half == 0) {                                      // 16 output columns: one warp per lane quarter
+                uint32_t r[16];
+                output_row_load(t_d, r);
+                tc::fence_before_thread_sync();
+                tc::mbar_arrive(o_free + s);                      // the next tile's layer 0 may overwrite D
+                if (row < n) output_row_store(r, out_activation, row, out16, radiance4);
+            }
         }
-    } else if (warp < 16) {
-        // ------------------------------------------------ encoder group of tile slot s
-        const int s = (warp - 8) >> 2, wk = warp & 3;
-        const uint32_t t_e = tmem_base + (uint32_t)(s * 256 + FN_COL_AE) + ((uint32_t)(wk * 32) << 16);
+    } else if (warp < FN_WARP_MMA) {
+        // ------------------------------------------------ encoders: four warps write the layer-0 operand
+        // of slot 0, then of slot 1 (one tile pair needs them for ~1/4 of its 9-layer period)
+        const int wk = warp & 3;
         const int row_in_tile = wk * 32 + lane;
+        const int s_begin = FN_ENC_WARPS == 8 ? (warp - FN_WARP_ENC) >> 2 : 0;
+        const int s_end = FN_ENC_WARPS == 8 ? s_begin + 1 : 2;
         uint32_t f_par = 0;
         bool first = true;
         for (long long pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
-            const long long row = (pair * 2 + s) * NET_TILE + row_in_tile;
-            const bool valid = row < n;
-            if (!first) {
-                tc::mbar_wait(enc_free + s, f_par);
-                f_par ^= 1;
-                tc::fence_after_thread_sync();
+#pragma unroll 1
+            for (int s = s_begin; s < s_end; s++) {
+                const uint32_t t_e = tmem_base + (uint32_t)(s * 256 + FN_COL_AE) + ((uint32_t)(wk * 32) << 16);
+                const long long row = (pair * 2 + s) * NET_TILE + row_in_tile;
+                const bool valid = row < n;
+                if (!first) {
+                    tc::mbar_wait(enc_free + s, f_par);
+                    tc::fence_after_thread_sync();
+                }
+                TmemRowSink sink{t_e};
+                frequency_row(samples + (valid ? row : 0) * stride, valid, sink);
+                tc::tmem_st_wait();
+                tc::fence_before_thread_sync();
+                tc::mbar_arrive(enc_ready + s);
             }
+            if (!first) f_par ^= 1;
             first = false;
-            TmemRowSink sink{t_e};
-            frequency_row(samples + (valid ? row : 0) * stride, valid, sink);
-            tc::tmem_st_wait();
-            tc::fence_before_thread_sync();
-            tc::mbar_arrive(enc_ready + s);
         }
-    } else if (warp == 16) {
+    } else if (warp == FN_WARP_MMA) {
         // ------------------------------------------------ MMA issue
         if (lane == 0) {
-            uint32_t cnt = 0, a_par0 = 0, a_par1 = 0, e_par = 0;
+            uint32_t cnt = 0, a_par0 = 0, a_par1 = 0, e_par = 0, o_par = 0;
+            bool first_pair = true;
             int tr = 0;
             const uint32_t ring = tc::smem_u32(smem + FnSmem::RING);
             for (long long pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
@@ -311,6 +338,8 @@ freqnet_forward_kernel(const uint8_t* __restrict__ packed, const float* __restri
                     for (int s = 0; s < 2; s++) {
                         if (l == 0) {
                             tc::mbar_wait(enc_ready + s, e_par);
+                            // the previous tile's output accumulators (D columns 0-15) have been read
+                            if (!first_pair) tc::mbar_wait(o_free + s, o_par);
                         } else {
                             tc::mbar_wait(a_ready + s, s ? a_par1 : a_par0);
                             if (s) a_par1 ^= 1; else a_par0 ^= 1;
@@ -327,7 +356,11 @@ freqnet_forward_kernel(const uint8_t* __restrict__ packed, const float* __restri
                         tc::mma_commit(d_ready + s);
                         fn_mark(2, tr);                       // per (l, s): MMAs issued + committed
                     }
-                    if (l == 0) e_par ^= 1;
+                    if (l == 0) {
+                        e_par ^= 1;
+                        if (!first_pair) o_par ^= 1;
+                        first_pair = false;
+                    }
                 }
             }
         }
