@@ -139,12 +139,18 @@ typedef struct rtxnerf_hits {
     long long capacity;   /* hit slots available in the arrays above */
 } rtxnerf_hits;
 
-/* Bytes of device scratch rtxnerf_ray_march_csr needs for n_rays. */
+/* Bytes of device scratch rtxnerf_ray_march_csr needs for n_rays (any max_hits). */
 size_t rtxnerf_ray_march_workspace_bytes(long long n_rays);
+/* Bytes of scratch that also let a march with this max_hits (33..1024) run as ONE traversal:
+ * the base size plus a staging slab for the hit records of the resident CTAs (independent of
+ * n_rays beyond 148 x 8 x 128 rays).  For other max_hits it equals the base size. */
+size_t rtxnerf_ray_march_workspace_bytes_for(long long n_rays, int max_hits);
 
 /* All on `stream`.  max_hits <= 32: ONE kernel (march once, hits parked in shared memory,
  * decoupled look-back for the CSR base, coalesced copy-out) after a memset of the status
- * words; larger caps: count -> scan -> fill.  max_hits caps hits per ray (H_max).  Hits
+ * words.  33..1024 with a workspace of ..._bytes_for(n_rays, max_hits): the same kernel as a
+ * persistent grid, hits parked in the workspace.  Otherwise count -> scan -> fill (every ray
+ * walked twice).  max_hits caps hits per ray (H_max).  Hits
  * beyond `capacity` are dropped and *total_hits still reports the true total, so the
  * caller can detect overflow; rays are never split. */
 int rtxnerf_ray_march_csr(const rtxnerf_grid* grid, const rtxnerf_camera* cam,

@@ -74,6 +74,7 @@ SIGNATURES = {
     "rtxnerf_write_ppm": (c_int, [C.c_char_p, c_void_p, c_int, c_int]),
     "rtxnerf_ray_march_dense": (c_int, [C.POINTER(Params), c_void_p]),
     "rtxnerf_ray_march_workspace_bytes": (c_size_t, [c_ll]),
+    "rtxnerf_ray_march_workspace_bytes_for": (c_size_t, [c_ll, c_int]),
     "rtxnerf_ray_march_csr": (c_int, [c_void_p, C.POINTER(Camera), c_ll, c_ll, c_int, C.POINTER(Hits),
                                       c_void_p, c_size_t, c_void_p]),
     "rtxnerf_launch_sampler": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,

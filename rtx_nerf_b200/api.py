@@ -274,6 +274,9 @@ def ray_march_csr(grid, look_at_dev, focal_length, aspect_ratio, width, height, 
         raise ValueError("HitBuffers too small for %d rays" % n_rays)
     cam = _lib.Camera(_p(look_at_dev), float(focal_length), float(aspect_ratio), int(width), int(height))
     st = hits.c_struct()
+    need = _lib.load().rtxnerf_ray_march_workspace_bytes_for(int(n_rays), int(max_hits))
+    if hits.workspace.numel() < need:      # first march with a cap above 32: room for the staged single pass
+        hits.workspace = torch.empty(need, dtype=torch.uint8, device=hits.workspace.device)
     _lib.check(_lib.load().rtxnerf_ray_march_csr(grid._h, C.byref(cam), int(ray_begin), int(n_rays), int(max_hits),
                                                  C.byref(st), _p(hits.workspace), hits.workspace.numel(),
                                                  _stream_ptr(stream)), "ray_march_csr")

@@ -467,17 +467,23 @@ __device__ __forceinline__ void st_status(unsigned long long* p, unsigned long l
     asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 
+// STAGED = false: hits parked in shared memory, one tile per CTA (cap <= ONEPASS_MAX_CAP).
+// STAGED = true (ONEPASS_MAX_CAP < cap <= STAGED_MAX_CAP): the same kernel with the hit records
+// parked in a per-CTA slab of the workspace in HBM/L2 and a persistent grid that keeps taking
+// tiles, so the slabs stay a few hundred MB whatever the ray count; still ONE traversal per ray
+// (count -> scan -> fill walks every ray twice).
+template <bool STAGED>
 __global__ void __launch_bounds__(MARCH_BLOCK)
 march_onepass_kernel(const uint32_t* __restrict__ bits, int G, CamArgs cam, long long ray_begin, long long n_rays,
                      int cap, int* __restrict__ num_hits, float* __restrict__ view_dirs,
                      float* __restrict__ ray_origins, int* __restrict__ indices, FillOut out,
                      unsigned long long* __restrict__ status, unsigned long long* __restrict__ ticket,
-                     long long* __restrict__ total_hits, int n_tiles)
+                     long long* __restrict__ total_hits, int n_tiles, uint32_t* __restrict__ gstage)
 {
     extern __shared__ __align__(16) uint32_t dyn[];
-    const int row = 6 * cap + 1;
-    uint32_t* rec = dyn;                                        // [MARCH_BLOCK][row]
-    float* pts = reinterpret_cast<float*>(dyn + MARCH_BLOCK * row);   // [2][MARCH_BLOCK*3]
+    const int row = STAGED ? 6 * cap : 6 * cap + 1;
+    uint32_t* rec = STAGED ? gstage + (size_t)blockIdx.x * MARCH_BLOCK * row : dyn;   // [MARCH_BLOCK][row]
+    float* pts = reinterpret_cast<float*>(dyn + (STAGED ? 0 : MARCH_BLOCK * row));    // [2][MARCH_BLOCK*3]
     float* dirs = pts + 2 * MARCH_BLOCK * 3;                    // [MARCH_BLOCK][3]
     int* excl = reinterpret_cast<int*>(dirs + MARCH_BLOCK * 3); // [MARCH_BLOCK + 1]
     uint8_t* owner = reinterpret_cast<uint8_t*>(excl + MARCH_BLOCK + 4);   // [MARCH_BLOCK * cap]: slot -> ray
@@ -486,6 +492,8 @@ march_onepass_kernel(const uint32_t* __restrict__ bits, int G, CamArgs cam, long
     __shared__ long long base_s;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
+    __shared__ float origin_s[3];
+  for (;;) {                                                    // STAGED: until the tickets run out
     if (tid == 0) tile_s = (int)atomicAdd(ticket, 1ull);
     __syncthreads();
     const int tile = tile_s;
@@ -569,7 +577,6 @@ march_onepass_kernel(const uint32_t* __restrict__ bits, int G, CamArgs cam, long
     if (lr < n_rays) indices[lr] = (int)(base + excl[tid]);
     // the origin is the same for every ray of a view (optixPrograms.cu:75-78); thread 0 of a
     // tile always holds a ray
-    __shared__ float origin_s[3];
     if (tid == 0) { origin_s[0] = ox0; origin_s[1] = oy0; origin_s[2] = oz0; }
     __syncthreads();
     const float o0x = origin_s[0], o0y = origin_s[1], o0z = origin_s[2];
@@ -614,12 +621,28 @@ march_onepass_kernel(const uint32_t* __restrict__ bits, int G, CamArgs cam, long
         }
         __syncthreads();
     }
+    if (!STAGED) return;
+    __syncthreads();                                            // tile_s, excl, owner, the slab: free again
+  }
 }
 
-static size_t onepass_smem_bytes(int cap)
+static size_t onepass_smem_bytes(int cap, bool staged = false)
 {
-    return sizeof(uint32_t) * ((size_t)MARCH_BLOCK * (6 * cap + 1) + 2 * MARCH_BLOCK * 3 + MARCH_BLOCK * 3 +
-                               MARCH_BLOCK + 4) + (size_t)MARCH_BLOCK * cap;
+    return sizeof(uint32_t) * ((staged ? 0 : (size_t)MARCH_BLOCK * (6 * cap + 1)) + 2 * MARCH_BLOCK * 3 +
+                               MARCH_BLOCK * 3 + MARCH_BLOCK + 4) + (size_t)MARCH_BLOCK * cap;
+}
+
+// staged single-pass march: persistent grid and its slab size
+#define STAGED_MAX_CAP 1024                      // slot -> ray owner table: MARCH_BLOCK * cap bytes of shared memory
+#define STAGED_CTAS_PER_SM 8
+static long long staged_grid(long long nb)
+{
+    const long long g = (long long)RTX_NUM_SMS * STAGED_CTAS_PER_SM;
+    return nb < g ? nb : g;
+}
+static size_t staged_slab_bytes(long long nb, int cap)
+{
+    return (size_t)staged_grid(nb) * MARCH_BLOCK * 6 * (size_t)cap * sizeof(uint32_t);
 }
 
 // Dense layout of the reference (slot = ray*arr + j, optixPrograms.cu:184), one pass.
@@ -743,6 +766,16 @@ extern "C" size_t rtxnerf_ray_march_workspace_bytes(long long n_rays)
            (size_t)nb * sizeof(unsigned long long) + sizeof(unsigned long long) + 256;
 }
 
+static size_t march_base_workspace(long long n_rays) { return (rtxnerf_ray_march_workspace_bytes(n_rays) + 255) & ~(size_t)255; }
+
+extern "C" size_t rtxnerf_ray_march_workspace_bytes_for(long long n_rays, int max_hits)
+{
+    long long nb = (n_rays + MARCH_BLOCK - 1) / MARCH_BLOCK;
+    if (nb < 1) nb = 1;
+    if (max_hits <= ONEPASS_MAX_CAP || max_hits > STAGED_MAX_CAP) return rtxnerf_ray_march_workspace_bytes(n_rays);
+    return march_base_workspace(n_rays) + staged_slab_bytes(nb, max_hits);
+}
+
 extern "C" int rtxnerf_ray_march_csr(const rtxnerf_grid* grid, const rtxnerf_camera* cam, long long ray_begin,
                                      long long n_rays, int max_hits, const rtxnerf_hits* hits, void* workspace,
                                      size_t workspace_bytes, void* stream)
@@ -777,14 +810,34 @@ extern "C" int rtxnerf_ray_march_csr(const rtxnerf_grid* grid, const rtxnerf_cam
         const size_t smem = onepass_smem_bytes(max_hits);
         static size_t smem_set = 0;
         if (smem > smem_set) {
-            RTX_CUDA_TRY(cudaFuncSetAttribute(march_onepass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+            RTX_CUDA_TRY(cudaFuncSetAttribute(march_onepass_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                               (int)onepass_smem_bytes(ONEPASS_MAX_CAP)));
             smem_set = onepass_smem_bytes(ONEPASS_MAX_CAP);
         }
         RTX_CUDA_TRY(cudaMemsetAsync(status, 0, ((size_t)nb + 1) * sizeof(unsigned long long), s));
-        march_onepass_kernel<<<(unsigned)nb, MARCH_BLOCK, smem, s>>>(
+        march_onepass_kernel<false><<<(unsigned)nb, MARCH_BLOCK, smem, s>>>(
             grid->d_bits, grid->G, c, ray_begin, n_rays, max_hits, hits->num_hits, hits->view_dirs,
-            hits->ray_origins, hits->indices, fo, status, ticket, hits->total_hits, (int)nb);
+            hits->ray_origins, hits->indices, fo, status, ticket, hits->total_hits, (int)nb, nullptr);
+        return rtx_launch_status();
+    }
+    if (max_hits <= STAGED_MAX_CAP && !two_pass && max_hits > ONEPASS_MAX_CAP &&
+        workspace_bytes >= rtxnerf_ray_march_workspace_bytes_for(n_rays, max_hits)) {
+        // one traversal, hit records staged in the workspace (the caller sized it with ..._bytes_for)
+        unsigned long long* status = reinterpret_cast<unsigned long long*>(
+            reinterpret_cast<char*>(block_sums) + (((size_t)nb * sizeof(int) + 7) & ~(size_t)7));
+        unsigned long long* ticket = status + nb;
+        uint32_t* gstage = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(workspace) + march_base_workspace(n_rays));
+        const size_t smem = onepass_smem_bytes(max_hits, true);
+        static size_t smem_set_staged = 0;
+        if (smem > smem_set_staged) {
+            RTX_CUDA_TRY(cudaFuncSetAttribute(march_onepass_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              (int)onepass_smem_bytes(STAGED_MAX_CAP, true)));
+            smem_set_staged = onepass_smem_bytes(STAGED_MAX_CAP, true);
+        }
+        RTX_CUDA_TRY(cudaMemsetAsync(status, 0, ((size_t)nb + 1) * sizeof(unsigned long long), s));
+        march_onepass_kernel<true><<<(unsigned)staged_grid(nb), MARCH_BLOCK, smem, s>>>(
+            grid->d_bits, grid->G, c, ray_begin, n_rays, max_hits, hits->num_hits, hits->view_dirs,
+            hits->ray_origins, hits->indices, fo, status, ticket, hits->total_hits, (int)nb, gstage);
         return rtx_launch_status();
     }
     march_count_kernel<<<(unsigned)nb, MARCH_BLOCK, 0, s>>>(grid->d_bits, grid->G, c, ray_begin, n_rays, max_hits,

@@ -146,3 +146,40 @@ def test_frequency_network_full_sample_buffer(cuda_api, orc):
     _, want = orc.mlp_forward(w, 112, 128, 8, 1, enc)
     np.testing.assert_allclose(rad[pick].cpu().numpy(), want, rtol=0, atol=4e-3)
     assert bool(torch.isfinite(rad).all())
+
+
+@pytest.mark.parametrize("G,kind,W,H,cap", [(64, "bernoulli", 320, 200, 64), (32, "dense", 96, 64, 96),
+                                             (128, "lego", 400, 300, 40), (512, "bernoulli", 1920, 1080, 64)])
+def test_staged_single_pass_march_equals_two_pass(cuda_api, G, kind, W, H, cap):
+    """max_hits in 33..1024: with a workspace of rtxnerf_ray_march_workspace_bytes_for the march is ONE
+    traversal (hit records staged in the workspace, persistent grid); with the base-size workspace the C ABI
+    falls back to count -> scan -> fill.  Every output array must be identical."""
+    import ctypes as C
+    import torch
+    from rtx_nerf_b200 import _lib
+    api = cuda_api
+    occ = {"bernoulli": lambda: synth.occupancy_bernoulli(G, 0.10 if G == 512 else 0.3, seed=5),
+           "dense": lambda: synth.occupancy_bernoulli(G, 1.0, seed=1),
+           "lego": lambda: synth.occupancy_lego(G, seed=0)}[kind]()
+    grid = api.OccupancyGrid.from_occupancy(occ, G)
+    pose, focal = synth.poses(3, seed=13)[2], synth.focal_length()
+    a = _march(api, grid, pose, focal, W, H, cap)                       # api sizes the workspace: staged path
+    lib = _lib.load()
+    R = W * H
+    assert a.workspace.numel() >= lib.rtxnerf_ray_march_workspace_bytes_for(R, cap) > \
+        lib.rtxnerf_ray_march_workspace_bytes(R)
+    total = _csr_properties(a, cap)
+    b = api.HitBuffers(R, R * cap)
+    base = lib.rtxnerf_ray_march_workspace_bytes(R)
+    pose_dev = _t(pose.reshape(-1))
+    cam = _lib.Camera(pose_dev.data_ptr(), float(focal), float(W / H), W, H)
+    st = b.c_struct()
+    rc = lib.rtxnerf_ray_march_csr(grid._h, C.byref(cam), 0, R, cap, C.byref(st), b.workspace.data_ptr(), base, None)
+    assert rc == 0
+    torch.cuda.synchronize()
+    assert int(b.total_hits.item()) == total
+    assert torch.equal(a.num_hits, b.num_hits) and torch.equal(a.indices, b.indices)
+    assert torch.equal(a.view_dirs, b.view_dirs)
+    for k in ("t_start", "t_end", "start_points", "end_points", "hit_cells"):
+        assert torch.equal(getattr(a, k)[:total], getattr(b, k)[:total]), k
+    grid.destroy()
