@@ -83,6 +83,11 @@ def main():
          lambda: chk(ref.ref_cuda_volrender_backward(vp(lg), vp(rad), vp(t_ref), vp(nh), vp(idx), B, S, vp(g_ref))),
          lambda: api.launch_volrender_backward_cuda(None, lg, rad, t_new, nh, idx, B, S, g_new)),
     )
+    import time
+    t0 = time.perf_counter()
+    while time.perf_counter() - t0 < 1.5:      # clock spin-up: a B200 out of idle needs ~1 s of load
+        pairs[0][3]()
+        torch.cuda.synchronize()
     print("rays %d, %d hits/ray x S=%d -> %d samples; identical device inputs" % (B, Hr, S, N))
     for name, byts, f_ref, f_new in pairs:
         with torch.cuda.stream(torch.cuda.default_stream()):

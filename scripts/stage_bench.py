@@ -41,7 +41,9 @@ def main():
     r = pipeline.ViewRenderer(grid, a.W, a.H, synth.focal_length(), a.W / a.H, a.S, a.hmax,
                               pipeline.CellRadiance(synth.cell_radiance(a.G)))
     pose = synth.poses(4, seed=1)[0]
-    r.render_host(pose)
+    t0 = time.perf_counter()
+    while time.perf_counter() - t0 < 1.5:      # clock spin-up: a B200 out of idle needs ~1 s of load
+        r.render_host(pose)
     Hh = r.total_hits()
     R, N = r.R, Hh * a.S
     nh = r.hits.num_hits.cpu().numpy()

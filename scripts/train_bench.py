@@ -39,6 +39,15 @@ def main():
                                                       tr.R, tr.S, tr.radiance_grad),
            net_bwd, tr.optimizer_step]
     tot = np.zeros(len(fns))
+    import time
+    t0 = time.perf_counter()
+    v.pose_dev.copy_(torch.as_tensor(poses[0].reshape(16)).cuda())
+    v.ray_begin = 0
+    while time.perf_counter() - t0 < 1.5:      # clock spin-up: a B200 out of idle needs ~1 s of load
+        tr.target.copy_(target)
+        for f in fns:
+            f()
+        torch.cuda.synchronize()
     for k in range(a.steps + 2):
         v.pose_dev.copy_(torch.as_tensor(poses[k].reshape(16)).cuda())
         v.ray_begin = (k * 7919) % (W * H - a.rays)
