@@ -308,6 +308,121 @@ __device__ __forceinline__ int march_ray(const uint32_t* __restrict__ bits, int 
     return nh;
 }
 
+// The same march as a FLAT loop: one sweep step per iteration for every lane that is inside a
+// segment, and the relaunch work (three exact cell locates + six exact divisions, ~150
+// instructions) batched: lanes that have just emitted a hit wait until the relaunch block runs
+// for the warp, which happens when every live lane wants it, when at least ENTER_MIN lanes do,
+// or every ENTER_EVERY iterations.  march_ray lets each lane run to its next hit and the warp
+// then waits for the slowest lane (with scattered occupancy ~38 steps for a mean of ~10); here
+// a lane idles for at most ENTER_EVERY - 1 steps.  The operations of a ray and their order are
+// unchanged, so the records are the same bits.  All lanes of `mask` must call it together.
+// Measured (round h): config 5 (512^3 Bernoulli 0.10, H_max 64) staged march 18.8 -> 13.5 ms;
+// config 2 (lego, 2.3 steps per hit, H_max 16) 0.33 -> 0.41 ms, so the shared-memory one-pass
+// path keeps march_ray and the staged path (max_hits > 32) takes this one.
+__constant__ int c_enter_every = 4, c_enter_min = 12;
+
+template <bool WANT_START, class Emit>
+__device__ __forceinline__ int march_ray_flat(const uint32_t* __restrict__ bits, int G, float ox, float oy,
+                                              float oz, float dx, float dy, float dz, int cap, bool valid,
+                                              unsigned mask, Emit emit)
+{
+    const float L = 2.0f / (float)G;
+    const float half_g = 0.5f * (float)G;
+    const float rx = __frcp_rn(dx), ry = __frcp_rn(dy), rz = __frcp_rn(dz);
+    const bool dfast = dir_fast(dx) & dir_fast(dy) & dir_fast(dz);
+    const float slx = dx < 0.0f ? -L : L, sly = dy < 0.0f ? -L : L, slz = dz < 0.0f ? -L : L;
+    const int six = dx < 0.0f ? -1 : 1, siy = dy < 0.0f ? -1 : 1, siz = dz < 0.0f ? -1 : 1;
+    const int enter_every = c_enter_every, enter_min = c_enter_min;
+    AxisState X, Y, Z;
+    X.near_t = X.far_t = X.far_plane = 0.f; X.i = 0;
+    Y = X; Z = X;
+    int nh = 0, since = 0;
+    bool done = !valid || cap <= 0, need_enter = true;
+    for (;;) {
+        const unsigned live = __ballot_sync(mask, !done);
+        if (!live) break;
+        const unsigned want = __ballot_sync(mask, need_enter && !done);
+        if (want && (want == live || __popc(want) >= enter_min || since >= enter_every)) {
+            since = 0;
+            if (need_enter && !done) {
+                if (dfast & origin_fast(ox) & origin_fast(oy) & origin_fast(oz)) {
+                    axis_enter(X, ox, dx, rx, G, L, half_g);
+                    axis_enter(Y, oy, dy, ry, G, L, half_g);
+                    axis_enter(Z, oz, dz, rz, G, L, half_g);
+                    need_enter = false;
+                } else {      // uncertified operands: the whole segment through the generic code
+                    const bool found = march_segment_generic<WANT_START>(bits, G, L, half_g, ox, oy, oz, dx, dy, dz,
+                                                                         nh, emit);
+                    if (!found || nh >= cap) done = true;
+                }
+            }
+        } else {
+            since++;
+        }
+        if (!need_enter && !done) {
+            // one step of march_segment
+            const float txx = fmaxf(X.near_t, X.far_t), txy = fmaxf(Y.near_t, Y.far_t), txz = fmaxf(Z.near_t, Z.far_t);
+            const unsigned p = ((unsigned)X.i * (unsigned)G + (unsigned)Y.i) * (unsigned)G + (unsigned)Z.i;
+            const bool occ = (__ldg(bits + (p >> 5)) >> (p & 31u)) & 1u;
+            bool accepted = false;
+            if (occ) {
+                const float tmin = fmaxf(fmaxf(fmaxf(-INFINITY, fminf(X.near_t, X.far_t)), fminf(Y.near_t, Y.far_t)),
+                                         fminf(Z.near_t, Z.far_t));
+                const float tmax = fminf(fminf(fminf(INFINITY, txx), txy), txz);
+                if (tmax > tmin) {
+                    const float t = (tmin < 0.0f && tmax > CLAMP_EPS) ? 0.0f : tmin;
+                    if (t >= 0.0f && t <= RAY_TMAX) {
+                        HitRecord h;
+                        h.t_start = t;
+                        if (WANT_START) {
+                            h.sx = rn_fma(t, dx, ox);
+                            h.sy = rn_fma(t, dy, oy);
+                            h.sz = rn_fma(t, dz, oz);
+                        }
+                        const float t_e = fminf(fminf(X.far_t, Y.far_t), Z.far_t);
+                        h.t_end = t_e;
+                        h.ex = rn_fma(dx, t_e, ox);
+                        h.ey = rn_fma(dy, t_e, oy);
+                        h.ez = rn_fma(dz, t_e, oz);
+                        h.cell = (int)p;
+                        emit(nh, h);
+                        nh++;
+                        ox = h.ex;
+                        oy = h.ey;
+                        oz = h.ez;
+                        accepted = true;
+                        need_enter = true;
+                        if (nh >= cap) done = true;
+                    }
+                }
+            }
+            if (!accepted) {
+                int ks = -1;
+                float best = INFINITY;
+                if (txx < best) { best = txx; ks = 0; }
+                if (txy < best) { best = txy; ks = 1; }
+                if (txz < best) { best = txz; ks = 2; }
+                if (ks < 0 || best > RAY_TMAX) {
+                    done = true;
+                } else {
+                    const float os = ks == 0 ? ox : (ks == 1 ? oy : oz);
+                    const float ds = ks == 0 ? dx : (ks == 1 ? dy : dz);
+                    const float rs = ks == 0 ? rx : (ks == 1 ? ry : rz);
+                    const float pl = (ks == 0 ? X.far_plane : (ks == 1 ? Y.far_plane : Z.far_plane)) +
+                                     (ks == 0 ? slx : (ks == 1 ? sly : slz));
+                    const float tn = div_exact(rn_sub(pl, os), ds, rs);
+                    int moved;
+                    if (ks == 0) { X.i += six; X.near_t = X.far_t; X.far_t = tn; X.far_plane = pl; moved = X.i; }
+                    else if (ks == 1) { Y.i += siy; Y.near_t = Y.far_t; Y.far_t = tn; Y.far_plane = pl; moved = Y.i; }
+                    else { Z.i += siz; Z.near_t = Z.far_t; Z.far_t = tn; Z.far_plane = pl; moved = Z.i; }
+                    if ((unsigned)moved >= (unsigned)G) done = true;
+                }
+            }
+        }
+    }
+    return nh;
+}
+
 // ------------------------------------------------------------------------------------ kernels
 struct CamArgs {
     const float* look_at;
@@ -472,7 +587,7 @@ __device__ __forceinline__ void st_status(unsigned long long* p, unsigned long l
 // parked in a per-CTA slab of the workspace in HBM/L2 and a persistent grid that keeps taking
 // tiles, so the slabs stay a few hundred MB whatever the ray count; still ONE traversal per ray
 // (count -> scan -> fill walks every ray twice).
-template <bool STAGED>
+template <bool STAGED, bool FLAT>
 __global__ void __launch_bounds__(MARCH_BLOCK)
 march_onepass_kernel(const uint32_t* __restrict__ bits, int G, CamArgs cam, long long ray_begin, long long n_rays,
                      int cap, int* __restrict__ num_hits, float* __restrict__ view_dirs,
@@ -503,7 +618,40 @@ march_onepass_kernel(const uint32_t* __restrict__ bits, int G, CamArgs cam, long
     // ---- 1+2: march, park the hits
     int nh = 0;
     float ox0 = 0.f, oy0 = 0.f, oz0 = 0.f;
-    if (lr < n_rays) {
+    if (FLAT) {
+        const bool valid = lr < n_rays;
+        RayGen r;
+        r.ox = r.oy = r.oz = 0.f;
+        r.dx = r.dy = r.dz = 0.5f;
+        r.theta = r.phi = 0.f;
+        if (valid) {
+            unsigned long long ray = (unsigned long long)(ray_begin + lr);
+            r = raygen(cam.look_at, cam.focal, cam.aspect, cam.width, cam.height, (unsigned)(ray % cam.width),
+                       (unsigned)(ray / cam.width));
+            ox0 = r.ox; oy0 = r.oy; oz0 = r.oz;
+            dirs[3 * tid] = r.dx; dirs[3 * tid + 1] = r.dy; dirs[3 * tid + 2] = r.dz;
+        }
+        uint32_t* my = rec + tid * row;
+        nh = march_ray_flat<false>(bits, G, r.ox, r.oy, r.oz, r.dx, r.dy, r.dz, cap, valid, 0xffffffffu,
+                                   [&](int j, const HitRecord& h) {
+            uint32_t* w = my + 6 * j;
+            w[0] = __float_as_uint(h.t_start);
+            w[1] = __float_as_uint(h.t_end);
+            w[2] = __float_as_uint(h.ex);
+            w[3] = __float_as_uint(h.ey);
+            w[4] = __float_as_uint(h.ez);
+            w[5] = (uint32_t)h.cell;
+        });
+        if (valid) {
+            num_hits[lr] = nh;
+            reinterpret_cast<float2*>(view_dirs)[lr] = make_float2(r.theta, r.phi);
+            if (ray_origins) {
+                ray_origins[3 * lr] = r.ox;
+                ray_origins[3 * lr + 1] = r.oy;
+                ray_origins[3 * lr + 2] = r.oz;
+            }
+        }
+    } else if (lr < n_rays) {
         unsigned long long ray = (unsigned long long)(ray_begin + lr);
         RayGen r = raygen(cam.look_at, cam.focal, cam.aspect, cam.width, cam.height,
                           (unsigned)(ray % cam.width), (unsigned)(ray / cam.width));
@@ -799,9 +947,16 @@ extern "C" int rtxnerf_ray_march_csr(const rtxnerf_grid* grid, const rtxnerf_cam
     CamArgs c{cam->look_at, cam->focal_length, cam->aspect_ratio, cam->width, cam->height};
     FillOut fo{hits->t_start, hits->t_end, hits->start_points, hits->end_points, hits->hit_cells, hits->capacity};
     static int two_pass = -1;   // development knob: RTXNERF_MARCH_TWO_PASS=1 forces count -> scan -> fill
+    static int flat = -1;       // development knob: RTXNERF_MARCH_FLAT=0/1 (+ _ENTER_EVERY, _ENTER_MIN)
     if (two_pass < 0) {
         const char* e = getenv("RTXNERF_MARCH_TWO_PASS");
         two_pass = (e && e[0] == '1') ? 1 : 0;
+        e = getenv("RTXNERF_MARCH_FLAT");
+        flat = e ? (e[0] == '1') : 2;        // 2 = default: flat loop for the staged path only
+        const char* ee = getenv("RTXNERF_MARCH_ENTER_EVERY");
+        const char* em = getenv("RTXNERF_MARCH_ENTER_MIN");
+        if (ee) { int v = atoi(ee); RTX_CUDA_TRY(cudaMemcpyToSymbol(c_enter_every, &v, sizeof(int))); }
+        if (em) { int v = atoi(em); RTX_CUDA_TRY(cudaMemcpyToSymbol(c_enter_min, &v, sizeof(int))); }
     }
     if (max_hits <= ONEPASS_MAX_CAP && !two_pass) {
         unsigned long long* status = reinterpret_cast<unsigned long long*>(
@@ -810,12 +965,17 @@ extern "C" int rtxnerf_ray_march_csr(const rtxnerf_grid* grid, const rtxnerf_cam
         const size_t smem = onepass_smem_bytes(max_hits);
         static size_t smem_set = 0;
         if (smem > smem_set) {
-            RTX_CUDA_TRY(cudaFuncSetAttribute(march_onepass_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+            RTX_CUDA_TRY(cudaFuncSetAttribute(march_onepass_kernel<false, false>,
+                                              cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              (int)onepass_smem_bytes(ONEPASS_MAX_CAP)));
+            RTX_CUDA_TRY(cudaFuncSetAttribute(march_onepass_kernel<false, true>,
+                                              cudaFuncAttributeMaxDynamicSharedMemorySize,
                                               (int)onepass_smem_bytes(ONEPASS_MAX_CAP)));
             smem_set = onepass_smem_bytes(ONEPASS_MAX_CAP);
         }
         RTX_CUDA_TRY(cudaMemsetAsync(status, 0, ((size_t)nb + 1) * sizeof(unsigned long long), s));
-        march_onepass_kernel<false><<<(unsigned)nb, MARCH_BLOCK, smem, s>>>(
+        auto kern = flat == 1 ? march_onepass_kernel<false, true> : march_onepass_kernel<false, false>;
+        kern<<<(unsigned)nb, MARCH_BLOCK, smem, s>>>(
             grid->d_bits, grid->G, c, ray_begin, n_rays, max_hits, hits->num_hits, hits->view_dirs,
             hits->ray_origins, hits->indices, fo, status, ticket, hits->total_hits, (int)nb, nullptr);
         return rtx_launch_status();
@@ -830,12 +990,17 @@ extern "C" int rtxnerf_ray_march_csr(const rtxnerf_grid* grid, const rtxnerf_cam
         const size_t smem = onepass_smem_bytes(max_hits, true);
         static size_t smem_set_staged = 0;
         if (smem > smem_set_staged) {
-            RTX_CUDA_TRY(cudaFuncSetAttribute(march_onepass_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+            RTX_CUDA_TRY(cudaFuncSetAttribute(march_onepass_kernel<true, false>,
+                                              cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              (int)onepass_smem_bytes(STAGED_MAX_CAP, true)));
+            RTX_CUDA_TRY(cudaFuncSetAttribute(march_onepass_kernel<true, true>,
+                                              cudaFuncAttributeMaxDynamicSharedMemorySize,
                                               (int)onepass_smem_bytes(STAGED_MAX_CAP, true)));
             smem_set_staged = onepass_smem_bytes(STAGED_MAX_CAP, true);
         }
         RTX_CUDA_TRY(cudaMemsetAsync(status, 0, ((size_t)nb + 1) * sizeof(unsigned long long), s));
-        march_onepass_kernel<true><<<(unsigned)staged_grid(nb), MARCH_BLOCK, smem, s>>>(
+        auto kern = flat != 0 ? march_onepass_kernel<true, true> : march_onepass_kernel<true, false>;
+        kern<<<(unsigned)staged_grid(nb), MARCH_BLOCK, smem, s>>>(
             grid->d_bits, grid->G, c, ray_begin, n_rays, max_hits, hits->num_hits, hits->view_dirs,
             hits->ray_origins, hits->indices, fo, status, ticket, hits->total_hits, (int)nb, gstage);
         return rtx_launch_status();
