@@ -343,6 +343,48 @@ int rtxnerf_adam_step(long long n, float* d_master, uint16_t* d_params, float* d
                       float* d_m2, float grad_scale, float lr, float beta1, float beta2, float eps,
                       int step, void* stream);
 
+/* ------------------------------------------------------------------------------------
+ * Seeded ray shuffle + batch assembly — replaces the front end of the reference's training
+ * loop (main.cu:612-676): std::random_shuffle of the host ray payloads (:615), the host loops
+ * collecting num_hits / gt pixel / view_dir of a batch (:622-626), their H2D copies (:627-629),
+ * thrust::reduce + exclusive_scan (:631-637) and the host gather + H2D of start/end points
+ * (:649-676).  The march results of all views stay on the device (the "ray store", filled by
+ * rtxnerf_ray_march_csr view after view); a batch is a slice of a stateless seeded permutation.
+ * ---------------------------------------------------------------------------------- */
+typedef struct rtxnerf_ray_store {
+    long long n_rays;             /* n_views * rays_per_view */
+    long long rays_per_view;
+    const long long* view_base;   /* device [n_views]: first hit slot of each view in the record arrays */
+    const int* num_hits;          /* [n_rays] */
+    const int* indices;           /* [n_rays]  CSR index LOCAL to the ray's view (as the march wrote it) */
+    const float* view_dirs;       /* [n_rays][2] */
+    const float* start_points;    /* [total hits][3] */
+    const float* end_points;      /* [total hits][3] */
+    const float* t_start;         /* [total hits] (may be NULL) */
+    const float* t_end;           /* [total hits] (may be NULL) */
+    const float* pixels_gt;       /* [n_rays][3] ground-truth colours (may be NULL) */
+} rtxnerf_ray_store;
+
+/* d_out[k] = ray id at position first + k of the shuffled order of n rays, 0 <= k < count.
+ * The permutation is a keyed bijection (4-round Feistel network, cycle-walked) over groups of
+ * `group` consecutive rays (n % group == 0): group = 1 shuffles single rays as the reference
+ * does, group = 32 keeps 32 adjacent pixels together.  A new epoch = a new seed. */
+int rtxnerf_ray_permutation(long long n, unsigned long long seed, int group, long long first,
+                            long long count, long long* d_out, void* stream);
+
+size_t rtxnerf_batch_workspace_bytes(long long batch_rays);
+
+/* Batch = positions [first, first + batch_rays) of the shuffled order (whole batches only,
+ * first + batch_rays <= n_rays; the reference slices past the end, Q6).  Writes into `batch`:
+ * num_hits, indices (exclusive scan), view_dirs, start_points, end_points, t_start / t_end
+ * (when present on both sides), *total_hits; ray_origins and hit_cells are not touched.  Hits
+ * beyond batch->capacity are dropped (total still true).  d_gt_pixels [batch_rays][3] and
+ * d_ray_ids [batch_rays] are optional.  Three kernels on `stream`. */
+int rtxnerf_batch_assemble(const rtxnerf_ray_store* store, unsigned long long seed, int group,
+                           long long first, long long batch_rays, const rtxnerf_hits* batch,
+                           float* d_gt_pixels, long long* d_ray_ids, void* workspace,
+                           size_t workspace_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

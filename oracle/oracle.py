@@ -348,6 +348,98 @@ def adam_step(master, grads, m1, m2, grad_scale, lr, beta1, beta2, eps, step):
 
 
 # --------------------------------------------------------------------------- the reference itself, on the host
+# ---------------------------------------------------------------------------------------
+# Ray shuffle + batch assembly.  Follows the reference's training-loop front end,
+# main.cu:612-676: shuffle the rays (:615), slice a batch (:621), collect num_hits / gt pixel /
+# view_dir (:622-626), exclusive scan (:631-637), gather start/end points in batch order
+# (:649-660).  std::random_shuffle's generator is implementation-defined, so the permutation
+# itself is this repo's definition (4-round Feistel, cycle-walked); everything after it is the
+# reference's gather, restated with plain loops over rays.
+# ---------------------------------------------------------------------------------------
+_M64 = (1 << 64) - 1
+
+
+def _splitmix64_stream(seed, count):
+    s, out = seed & _M64, []
+    for _ in range(count):
+        s = (s + 0x9E3779B97F4A7C15) & _M64
+        z = s
+        z = ((z ^ (z >> 30)) * 0xBF58476D1CE4E5B9) & _M64
+        z = ((z ^ (z >> 27)) * 0x94D049BB133111EB) & _M64
+        out.append(z ^ (z >> 31))
+    return out
+
+
+def _mix32(h):
+    h = h.astype(np.uint64)
+    h ^= h >> np.uint64(16)
+    h = (h * np.uint64(0x85EBCA6B)) & np.uint64(0xFFFFFFFF)
+    h ^= h >> np.uint64(13)
+    h = (h * np.uint64(0xC2B2AE35)) & np.uint64(0xFFFFFFFF)
+    h ^= h >> np.uint64(16)
+    return h
+
+
+def ray_permutation(n, seed, group=1, first=0, count=None):
+    """Ray ids at positions [first, first+count) of the seeded shuffle of n rays (int64)."""
+    if count is None:
+        count = n - first
+    if n <= 0 or group <= 0 or n % group or first < 0 or count < 0 or first + count > n:
+        raise ValueError("ray_permutation: bad arguments")
+    ng = n // group
+    bits = 2
+    while bits < 64 and (1 << bits) < ng:
+        bits += 1
+    bits += bits & 1
+    hb = np.uint64(bits // 2)
+    mask = np.uint64((1 << (bits // 2)) - 1)
+    keys = [np.uint64(k >> 32) for k in _splitmix64_stream(seed, 4)]
+    pos = np.arange(first, first + count, dtype=np.uint64)
+    x = pos // np.uint64(group)
+    todo = np.ones(count, dtype=bool)
+    while todo.any():
+        xi = x[todo]
+        L, R = (xi >> hb) & mask, xi & mask
+        for k in keys:
+            F = _mix32(R ^ k) & mask
+            L, R = R, L ^ F
+        xi = (L << hb) | R
+        x[todo] = xi
+        todo[todo] = xi >= np.uint64(ng)
+    return (x * np.uint64(group) + pos % np.uint64(group)).astype(np.int64)
+
+
+def batch_assemble(store, seed, group, first, batch_rays, capacity=None):
+    """store: dict(rays_per_view, view_base[n_views] int64, num_hits, indices (view-local), view_dirs [n][2],
+    start_points / end_points [H][3], optional t_start / t_end [H], pixels_gt [n][3]).  Returns a dict
+    with the batch CSR (main.cu:622-660) in shuffled order."""
+    n = len(store["num_hits"])
+    ids = ray_permutation(n, seed, group, first, batch_rays)
+    nh = store["num_hits"][ids].astype(np.int32)
+    ind, total = exclusive_scan(nh)
+    cap = total if capacity is None else min(total, int(capacity))
+    out = dict(ray_ids=ids, num_hits=nh, indices=ind, total_hits=total,
+               view_dirs=store["view_dirs"][ids].astype(np.float32),
+               start_points=np.zeros((cap, 3), np.float32), end_points=np.zeros((cap, 3), np.float32))
+    if store.get("pixels_gt") is not None:
+        out["gt_pixels"] = store["pixels_gt"][ids].astype(np.float32)
+    for name in ("t_start", "t_end"):
+        if store.get(name) is not None:
+            out[name] = np.zeros(cap, np.float32)
+    for k, r in enumerate(ids):                      # the host gather loop of main.cu:651-660
+        src = int(store["view_base"][r // store["rays_per_view"]]) + int(store["indices"][r])
+        for j in range(int(nh[k])):
+            dst = int(ind[k]) + j
+            if dst >= cap:
+                break
+            out["start_points"][dst] = store["start_points"][src + j]
+            out["end_points"][dst] = store["end_points"][src + j]
+            for name in ("t_start", "t_end"):
+                if name in out:
+                    out[name][dst] = store[name][src + j]
+    return out
+
+
 def ref_ray_march(look_at, focal, aspect, W, H, G, aabb, arr_size, rays=None):
     """The reference's own OptiX programs over the emulated runtime (oracle/host_shim/optix.h)."""
     r = ref_host()

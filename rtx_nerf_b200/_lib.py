@@ -51,6 +51,13 @@ class FreqNet(C.Structure):
                 ("n_hidden", c_int), ("out_activation", c_int)]
 
 
+class RayStore(C.Structure):
+    """rtxnerf_ray_store (include/rtxnerf.h)."""
+    _fields_ = [("n_rays", c_ll), ("rays_per_view", c_ll), ("view_base", c_void_p), ("num_hits", c_void_p),
+                ("indices", c_void_p), ("view_dirs", c_void_p), ("start_points", c_void_p),
+                ("end_points", c_void_p), ("t_start", c_void_p), ("t_end", c_void_p), ("pixels_gt", c_void_p)]
+
+
 class Mlp(C.Structure):
     """rtxnerf_mlp (include/rtxnerf.h)."""
     _fields_ = [("weights", c_void_p), ("in_dim", c_int), ("width", c_int), ("n_hidden", c_int),
@@ -106,6 +113,10 @@ SIGNATURES = {
     "rtxnerf_l2_loss": (c_int, [c_void_p, c_void_p, c_ll, c_float, c_void_p, c_void_p, c_void_p, c_void_p]),
     "rtxnerf_adam_step": (c_int, [c_ll, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_float, c_float,
                                   c_float, c_float, c_int, c_void_p]),
+    "rtxnerf_ray_permutation": (c_int, [c_ll, C.c_ulonglong, c_int, c_ll, c_ll, c_void_p, c_void_p]),
+    "rtxnerf_batch_workspace_bytes": (c_size_t, [c_ll]),
+    "rtxnerf_batch_assemble": (c_int, [C.POINTER(RayStore), C.c_ulonglong, c_int, c_ll, c_ll, C.POINTER(Hits),
+                                       c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
 }
 
 _lib = None

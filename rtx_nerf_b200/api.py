@@ -291,6 +291,109 @@ def cell_radiance(hit_cells, total_hits, capacity_hits, samples_per_segment, cel
     _lib.count_launches(1 if capacity_hits > 0 else 0)
 
 
+# ----------------------------------------------------------------------------- ray store / batches
+class RayStore:
+    """March results of ALL training views resident in HBM (replaces the host `ray_payloads` vector of
+    main.cu:509-541): per-ray num_hits / view-local CSR index / view_dir / gt pixel, per-hit entry and
+    exit points, one hit base per view.  Filled view by view with ray_march_csr (`add_view`)."""
+
+    def __init__(self, n_views, rays_per_view, capacity_hits, device="cuda", want_t=False, pixels_gt=None):
+        dev = torch.device(device)
+        self.n_views, self.rays_per_view = int(n_views), int(rays_per_view)
+        self.n_rays = self.n_views * self.rays_per_view
+        self.capacity = int(capacity_hits)
+        self.num_hits = torch.zeros(self.n_rays, dtype=torch.int32, device=dev)
+        self.indices = torch.zeros(self.n_rays, dtype=torch.int32, device=dev)
+        self.view_dirs = torch.zeros((self.n_rays, 2), dtype=torch.float32, device=dev)
+        self.start_points = torch.empty((self.capacity, 3), dtype=torch.float32, device=dev)
+        self.end_points = torch.empty((self.capacity, 3), dtype=torch.float32, device=dev)
+        self.t_start = torch.empty(self.capacity, dtype=torch.float32, device=dev) if want_t else None
+        self.t_end = torch.empty(self.capacity, dtype=torch.float32, device=dev) if want_t else None
+        self.pixels_gt = pixels_gt
+        if pixels_gt is not None:
+            _chk_dev(pixels_gt, torch.float32, "pixels_gt")
+            if pixels_gt.numel() != self.n_rays * 3:
+                raise ValueError("pixels_gt must be [n_rays][3]")
+        self.view_base = torch.zeros(self.n_views, dtype=torch.int64, device=dev)
+        self.view_base_host = [0] * self.n_views
+        self.used_hits = 0
+        self.views_filled = 0
+        self._total = torch.zeros(1, dtype=torch.int64, device=dev)
+        self._workspace = torch.empty(_lib.load().rtxnerf_ray_march_workspace_bytes(self.rays_per_view),
+                                      dtype=torch.uint8, device=dev)
+
+    def add_view(self, grid, look_at_dev, focal_length, aspect_ratio, width, height, max_hits):
+        """Marches the next view straight into the store's slices.  Synchronises once (reads the
+        view's hit total to place the next view): dataset preparation, not the per-step path."""
+        if width * height != self.rays_per_view:
+            raise ValueError("view size does not match rays_per_view")
+        v = self.views_filled
+        if v >= self.n_views:
+            raise ValueError("ray store is full")
+        r0, h0 = v * self.rays_per_view, self.used_hits
+        room = self.capacity - h0
+        cam = _lib.Camera(_p(look_at_dev), float(focal_length), float(aspect_ratio), int(width), int(height))
+        sl = lambda t, a: None if t is None else C.c_void_p(t.data_ptr() + a * t.element_size())
+        st = _lib.Hits(sl(self.num_hits, r0), sl(self.indices, r0), sl(self.view_dirs, 2 * r0), None,
+                       sl(self.t_start, h0), sl(self.t_end, h0), sl(self.start_points, 3 * h0),
+                       sl(self.end_points, 3 * h0), None, _p(self._total), room)
+        need = _lib.load().rtxnerf_ray_march_workspace_bytes_for(self.rays_per_view, int(max_hits))
+        if self._workspace.numel() < need:
+            self._workspace = torch.empty(need, dtype=torch.uint8, device=self._workspace.device)
+        _lib.check(_lib.load().rtxnerf_ray_march_csr(grid._h, C.byref(cam), 0, self.rays_per_view, int(max_hits),
+                                                     C.byref(st), _p(self._workspace), self._workspace.numel(),
+                                                     _stream_ptr(None)), "ray_march_csr (ray store)")
+        total = int(self._total.item())
+        if total > room:
+            raise _lib.RtxNerfError("ray store capacity exceeded: view %d needs %d hit slots, %d left" % (v, total, room))
+        self.view_base_host[v] = h0
+        self.view_base[v] = h0
+        self.used_hits = h0 + total
+        self.views_filled = v + 1
+        _lib.count_launches(3)
+        return total
+
+    def c_struct(self):
+        return _lib.RayStore(self.n_rays, self.rays_per_view, _p(self.view_base), _p(self.num_hits), _p(self.indices),
+                             _p(self.view_dirs), _p(self.start_points), _p(self.end_points), _p(self.t_start),
+                             _p(self.t_end), _p(self.pixels_gt))
+
+
+def ray_permutation(n, seed, group=1, first=0, count=None, out=None, stream=None):
+    """Ray ids at positions [first, first+count) of the seeded shuffle (int64, device): the device
+    stand-in for std::random_shuffle(ray_payloads) at main.cu:615."""
+    count = n - first if count is None else count
+    if out is None:
+        out = torch.empty(count, dtype=torch.int64, device="cuda")
+    _chk_dev(out, torch.int64, "out")
+    _lib.check(_lib.load().rtxnerf_ray_permutation(int(n), int(seed), int(group), int(first), int(count), _p(out),
+                                                   _stream_ptr(stream)), "ray_permutation")
+    _lib.count_launches(1 if count > 0 else 0)
+    return out
+
+
+def batch_assemble(store, seed, group, first, batch_rays, hits, gt_pixels=None, ray_ids=None, workspace=None,
+                   stream=None):
+    """One training batch from the ray store: replaces main.cu:621-676 (host slice + collect +
+    H2D + thrust reduce/scan + host gather + H2D).  `hits` is a HitBuffers that receives the batch
+    CSR (num_hits, indices, view_dirs, start/end points, t's, total_hits).  Asynchronous."""
+    if store.views_filled != store.n_views:
+        raise ValueError("ray store holds %d of %d views" % (store.views_filled, store.n_views))
+    if batch_rays > hits.n_rays:
+        raise ValueError("HitBuffers too small for %d rays" % batch_rays)
+    lib = _lib.load()
+    need = lib.rtxnerf_batch_workspace_bytes(int(batch_rays))
+    if workspace is None:
+        workspace = hits.workspace
+        if workspace.numel() < need:
+            workspace = hits.workspace = torch.empty(need, dtype=torch.uint8, device=hits.num_hits.device)
+    st, hs = store.c_struct(), hits.c_struct()
+    _lib.check(lib.rtxnerf_batch_assemble(C.byref(st), int(seed), int(group), int(first), int(batch_rays),
+                                          C.byref(hs), _p(gt_pixels), _p(ray_ids), _p(workspace), workspace.numel(),
+                                          _stream_ptr(stream)), "batch_assemble")
+    _lib.count_launches(3 if batch_rays > 0 else 0)
+
+
 # ----------------------------------------------------------------------------- network
 IMPL_TCGEN05 = 0
 IMPL_SIMT = 1

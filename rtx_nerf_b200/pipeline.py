@@ -257,6 +257,19 @@ class Trainer:
         self.allreduce()
         self.optimizer_step()
 
+    def step_from_store(self, store, seed, first, group=1):
+        """One step on positions [first, first + n_rays) of the seeded shuffle of a resident RayStore
+        (the reference's own batching, main.cu:612-676: shuffled rays of ALL views, not a range of
+        one view).  batch_assemble takes the place of the march: three launches, no host work."""
+        v = self.view
+        api.batch_assemble(store, seed, group, first, self.R, v.hits, gt_pixels=self.target)
+        v.stage_sampler()
+        v.stage_radiance()
+        v.stage_composite()
+        self.backward()
+        self.allreduce()
+        self.optimizer_step()
+
     @property
     def launches_per_step(self):
         return self.view.launches_per_view + 1 + 1 + 2 + 1   # + loss, compositing bwd, network bwd (2), Adam
