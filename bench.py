@@ -359,14 +359,32 @@ def run_ours(args):
         train = dict(ms=a.elapsed_time(b) / t_steps, allreduce_ms=ar_ms, allreduce_alone_ms=ar_alone, rays=TR,
                      samples=float(tr.view.hits.total_hits.item()) * TS, grad_bytes=tr.grads.numel() * 4,
                      launches_per_step=tr.launches_per_step, loss=float(tr.loss_sum.item()) / (t_warm + t_steps))
+        # the same step fed the reference's way (main.cu:612-676): 2^18 rays drawn from ALL of this rank's views
+        # by the seeded shuffle of a resident ray store (batch_assemble instead of a per-step march)
+        SV = 4
+        store = api.RayStore(SV, W * H, SV * W * H * THM, pixels_gt=torch.rand((SV * W * H, 3), device="cuda"))
+        for k in range(SV):
+            store.add_view(grid, poses_dev[k % len(poses_dev)], focal, W / H, W, H, THM)
+        n_batches = store.n_rays // TR
+        for k in range(t_warm):
+            tr.step_from_store(store, 1 + rank, (k % n_batches) * TR, 32)
+        barrier()
+        a.record()
+        for k in range(t_steps):
+            tr.step_from_store(store, 1 + rank, ((t_warm + k) % n_batches) * TR, 32)
+        b.record()
+        barrier()
+        train.update(shuffled_ms=a.elapsed_time(b) / t_steps, shuffled_views=SV,
+                     shuffled_samples=float(tr.view.hits.total_hits.item()) * TS)
+        del store
 
     # ---- max over ranks
     tv = [train["ms"], train["allreduce_ms"], train["samples"]] if train else [0.0, 0.0, 0.0]
     ar_alone_all = 0.0
     if train and world > 1:
-        t_ar = torch.tensor([train["allreduce_alone_ms"]], dtype=torch.float64, device="cuda")
+        t_ar = torch.tensor([train["allreduce_alone_ms"], train["shuffled_ms"]], dtype=torch.float64, device="cuda")
         dist.all_reduce(t_ar, op=dist.ReduceOp.MAX)
-        ar_alone_all = float(t_ar[0])
+        ar_alone_all, train["shuffled_ms"] = float(t_ar[0]), float(t_ar[1])
     vals = torch.tensor([ms_total, e2e_s * 1e3, float(hits)] + tv + stage_ms, dtype=torch.float64, device="cuda")
     per_rank = [[ms_total / args.steps, spin_info["last_ms_per_view"]]]
     if world > 1:
@@ -440,7 +458,11 @@ def run_ours(args):
                 ms_per_step=train["ms"], rays_per_s=train["rays"] * world / (train["ms"] * 1e-3),
                 samples_per_s=train["samples_all"] / (train["ms"] * 1e-3), allreduce_ms=train["allreduce_ms"], allreduce_alone_ms=ar_alone_all,
                 allreduce_bytes=train["grad_bytes"], launches_per_step=train["launches_per_step"],
-                mean_loss=train["loss"], scaling="weak")
+                mean_loss=train["loss"], scaling="weak",
+                shuffled=dict(workload="same step, rays drawn from %d resident views per rank by the seeded shuffle "
+                                       "(RayStore + batch_assemble, groups of 32 adjacent pixels)" % train["shuffled_views"],
+                              ms_per_step=train["shuffled_ms"], rays_per_s=train["rays"] * world / (train["shuffled_ms"] * 1e-3),
+                              samples_last_step=train["shuffled_samples"]))
         if world == 1 and not args.no_cpu:
             nthreads = os.cpu_count() or 1
             cpu_path(1000, my_poses, nthreads)

@@ -22,6 +22,19 @@ def ray_shard(n_rays, rank, world):
     return begin, begin + base + (1 if rank < rem else 0)
 
 
+def batch_first(step, rank, world, batch_rays, n_rays):
+    """First position, in the seeded shuffle of a store of n_rays rays shared by all ranks, of rank
+    `rank`'s batch at global step `step` (api.batch_assemble's `first`): consecutive whole batches are dealt
+    round-robin, so within an epoch no ray is used twice on any rank.  Returns (epoch, first) — the epoch is
+    the shuffle seed's offset; the tail that does not fill a batch for every rank is skipped (the reference
+    slices past the end of its vector there, Q6)."""
+    rounds_per_epoch = n_rays // (batch_rays * world)
+    if rounds_per_epoch <= 0:
+        raise ValueError("ray store smaller than one batch per rank")
+    epoch, rnd = divmod(step, rounds_per_epoch)
+    return epoch, (rnd * world + rank) * batch_rays
+
+
 def allreduce_sum_(flat, group=None):
     """In-place sum over ranks of the flat gradient buffer (NCCL on GPUs, gloo in the CPU tests)."""
     if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:

@@ -13,6 +13,7 @@ timeout 300 python scripts/stage_bench.py > $O/stage_bench.txt 2>&1
 timeout 300 python scripts/train_bench.py > $O/train_bench.txt 2>&1
 timeout 300 python scripts/ref_kernels_bench.py --json $O/ref_kernels.json > $O/ref_kernels.txt 2>&1; echo "ref-kernels rc=$?" | tee -a $O/rc.txt
 timeout 300 python scripts/freqnet_bench.py > $O/freqnet_bench.txt 2>&1
+timeout 300 python scripts/batch_bench.py > $O/batch_bench.txt 2>&1; echo "batch-bench rc=$?" | tee -a $O/rc.txt
 if [ "$2" != "noprof" ]; then
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/launches.csv \
   python bench.py --steps 2 --warmup 3 --no-cpu --spinup 0 > $O/ncu_launch.log 2>&1; echo "ncu-list rc=$?" | tee -a $O/rc.txt
@@ -23,5 +24,7 @@ timeout 900 ncu --set full --clock-control none --import-source on -s 12 -c 4 -o
   python bench.py --steps 2 --warmup 3 --no-cpu --no-train --no-refnet --spinup 0 --staged > $O/ncu_staged.log 2>&1; echo "ncu-staged rc=$?" | tee -a $O/rc.txt
 timeout 900 ncu --set full --clock-control none --import-source on -s 24 -c 14 -o $O/train_full -f \
   python scripts/train_bench.py --steps 1 > $O/ncu_train.log 2>&1; echo "ncu-train rc=$?" | tee -a $O/rc.txt
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:batch_ -s 30 -c 3 -o $O/batch_full -f \
+  python scripts/batch_bench.py --reps 3 > $O/ncu_batch.log 2>&1; echo "ncu-batch rc=$?" | tee -a $O/rc.txt
 fi
-tail -3 $O/pytest.log; cat $O/smoke.log | tail -2; cat $O/bench.json | cut -c1-600; cat $O/stage_bench.txt; cat $O/train_bench.txt; cat $O/ref_kernels.txt; tail -3 $O/freqnet_bench.txt
+tail -3 $O/pytest.log; cat $O/smoke.log | tail -2; cat $O/bench.json | cut -c1-600; cat $O/stage_bench.txt; cat $O/train_bench.txt; cat $O/ref_kernels.txt; tail -3 $O/freqnet_bench.txt; cat $O/batch_bench.txt; cat $O/rc.txt

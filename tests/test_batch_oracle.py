@@ -97,3 +97,20 @@ def test_batch_assemble_capacity_and_empty(orc):
     st["indices"][:] = 0
     miss = orc.batch_assemble(st, 3, 1, 0, 64)
     assert miss["total_hits"] == 0 and np.all(miss["indices"] == 0)
+
+
+def test_ranks_deal_disjoint_batches(orc):
+    """parallel.batch_first: over an epoch the ranks' batches are disjoint slices of one shuffle."""
+    from rtx_nerf_b200 import parallel
+    n, B, world = 4096, 256, 3
+    seen = np.zeros(n, np.int32)
+    rounds = n // (B * world)
+    for step in range(rounds):
+        for rank in range(world):
+            epoch, first = parallel.batch_first(step, rank, world, B, n)
+            assert epoch == 0 and first + B <= n
+            seen[orc.ray_permutation(n, 100 + epoch, 32, first, B)] += 1
+    assert seen.max() == 1 and seen.sum() == rounds * world * B
+    assert parallel.batch_first(rounds, 1, world, B, n) == (1, B)
+    with pytest.raises(ValueError):
+        parallel.batch_first(0, 0, 8, 1024, 4096)
