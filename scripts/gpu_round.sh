@@ -26,5 +26,8 @@ timeout 900 ncu --set full --clock-control none --import-source on -s 24 -c 14 -
   python scripts/train_bench.py --steps 1 > $O/ncu_train.log 2>&1; echo "ncu-train rc=$?" | tee -a $O/rc.txt
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:batch_ -s 30 -c 3 -o $O/batch_full -f \
   python scripts/batch_bench.py --reps 3 > $O/ncu_batch.log 2>&1; echo "ncu-batch rc=$?" | tee -a $O/rc.txt
+# gpurun merges at most 64 MiB back: summarise on the box, then drop the largest reports until the directory fits
+for r in $O/*.ncu-rep; do python scripts/ncu_summary.py $r > ${r%.ncu-rep}.txt 2>/dev/null; done
+while [ $(du -sm gpurun_out | cut -f1) -ge 60 ]; do big=$(ls -S $O/*.ncu-rep 2>/dev/null | head -1); [ -z "$big" ] && break; rm -f $big; done
 fi
 tail -3 $O/pytest.log; cat $O/smoke.log | tail -2; cat $O/bench.json | cut -c1-600; cat $O/stage_bench.txt; cat $O/train_bench.txt; cat $O/ref_kernels.txt; tail -3 $O/freqnet_bench.txt; cat $O/batch_bench.txt; cat $O/rc.txt
