@@ -161,3 +161,33 @@ def test_trainer_step_gradients_vs_oracle_and_loss_decreases(cuda_api, orc):
         losses.append(float(tr.loss_sum.item()))
     assert losses[-1] < losses[0], losses
     assert torch.isfinite(tr.master).all()
+
+
+@pytest.mark.parametrize("n,offset", [(4099, 0), (4096, 0), (3, 0), (4099, 1), (1 << 20, 0)])
+def test_adam_vectorised_body_equals_scalar_kernel(cuda_api, n, offset):
+    """The 4-per-thread body (+ scalar tail) and the scalar kernel (unaligned callers) give the same bits:
+    master, fp16 copy, both moments; untouched entries (zero gradient, zero moments) included."""
+    import torch
+    api = cuda_api
+    rng = np.random.default_rng(n + offset)
+    g0 = (rng.normal(0, 1, n + offset) * 64).astype(np.float32)
+    g0[rng.random(n + offset) < 0.5] = 0.0
+    w0 = rng.normal(0, 0.1, n + offset).astype(np.float32)
+    out = []
+    for off in (offset, 1 if offset == 0 else offset):     # second run: slices starting 4 B off 16-byte alignment
+        pad = off
+        bufs = [torch.zeros(n + pad + 3, dtype=torch.float32, device="cuda") for _ in range(4)]
+        half = torch.zeros(n + pad + 3, dtype=torch.float16, device="cuda")
+        dm, dg, d1, d2 = [b[pad:pad + n] for b in bufs]
+        dp = half[pad:pad + n]
+        dm.copy_(_t(w0[:n]))
+        for step in (1, 2):
+            dg.copy_(_t(g0[:n]))
+            api.adam_step(dm, dp, dg, d1, d2, 1.0 / 128.0, step)
+        torch.cuda.synchronize()
+        assert bool((dg == 0).all())
+        for b in bufs:                                       # nothing written outside the slice
+            assert bool((b[:pad] == 0).all()) and bool((b[pad + n:] == 0).all())
+        out.append([x.cpu().numpy().copy() for x in (dm, dp, d1, d2)])
+    for a, b in zip(*out):
+        assert np.array_equal(a.view(np.uint8), b.view(np.uint8))
