@@ -163,7 +163,7 @@ def test_trainer_step_gradients_vs_oracle_and_loss_decreases(cuda_api, orc):
     assert torch.isfinite(tr.master).all()
 
 
-@pytest.mark.parametrize("n,offset", [(4099, 0), (4096, 0), (3, 0), (4099, 1), (1 << 20, 0)])
+@pytest.mark.parametrize("n,offset", [(4099, 0), (4096, 0), (3, 0), (4099, 1), ((1 << 21) + 5, 0)])
 def test_adam_vectorised_body_equals_scalar_kernel(cuda_api, n, offset):
     """The 4-per-thread body (+ scalar tail) and the scalar kernel (unaligned callers) give the same bits:
     master, fp16 copy, both moments; untouched entries (zero gradient, zero moments) included."""
