@@ -16,6 +16,12 @@ def test_permutation_is_a_bijection(orc, n, group):
         assert np.all(g[:, 0] % group == 0) and np.all(np.diff(g, axis=1) == 1)
 
 
+def test_one_group_is_the_identity(orc):
+    """group = n: a single group, so batches are contiguous ray ranges (the per-view front end)."""
+    assert orc.ray_permutation(1024, 5, 1024).tolist() == list(range(1024))
+    assert orc.ray_permutation(1024, 9, 1024, 128, 256).tolist() == list(range(128, 384))
+
+
 def test_permutation_slices_and_seeds(orc):
     n = 10007
     whole = orc.ray_permutation(n, seed=7)

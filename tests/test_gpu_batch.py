@@ -184,3 +184,46 @@ def test_batch_full_size_properties(cuda_api):
         assert torch.equal(hits.end_points[:T], store.end_points[src])
     assert int(seen.max()) <= 1 and int(seen.sum(dtype=torch.int64)) == (n // B) * B
     grid.destroy()
+
+
+def test_store_fed_forward_equals_the_per_view_forward(cuda_api):
+    """One group spanning the whole store makes the shuffle the identity, so a batch is a contiguous ray
+    range of the view — exactly what Trainer.step marches itself.  Hit records, samples and composited
+    pixels must then be bit-identical between the two front ends (same kernels downstream)."""
+    import torch
+    from rtx_nerf_b200 import pipeline
+    api = cuda_api
+    G, W, H, HM, S, R, first = 32, 32, 32, 8, 4, 256, 128
+    occ = synth.occupancy_bernoulli(G, 0.3, seed=40)
+    grid = api.OccupancyGrid.from_occupancy(occ, G)
+    lv = synth.hashgrid_levels()
+    net = api.Network(lv, synth.hashgrid_table(lv, seed=41), synth.mlp_weights(seed=42))
+    pose = _t(synth.poses(1, seed=43)[0])
+    gt = torch.rand((W * H, 3), device="cuda")
+    store = api.RayStore(1, W * H, W * H * HM, pixels_gt=gt)
+    store.add_view(grid, pose, synth.focal_length(), 1.0, W, H, HM)
+    assert api.ray_permutation(W * H, 5, W * H).cpu().tolist() == list(range(W * H))
+    tr = pipeline.Trainer(grid, net, W, H, synth.focal_length(), 1.0, S, HM, R)
+    v = tr.view
+    v.pose_dev.copy_(pose.reshape(16))
+    v.ray_begin = first
+    tr.forward()
+    torch.cuda.synchronize()
+    T = int(v.hits.total_hits.item())
+    a = [x.clone() for x in (v.hits.num_hits, v.hits.indices, v.hits.view_dirs, v.hits.start_points[:T],
+                             v.hits.end_points[:T], v.samples[:T * S], v.t_vals[:T * S], v.pixels)]
+    for x in (v.hits.num_hits, v.hits.indices, v.hits.view_dirs, v.hits.start_points, v.hits.end_points, v.samples,
+              v.t_vals, v.pixels):
+        x.zero_()
+    api.batch_assemble(store, 5, W * H, first, R, v.hits, gt_pixels=tr.target)
+    v.stage_sampler()
+    v.stage_radiance()
+    v.stage_composite()
+    torch.cuda.synchronize()
+    assert int(v.hits.total_hits.item()) == T and T > 0
+    b = (v.hits.num_hits, v.hits.indices, v.hits.view_dirs, v.hits.start_points[:T], v.hits.end_points[:T],
+         v.samples[:T * S], v.t_vals[:T * S], v.pixels)
+    for i, (x, y) in enumerate(zip(a, b)):
+        assert torch.equal(x, y), i
+    assert torch.equal(tr.target, gt[first:first + R])
+    grid.destroy()
