@@ -575,6 +575,17 @@ static inline uint32_t grid_index(uint32_t x, uint32_t y, uint32_t z, uint32_t r
     return idx % size;
 }
 
+/* [-1,1] -> [0,1] with the clamp of fma.rn.sat.f32 (hashgrid.cuh unit_coord): a position outside
+ * the cube takes the features of its nearest face, a NaN those of 0, and no corner index can leave
+ * its level (tiny-cuda-nn keeps indices in range with its modulo; this is the cheaper guard). */
+static inline float unit_coord(float p)
+{
+    float x = fmaf(p, 0.5f, 0.5f);
+    if (!(x >= 0.0f)) x = 0.0f;
+    if (x > 1.0f) x = 1.0f;
+    return x;
+}
+
 void orc_hashgrid_encode(int L, int F, const float* scales, const uint32_t* ress,
                          const uint32_t* sizes, const long long* offsets, const uint16_t* table,
                          const float* samples, int sample_stride, long long n, uint16_t* encoded,
@@ -584,7 +595,7 @@ void orc_hashgrid_encode(int L, int F, const float* scales, const uint32_t* ress
     for (long long s = 0; s < n; s++) {
         const float* p = samples + (size_t)s * sample_stride;
         float x01[3];
-        for (int k = 0; k < 3; k++) x01[k] = fmaf(p[k], 0.5f, 0.5f); /* [-1,1] -> [0,1] */
+        for (int k = 0; k < 3; k++) x01[k] = unit_coord(p[k]); /* [-1,1] -> [0,1], clamped */
         for (int l = 0; l < L; l++) {
             float frac[3];
             uint32_t g[3];
@@ -770,7 +781,7 @@ void orc_hashgrid_backward(int L, const float* scales, const uint32_t* ress, con
     for (long long s = 0; s < n; s++) {
         const float* p = samples + (size_t)s * sample_stride;
         float x01[3];
-        for (int k = 0; k < 3; k++) x01[k] = fmaf(p[k], 0.5f, 0.5f);
+        for (int k = 0; k < 3; k++) x01[k] = unit_coord(p[k]); /* [-1,1] -> [0,1], clamped */
         for (int l = 0; l < L; l++) {
             float g0 = orc_h2f(d_enc[(size_t)s * L * 2 + (size_t)l * 2]);
             float g1 = orc_h2f(d_enc[(size_t)s * L * 2 + (size_t)l * 2 + 1]);

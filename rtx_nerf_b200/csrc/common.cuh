@@ -4,6 +4,9 @@
 #include <cuda_runtime.h>
 #include <cuda_fp16.h>
 #include <stdint.h>
+#include <stdlib.h>
+
+#include <atomic>
 
 #include "../../include/rtxnerf.h"
 
@@ -30,6 +33,43 @@ static inline int rtx_launch_status(int n_launched = 1)
 {
     __atomic_fetch_add(&g_rtx_kernel_launches, (unsigned long long)n_launched, __ATOMIC_RELAXED);
     return (int)cudaGetLastError();
+}
+
+// Function attributes (dynamic shared memory above 48 KB) are per device and per context: remember
+// which devices of this process have them, so that a host driving several GPUs from several
+// threads (SURVEY 8b "Threading") gets them on each.  Racing threads may both set the attribute;
+// that is idempotent.
+struct RtxPerDeviceOnce {
+    std::atomic<unsigned long long> done[4];   // 256 device ordinals
+};
+// 1: the current device is already marked, 0: not yet, < 0 never (errors are returned as positive CUDA codes by
+// the callers through RTX_CUDA_TRY on cudaGetDevice)
+static inline bool rtx_device_done(RtxPerDeviceOnce& st)
+{
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return false;
+    return (st.done[(dev >> 6) & 3].load(std::memory_order_acquire) >> (dev & 63)) & 1ull;
+}
+static inline void rtx_device_mark(RtxPerDeviceOnce& st)
+{
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return;
+    st.done[(dev >> 6) & 3].fetch_or(1ull << (dev & 63), std::memory_order_release);
+}
+template <class Kernel>
+static inline int rtx_set_max_smem(RtxPerDeviceOnce& st, Kernel kernel, int bytes)
+{
+    if (rtx_device_done(st)) return 0;
+    RTX_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+    rtx_device_mark(st);
+    return 0;
+}
+// development knobs from the environment: read once per process (C++11 static initialisation is
+// thread-safe), never per device
+static inline int rtx_env_int(const char* name, int dflt)
+{
+    const char* e = getenv(name);
+    return (e && *e) ? atoi(e) : dflt;
 }
 
 // ---------------------------------------------------------------------------------------

@@ -26,6 +26,10 @@ struct Levels {
 #define HG_PRIME_Y 2654435761u
 #define HG_PRIME_Z 805459861u
 
+// [-1,1] -> [0,1], clamped: every index below stays inside its level whatever the caller passes
+// (a NaN becomes 0).  FFMA.SAT: the clamp is free.  The oracle clamps the same way.
+__device__ __forceinline__ float unit_coord(float p) { return __saturatef(rn_fma(p, 0.5f, 0.5f)); }
+
 struct LevelPoint {
     uint32_t idx[8];   // entry index of corner c = (cx) | (cy << 1) | (cz << 2) within the level
     float w[8];        // trilinear weight of corner c
@@ -237,4 +241,168 @@ __device__ __forceinline__ __half2 encode_level_any(const Levels& lv, const char
     if (m == 1u) return encode_level_fast<1>(lv, l, table_bytes, x01, y01, z01);
     if (m == 0u) return encode_level_fast<0>(lv, l, table_bytes, x01, y01, z01);
     return encode_level(reinterpret_cast<const __half2*>(table_bytes), lv, l, x01, y01, z01);
+}
+
+// =========================================================================================
+// Lean paths (round 2): the same features, bit for bit, in fewer instructions and with nothing
+// on the conversion pipe.  What changed against encode_level_fast:
+//   * floor + integer cell without FRND / F2I (quarter-rate XU pipe): s = p + 2^23 rounded DOWN
+//     (FADD.RM) is 2^23 + floor(p) exactly for 0 <= p < 2^23, so floor(p) = s - 2^23, the cell is
+//     the low mantissa bits of s, and p - floor(p) is exact either way.  The raw bits
+//     (0x4B000000 + cell) are used as they are: hashed levels multiply by odd primes and mask
+//     below bit 22, so the bias never reaches a kept bit (host check: size <= 2^22); dense
+//     levels subtract one per-level constant from the linear index;
+//   * ONE parity predicate per hashed level: the primes are odd, so bit 0 of
+//     (gx+cx) ^ (gy+cy)*P ^ (gz+cz)*Q is (gx ^ gy ^ gz ^ cx ^ cy ^ cz) & 1;
+//   * addresses are base + entry * 4 in ONE IMAD.WIDE.U32 (with a byte offset and multiplier 1 the
+//     compiler turns the mad into a two-instruction 64-bit add);
+//   * per-level constants come from a host-derived table in the kernel parameters (LeanLevels),
+//     dense levels first, hashed power-of-two levels after them — the layout every instant-ngp
+//     style configuration has; anything else keeps the generic path.
+// =========================================================================================
+struct LevelK {
+    float scale;
+    uint32_t base;    // first entry of the level inside the table
+    uint32_t a;       // dense: res         hashed: size - 1
+    uint32_t b;       // dense: res * res   hashed: (size - 1) & ~1
+    uint32_t c;       // dense: 0x4B000000 * (1 + res + res^2) mod 2^32 (bias of the raw cell bits)
+    uint32_t size;    // dense: entries of the level (wrap test)
+};
+struct LeanLevels {
+    LevelK k[RTXNERF_MAX_LEVELS];
+    int n_levels, n_dense;   // levels [0, n_dense) dense, [n_dense, n_levels) hashed with size = 2^k
+    int ok;                  // 0: this configuration needs the generic path
+};
+
+static inline void lean_levels_from(const Levels& lv, LeanLevels* out)
+{
+    out->n_levels = lv.n_levels;
+    out->ok = 1;
+    int nd = 0;
+    while (nd < lv.n_levels && lv.mode[nd] == 0u) nd++;
+    out->n_dense = nd;
+    for (int l = 0; l < RTXNERF_MAX_LEVELS; l++) {
+        LevelK& k = out->k[l];
+        k.scale = 0.f; k.base = 0; k.a = 0; k.b = 0; k.c = 0; k.size = 2;
+        if (l >= lv.n_levels) continue;
+        if (l >= nd && lv.mode[l] != 1u) out->ok = 0;
+        if (!(lv.scale[l] >= 0.0f && lv.scale[l] < 4194304.0f)) out->ok = 0;
+        if (lv.size[l] > (1u << 22)) out->ok = 0;
+        k.scale = lv.scale[l];
+        k.base = lv.offset[l];
+        k.size = lv.size[l];
+        if (l < nd) {
+            k.a = lv.res[l];
+            k.b = lv.res[l] * lv.res[l];
+            k.c = 0x4B000000u * (1u + k.a + k.b);
+        } else {
+            k.a = lv.size[l] - 1u;
+            k.b = k.a & ~1u;
+        }
+    }
+}
+
+// frac = p - floor(p) and the raw cell bits 0x4B000000 + floor(p), for 0 <= p < 2^23
+__device__ __forceinline__ void floor_split(float p, float& frac, uint32_t& cell_bits)
+{
+    const float s = __fadd_rd(p, 8388608.0f);
+    cell_bits = __float_as_uint(s);
+    frac = rn_sub(p, rn_sub(s, 8388608.0f));
+}
+
+// address of table entry `idx` (4 bytes each).  ptxas lowers this to LEA + LEA.HI.X here (it keeps
+// IMAD.WIDE.U32 only for the immediate form and prefers the integer pipe in this FMA-heavy loop;
+// a register multiplier makes it split off the 64-bit add: three instructions) — measured on the
+// SASS, nothing to gain by spelling it differently.
+__device__ __forceinline__ const uint32_t* entry_addr(const uint32_t* base, uint32_t idx)
+{
+    uint64_t r;
+    asm("mad.wide.u32 %0, %1, 4, %2;" : "=l"(r) : "r"(idx), "l"(reinterpret_cast<uint64_t>(base)));
+    return reinterpret_cast<const uint32_t*>(r);
+}
+
+// fp32 blend of the 8 corner values in corner order (the arithmetic of encode_level, unchanged)
+__device__ __forceinline__ uint32_t blend8(const uint32_t (&v)[8], float wx, float wy, float wz)
+{
+    const float ux = rn_sub(1.0f, wx), uy = rn_sub(1.0f, wy), uz = rn_sub(1.0f, wz);
+    const float w00 = rn_mul(ux, uy), w10 = rn_mul(wx, uy), w01 = rn_mul(ux, wy), w11 = rn_mul(wx, wy);
+    const float w[8] = {rn_mul(w00, uz), rn_mul(w10, uz), rn_mul(w01, uz), rn_mul(w11, uz),
+                        rn_mul(w00, wz), rn_mul(w10, wz), rn_mul(w01, wz), rn_mul(w11, wz)};
+    float a0 = 0.0f, a1 = 0.0f;
+#pragma unroll
+    for (int c = 0; c < 8; c++) {
+        const float2 f = h2_bits_to_f2(v[c]);
+        a0 = rn_fma(w[c], f.x, a0);
+        a1 = rn_fma(w[c], f.y, a1);
+    }
+    const __half2 h = __floats2half2_rn(a0, a1);
+    return *reinterpret_cast<const uint32_t*>(&h);
+}
+
+__device__ __forceinline__ uint32_t encode_hashed_lean(const LevelK& k,
+                                                       const uint32_t* __restrict__ table32, float x01, float y01,
+                                                       float z01)
+{
+    const uint32_t* lb = table32 + k.base;
+    float wx, wy, wz;
+    uint32_t bx, by, bz;
+    floor_split(rn_fma(k.scale, x01, 0.5f), wx, bx);
+    floor_split(rn_fma(k.scale, y01, 0.5f), wy, by);
+    floor_split(rn_fma(k.scale, z01, 0.5f), wz, bz);
+    const uint32_t mask = k.a, mask_pair = k.b;
+    const uint32_t bx1 = bx + 1u;
+    const uint32_t hy0 = by * HG_PRIME_Y, hy1 = hy0 + HG_PRIME_Y;
+    const uint32_t hz0 = bz * HG_PRIME_Z, hz1 = hz0 + HG_PRIME_Z;
+    const uint32_t yz[4] = {hy0 ^ hz0, hy1 ^ hz0, hy0 ^ hz1, hy1 ^ hz1};
+    const bool odd00 = ((bx ^ by ^ bz) & 1u) != 0u;   // corner (x0, y0, z0) is the upper entry of its pair
+    const bool split = (bx & 1u) != 0u;               // odd gx: x1 lies outside the pair of x0
+    uint32_t v[8];
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+        const uint2 e = __ldg(reinterpret_cast<const uint2*>(entry_addr(lb, (bx ^ yz[q]) & mask_pair)));
+        const bool odd = (q == 0 || q == 3) ? odd00 : !odd00;
+        v[2 * q] = odd ? e.y : e.x;
+        uint32_t other = odd ? e.x : e.y;
+        if (split) other = __ldg(entry_addr(lb, (bx1 ^ yz[q]) & mask));
+        v[2 * q + 1] = other;
+    }
+    return blend8(v, wx, wy, wz);
+}
+
+__device__ __forceinline__ uint32_t encode_dense_lean(const LevelK& k,
+                                                      const uint32_t* __restrict__ table32, float x01, float y01,
+                                                      float z01)
+{
+    const uint32_t* lb = table32 + k.base;
+    float wx, wy, wz;
+    uint32_t bx, by, bz;
+    floor_split(rn_fma(k.scale, x01, 0.5f), wx, bx);
+    floor_split(rn_fma(k.scale, y01, 0.5f), wy, by);
+    floor_split(rn_fma(k.scale, z01, 0.5f), wz, bz);
+    const uint32_t res = k.a, s2 = k.b;
+    const uint32_t base = bx + by * res + bz * s2 - k.c;      // gx + gy*res + gz*res^2
+    const uint32_t idx[4] = {base, base + res, base + s2, base + res + s2};
+    uint32_t v[8];
+    if (base + 1u + res + s2 >= k.size) {
+        // far faces of the grid: a corner index may pass the end of the level; idx < 2 * size,
+        // so one conditional subtraction is the modulo of the generic path
+#pragma unroll
+        for (int c = 0; c < 8; c++) {
+            uint32_t i = idx[c >> 1] + (uint32_t)(c & 1);
+            if (i >= k.size) i -= k.size;
+            v[c] = __ldg(entry_addr(lb, i));
+        }
+    } else {
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            const uint32_t* pa = entry_addr(lb, idx[q] & ~1u);
+            const bool odd = (idx[q] & 1u) != 0u;
+            const uint2 e = __ldg(reinterpret_cast<const uint2*>(pa));
+            uint32_t other = e.y;
+            if (odd) other = __ldg(pa + 2);   // x1 opens the next pair
+            v[2 * q] = odd ? e.y : e.x;
+            v[2 * q + 1] = other;
+        }
+    }
+    return blend8(v, wx, wy, wz);
 }

@@ -946,33 +946,29 @@ extern "C" int rtxnerf_ray_march_csr(const rtxnerf_grid* grid, const rtxnerf_cam
     int* block_sums = reinterpret_cast<int*>(block_offsets + nb);
     CamArgs c{cam->look_at, cam->focal_length, cam->aspect_ratio, cam->width, cam->height};
     FillOut fo{hits->t_start, hits->t_end, hits->start_points, hits->end_points, hits->hit_cells, hits->capacity};
-    static int two_pass = -1;   // development knob: RTXNERF_MARCH_TWO_PASS=1 forces count -> scan -> fill
-    static int flat = -1;       // development knob: RTXNERF_MARCH_FLAT=0/1 (+ _ENTER_EVERY, _ENTER_MIN)
-    if (two_pass < 0) {
-        const char* e = getenv("RTXNERF_MARCH_TWO_PASS");
-        two_pass = (e && e[0] == '1') ? 1 : 0;
-        e = getenv("RTXNERF_MARCH_FLAT");
-        flat = e ? (e[0] == '1') : 2;        // 2 = default: flat loop for the staged path only
-        const char* ee = getenv("RTXNERF_MARCH_ENTER_EVERY");
-        const char* em = getenv("RTXNERF_MARCH_ENTER_MIN");
-        if (ee) { int v = atoi(ee); RTX_CUDA_TRY(cudaMemcpyToSymbol(c_enter_every, &v, sizeof(int))); }
-        if (em) { int v = atoi(em); RTX_CUDA_TRY(cudaMemcpyToSymbol(c_enter_min, &v, sizeof(int))); }
+    // development knobs, read once per process: RTXNERF_MARCH_TWO_PASS=1 forces count -> scan -> fill,
+    // RTXNERF_MARCH_FLAT=0/1 picks the loop shape (default 2: flat loop for the staged path only);
+    // _ENTER_EVERY / _ENTER_MIN tune the flat loop's relaunch batching (a __constant__ per device)
+    static const int two_pass = rtx_env_int("RTXNERF_MARCH_TWO_PASS", 0) == 1 ? 1 : 0;
+    static const int flat = rtx_env_int("RTXNERF_MARCH_FLAT", 2);
+    static const int enter_every = rtx_env_int("RTXNERF_MARCH_ENTER_EVERY", 0);
+    static const int enter_min = rtx_env_int("RTXNERF_MARCH_ENTER_MIN", 0);
+    static RtxPerDeviceOnce knobs_set;
+    if ((enter_every || enter_min) && !rtx_device_done(knobs_set)) {
+        if (enter_every) RTX_CUDA_TRY(cudaMemcpyToSymbol(c_enter_every, &enter_every, sizeof(int)));
+        if (enter_min) RTX_CUDA_TRY(cudaMemcpyToSymbol(c_enter_min, &enter_min, sizeof(int)));
+        rtx_device_mark(knobs_set);
     }
     if (max_hits <= ONEPASS_MAX_CAP && !two_pass) {
         unsigned long long* status = reinterpret_cast<unsigned long long*>(
             reinterpret_cast<char*>(block_sums) + (((size_t)nb * sizeof(int) + 7) & ~(size_t)7));
         unsigned long long* ticket = status + nb;
         const size_t smem = onepass_smem_bytes(max_hits);
-        static size_t smem_set = 0;
-        if (smem > smem_set) {
-            RTX_CUDA_TRY(cudaFuncSetAttribute(march_onepass_kernel<false, false>,
-                                              cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                              (int)onepass_smem_bytes(ONEPASS_MAX_CAP)));
-            RTX_CUDA_TRY(cudaFuncSetAttribute(march_onepass_kernel<false, true>,
-                                              cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                              (int)onepass_smem_bytes(ONEPASS_MAX_CAP)));
-            smem_set = onepass_smem_bytes(ONEPASS_MAX_CAP);
-        }
+        static RtxPerDeviceOnce smem_a, smem_b;
+        RTX_CUDA_TRY((cudaError_t)rtx_set_max_smem(smem_a, march_onepass_kernel<false, false>,
+                                                   (int)onepass_smem_bytes(ONEPASS_MAX_CAP)));
+        RTX_CUDA_TRY((cudaError_t)rtx_set_max_smem(smem_b, march_onepass_kernel<false, true>,
+                                                   (int)onepass_smem_bytes(ONEPASS_MAX_CAP)));
         RTX_CUDA_TRY(cudaMemsetAsync(status, 0, ((size_t)nb + 1) * sizeof(unsigned long long), s));
         auto kern = flat == 1 ? march_onepass_kernel<false, true> : march_onepass_kernel<false, false>;
         kern<<<(unsigned)nb, MARCH_BLOCK, smem, s>>>(
@@ -988,16 +984,11 @@ extern "C" int rtxnerf_ray_march_csr(const rtxnerf_grid* grid, const rtxnerf_cam
         unsigned long long* ticket = status + nb;
         uint32_t* gstage = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(workspace) + march_base_workspace(n_rays));
         const size_t smem = onepass_smem_bytes(max_hits, true);
-        static size_t smem_set_staged = 0;
-        if (smem > smem_set_staged) {
-            RTX_CUDA_TRY(cudaFuncSetAttribute(march_onepass_kernel<true, false>,
-                                              cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                              (int)onepass_smem_bytes(STAGED_MAX_CAP, true)));
-            RTX_CUDA_TRY(cudaFuncSetAttribute(march_onepass_kernel<true, true>,
-                                              cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                              (int)onepass_smem_bytes(STAGED_MAX_CAP, true)));
-            smem_set_staged = onepass_smem_bytes(STAGED_MAX_CAP, true);
-        }
+        static RtxPerDeviceOnce smem_c, smem_d;
+        RTX_CUDA_TRY((cudaError_t)rtx_set_max_smem(smem_c, march_onepass_kernel<true, false>,
+                                                   (int)onepass_smem_bytes(STAGED_MAX_CAP, true)));
+        RTX_CUDA_TRY((cudaError_t)rtx_set_max_smem(smem_d, march_onepass_kernel<true, true>,
+                                                   (int)onepass_smem_bytes(STAGED_MAX_CAP, true)));
         RTX_CUDA_TRY(cudaMemsetAsync(status, 0, ((size_t)nb + 1) * sizeof(unsigned long long), s));
         auto kern = flat != 0 ? march_onepass_kernel<true, true> : march_onepass_kernel<true, false>;
         kern<<<(unsigned)staged_grid(nb), MARCH_BLOCK, smem, s>>>(

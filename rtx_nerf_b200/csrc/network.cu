@@ -27,7 +27,7 @@ hashgrid_encode_kernel(Levels lv, const __half2* __restrict__ table, const float
     const long long n = row_count(d_count, count_scale, n_max);
     for (long long s = (long long)blockIdx.x * blockDim.x + threadIdx.x; s < n; s += (long long)gridDim.x * blockDim.x) {
         const float* p = samples + s * stride;
-        const float x01 = rn_fma(p[0], 0.5f, 0.5f), y01 = rn_fma(p[1], 0.5f, 0.5f), z01 = rn_fma(p[2], 0.5f, 0.5f);
+        const float x01 = unit_coord(p[0]), y01 = unit_coord(p[1]), z01 = unit_coord(p[2]);
         for (int l = 0; l < lv.n_levels; l++)
             encoded[s * lv.n_levels + l] =
                 encode_level(table, lv, l, x01, y01, z01);
@@ -97,9 +97,9 @@ network_forward_tc_kernel(Levels lv, const __half2* __restrict__ table, const ui
             float x01 = 0.5f, y01 = 0.5f, z01 = 0.5f;
             if (valid) {
                 const float* p = reinterpret_cast<const float*>(input) + s * input_stride;
-                x01 = rn_fma(ld_stream_f1(p), 0.5f, 0.5f);
-                y01 = rn_fma(ld_stream_f1(p + 1), 0.5f, 0.5f);
-                z01 = rn_fma(ld_stream_f1(p + 2), 0.5f, 0.5f);
+                x01 = unit_coord(ld_stream_f1(p));
+                y01 = unit_coord(ld_stream_f1(p + 1));
+                z01 = unit_coord(ld_stream_f1(p + 2));
             }
             // rolled over levels: per-level parameters come from the constant bank, the body
             // stays small enough for the instruction cache, 8 gathers are in flight per thread
@@ -184,7 +184,7 @@ network_forward_simt_kernel(Levels lv, const __half2* __restrict__ table, const 
         float a[NET_W], b[NET_W];
         if (encode) {
             const float* p = reinterpret_cast<const float*>(input) + s * input_stride;
-            const float x01 = rn_fma(p[0], 0.5f, 0.5f), y01 = rn_fma(p[1], 0.5f, 0.5f), z01 = rn_fma(p[2], 0.5f, 0.5f);
+            const float x01 = unit_coord(p[0]), y01 = unit_coord(p[1]), z01 = unit_coord(p[2]);
             for (int l = 0; l < NET_IN / 2; l++) {
                 float2 f = make_float2(0.f, 0.f);
                 if (l < lv.n_levels)
@@ -264,14 +264,9 @@ extern "C" int rtxnerf_network_forward(const rtxnerf_hashgrid* enc, const rtxner
         return rtx_launch_status();
     }
     if (impl != RTXNERF_IMPL_TCGEN05) return RTXNERF_EINVAL;
-    static bool attr_set = false;
-    if (!attr_set) {
-        RTX_CUDA_TRY(cudaFuncSetAttribute(network_forward_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                          NetSmem::BYTES));
-        RTX_CUDA_TRY(cudaFuncSetAttribute(network_forward_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                          NetSmem::BYTES));
-        attr_set = true;
-    }
+    static RtxPerDeviceOnce attr_enc, attr_pre;
+    RTX_CUDA_TRY((cudaError_t)rtx_set_max_smem(attr_enc, network_forward_tc_kernel<true>, NetSmem::BYTES));
+    RTX_CUDA_TRY((cudaError_t)rtx_set_max_smem(attr_pre, network_forward_tc_kernel<false>, NetSmem::BYTES));
     long long tiles = (n_max + NET_TILE - 1) / NET_TILE;
     const long long resident = (long long)RTX_NUM_SMS * NET_CTAS_PER_SM;
     long long blocks = tiles < resident ? tiles : resident;

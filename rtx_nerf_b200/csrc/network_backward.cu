@@ -320,9 +320,9 @@ hashgrid_backward_kernel(Levels lv, const float* __restrict__ samples, int strid
             uint32_t* my = stage[threadIdx.x];
             if (valid) {
                 const float* p = samples + s * stride;
-                x01 = rn_fma(ld_stream_f1(p), 0.5f, 0.5f);
-                y01 = rn_fma(ld_stream_f1(p + 1), 0.5f, 0.5f);
-                z01 = rn_fma(ld_stream_f1(p + 2), 0.5f, 0.5f);
+                x01 = unit_coord(ld_stream_f1(p));
+                y01 = unit_coord(ld_stream_f1(p + 1));
+                z01 = unit_coord(ld_stream_f1(p + 2));
                 const uint4* ge = reinterpret_cast<const uint4*>(d_encoded + s * NET_IN);
 #pragma unroll
                 for (int c = 0; c < NET_IN / 8; c++) {
@@ -548,11 +548,8 @@ extern "C" int rtxnerf_network_backward_rays(const rtxnerf_hashgrid* enc, const 
     if (rc) return rc;
     if (enc->n_levels * 2 > NET_IN) return RTXNERF_ECONFIG;
     if (n_rays == 0 || n_max == 0) return RTXNERF_OK;
-    static bool attr_set = false;
-    if (!attr_set) {
-        RTX_CUDA_TRY(cudaFuncSetAttribute(mlp_backward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, NbSmem::BYTES));
-        attr_set = true;
-    }
+    static RtxPerDeviceOnce attr_set;
+    RTX_CUDA_TRY((cudaError_t)rtx_set_max_smem(attr_set, mlp_backward_kernel, NbSmem::BYTES));
     cudaStream_t s = (cudaStream_t)stream;
     const long long tiles = (n_max + NET_TILE - 1) / NET_TILE;
     const long long resident = (long long)RTX_NUM_SMS * 2;   // 2 CTAs per SM: 2 x 256 TMEM columns, 2 x 75 KB
@@ -591,10 +588,11 @@ extern "C" int rtxnerf_adam_step(long long n, float* d_master, uint16_t* d_param
     if (!d_master || !d_params || !d_grads || !d_m1 || !d_m2 || n < 0 || step < 1) return RTXNERF_EINVAL;
     if (n == 0) return RTXNERF_OK;
     const float lr_t = lr * sqrtf(1.0f - powf(beta2, (float)step)) / (1.0f - powf(beta1, (float)step));
+    static const int adam_scalar = rtx_env_int("RTXNERF_ADAM_SCALAR", 0);   // development knob
     // body: 4 parameters per thread when every array is 16-byte aligned (8 for the fp16 copy); the tail
     // (n % 4) and unaligned callers go through the scalar kernel
     const bool aligned = (((uintptr_t)d_master | (uintptr_t)d_grads | (uintptr_t)d_m1 | (uintptr_t)d_m2) & 15) == 0 &&
-                         ((uintptr_t)d_params & 7) == 0 && !getenv("RTXNERF_ADAM_SCALAR");
+                         ((uintptr_t)d_params & 7) == 0 && !adam_scalar;
     const long long n4 = aligned ? n / 4 : 0;
     int launched = 0;
     if (n4 > 0) {

@@ -430,12 +430,8 @@ extern "C" int rtxnerf_freqnet_forward(const rtxnerf_freqnet* net, const float* 
     if (!d_samples || (!d_out16 && !d_radiance4) || n_max < 0 || sample_stride < 5 || count_scale < 1)
         return RTXNERF_EINVAL;
     if (n_max == 0) return RTXNERF_OK;
-    static bool attr = false;
-    if (!attr) {
-        RTX_CUDA_TRY(cudaFuncSetAttribute(freqnet_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                          FnSmem::BYTES));
-        attr = true;
-    }
+    static RtxPerDeviceOnce attr;
+    RTX_CUDA_TRY((cudaError_t)rtx_set_max_smem(attr, freqnet_forward_kernel, FnSmem::BYTES));
     const long long pairs = ((n_max + NET_TILE - 1) / NET_TILE + 1) / 2;
     const long long blocks = pairs < RTX_NUM_SMS ? pairs : RTX_NUM_SMS;   // one CTA per SM owns all 512 TMEM columns
     freqnet_forward_kernel<<<(unsigned)blocks, FN_THREADS, FnSmem::BYTES, (cudaStream_t)stream>>>(

@@ -19,6 +19,7 @@
 #include "common.cuh"
 #include "hashgrid.cuh"
 #include "mlp_tile.cuh"
+#include "rays_roles.cuh"
 
 #define NETR_WGS 4
 #define NETR_THREADS (NETR_WGS * NET_TILE)
@@ -122,9 +123,9 @@ network_forward_rays_kernel(Levels lv, const uint32_t* __restrict__ table32, con
             for (int i = 0; i < NET_IN / 2; i++) pk[i] = 0u;
             if (valid) {
                 const float* p = samples + s * stride;
-                const float x01 = rn_fma(ld_stream_f1(p), 0.5f, 0.5f);
-                const float y01 = rn_fma(ld_stream_f1(p + 1), 0.5f, 0.5f);
-                const float z01 = rn_fma(ld_stream_f1(p + 2), 0.5f, 0.5f);
+                const float x01 = unit_coord(ld_stream_f1(p));
+                const float y01 = unit_coord(ld_stream_f1(p + 1));
+                const float z01 = unit_coord(ld_stream_f1(p + 2));
 #pragma unroll 1
                 for (int c = 0; c < NET_IN / 4; c++) {
                     uint32_t f0, f1;
@@ -273,9 +274,9 @@ network_forward_rays2_kernel(Levels lv, const uint32_t* __restrict__ table32, co
             // ---- gather: four levels (one 16-byte chunk of this row of the A tile) at a time
             if (valid) {
                 const float* p = samples + s * stride;
-                const float x01 = rn_fma(ld_stream_f1(p), 0.5f, 0.5f);
-                const float y01 = rn_fma(ld_stream_f1(p + 1), 0.5f, 0.5f);
-                const float z01 = rn_fma(ld_stream_f1(p + 2), 0.5f, 0.5f);
+                const float x01 = unit_coord(ld_stream_f1(p));
+                const float y01 = unit_coord(ld_stream_f1(p + 1));
+                const float z01 = unit_coord(ld_stream_f1(p + 2));
 #pragma unroll 1
                 for (int c = 0; c < NET_IN / 8; c++) {
                     uint4 f;
@@ -349,21 +350,28 @@ extern "C" int rtxnerf_network_forward_rays(const rtxnerf_hashgrid* enc, const r
     if (rc) return rc;
     if (enc->n_levels * 2 > NET_IN) return RTXNERF_ECONFIG;
     if (n_rays == 0) return RTXNERF_OK;
-    // 2 CTAs x 512 threads per SM (64 registers) measured faster than 3 (40 registers, spills)
-    static int min_ctas = 0;
-    if (!min_ctas) {
-        const char* e = getenv("RTXNERF_NETR_CTAS");   // development knob
-        min_ctas = (e && e[0] == '3') ? 3 : 2;
-        RTX_CUDA_TRY(cudaFuncSetAttribute(network_forward_rays_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                          NetRSmem::BYTES));
-        RTX_CUDA_TRY(cudaFuncSetAttribute(network_forward_rays_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                          NetRSmem::BYTES));
+    // development knobs (read once per process): RTXNERF_NETR_VERSION = 1 mutex kernel, 2x = round-1 v2
+    // shapes, 3 (default) = the decoupled-role kernel of rays_roles.cuh
+    static const int min_ctas = rtx_env_int("RTXNERF_NETR_CTAS", 2) == 3 ? 3 : 2;
+    static const int version = rtx_env_int("RTXNERF_NETR_VERSION", 3) < 1 ? 3 : rtx_env_int("RTXNERF_NETR_VERSION", 3);
+    if (version == 3) {
+        RrArgs a = {};
+        a.samples = d_samples;
+        a.stride = sample_stride;
+        a.out16 = d_out16;
+        a.radiance4 = d_radiance4;
+        a.encoded_out = d_encoded_out;
+        a.num_hits = d_num_hits;
+        a.indices = d_indices;
+        a.n_rays = n_rays;
+        a.S = samples_per_segment;
+        a.out_activation = mlp->out_activation;
+        return rr_launch(false, enc, mlp, lv, a, (cudaStream_t)stream);
     }
-    static int version = 0;
-    if (!version) {
-        const char* e = getenv("RTXNERF_NETR_VERSION");   // development knob: 1 = mutex kernel, 2x = v2 shapes
-        version = e ? atoi(e) : 2;
-        if (version < 1) version = 2;
+    {
+        static RtxPerDeviceOnce a2, a3;
+        RTX_CUDA_TRY((cudaError_t)rtx_set_max_smem(a2, network_forward_rays_kernel<2>, NetRSmem::BYTES));
+        RTX_CUDA_TRY((cudaError_t)rtx_set_max_smem(a3, network_forward_rays_kernel<3>, NetRSmem::BYTES));
     }
     const long long groups = ((long long)n_rays + 31) / 32;
     if (version >= 2) {
@@ -372,12 +380,9 @@ extern "C" int rtxnerf_network_forward_rays(const rtxnerf_hashgrid* enc, const r
 #endif
 #define NETR2_LAUNCH(WGS, MINB)                                                                                     \
     do {                                                                                                            \
-        static bool attr = false;                                                                                   \
-        if (!attr) {                                                                                                \
-            RTX_CUDA_TRY(cudaFuncSetAttribute(network_forward_rays2_kernel<WGS, MINB>,                              \
-                                              cudaFuncAttributeMaxDynamicSharedMemorySize, NetR2Smem<WGS>::BYTES)); \
-            attr = true;                                                                                            \
-        }                                                                                                           \
+        static RtxPerDeviceOnce attr;                                                                               \
+        RTX_CUDA_TRY((cudaError_t)rtx_set_max_smem(attr, network_forward_rays2_kernel<WGS, MINB>,                   \
+                                                   NetR2Smem<WGS>::BYTES));                                         \
         long long nb = (groups + WGS - 1) / WGS;                                                                    \
         /* not a resident-only grid: one CTA per WGS groups (up to 64 per SM) lets the hardware scheduler       */ \
         /* balance the groups; the static grid-stride split over MINB CTAs per SM measured 5 % slower           */ \

@@ -1,0 +1,366 @@
+// rays_roles.cuh — the ray-coherent network kernel with DECOUPLED ROLES (round 2).
+//
+// Replaces the reference's call sequence main.cu:704-746 (launchSampler -> network->forward ->
+// convertHalfToFloat -> launch_volrender_cuda) in render mode, and main.cu:715-728 (network->forward
+// on the sampler's rows) in staged mode.
+//
+// Round 1's kernels (view_fused.cu, network_rays.cu v2) ran every warp through the whole chain
+//   encode 16 levels -> barrier -> MMA L0 -> wait -> ReLU -> barrier -> MMA L1 -> wait -> ReLU -> barrier -> MMA L2
+// so the ~2000-instruction encoding and the three tensor-core round trips of a tile were serial
+// on the same four warps (ncu: issue slots 65 % busy, tensor pipe 6 %).  Here a 512-thread CTA is
+//   warps 0-3   the MLP group: thread 0 issues the tcgen05.mma's, the four warps run the TMEM
+//               epilogues (ReLU -> fp16 -> A operand of the next layer, written back to TMEM with
+//               tcgen05.st: activations never touch shared memory) and, in render mode, warp 0
+//               composites the rays front to back (vol_render.cu:55-67);
+//   warps 4-15  three encoder groups of four warps.  A tile is 4 sample slots x 32 adjacent rays
+//               (lane = ray, warp = slot: one gather instruction touches neighbouring rays at the
+//               same depth).  Tiles of the CTA's ray groups are dealt round-robin to the encoder
+//               groups; a group writes the 32 features of its 128 rows straight into TMEM as the
+//               layer-0 A operand (16 columns, two buffers per group) and never waits for the MLP.
+// The MLP group consumes tiles in order; hand-offs are mbarriers (enc_ready: 128 encoder threads
+// -> MMA thread, enc_free: MMA thread -> encoder group once layer 0 has read the operand).
+// TMEM per CTA (256 columns, two CTAs per SM): D 64 | A_hidden 32 | 6 x A_encoded 16.
+// Shared memory is only the weights (14 KB) and the 4 KB radiance exchange, so ~190 KB of the SM
+// stays L1 for the hash-table gathers.
+#pragma once
+#include "common.cuh"
+#include "hashgrid.cuh"
+#include "mlp_tile.cuh"
+
+#define RR_ENC_GROUPS 3
+#define RR_THREADS ((RR_ENC_GROUPS + 1) * NET_TILE)
+#define RR_BUFS (2 * RR_ENC_GROUPS)
+#define RR_COL_D 0
+#define RR_COL_AH 64
+#define RR_COL_AE 96
+#define RR_TMEM_COLS 256
+#ifndef RR_GROUPS_PER_CTA
+#define RR_GROUPS_PER_CTA 4      // consecutive 32-ray groups one CTA walks (hardware scheduler balances CTAs)
+#endif
+
+struct RrSmem {
+    static constexpr int W0 = 0;
+    static constexpr int W1 = W0 + NET_W * NET_IN * 2;
+    static constexpr int W2 = W1 + NET_W * NET_W * 2;
+    static constexpr int EXCH = W2 + NET_OUT * NET_W * 2;            // [2][4][32] float4
+    static constexpr int BAR = EXCH + 2 * 4 * 32 * 16;               // enc_ready[6], enc_free[6], mma, tmem slot
+    static constexpr int BYTES = BAR + 8 * (2 * RR_BUFS + 1) + 16;
+};
+
+struct RrArgs {
+    // render mode: sample positions from the CSR entry / exit points, pixels out
+    const float* start_points;
+    const float* end_points;
+    float* pixels;
+    // staged mode: sample rows in, radiance / out16 / encoded features out
+    const float* samples;
+    int stride;
+    uint16_t* out16;
+    float* radiance4;
+    uint16_t* encoded_out;
+    // both
+    const int* num_hits;
+    const int* indices;
+    int n_rays, S, out_activation;
+};
+
+__device__ __forceinline__ void rr_mlp_barrier() { asm volatile("bar.sync 1, %0;" ::"n"(NET_TILE) : "memory"); }
+
+// segment-local sample parameter after i steps of 1/S (sampler.cu:54-66: t += 1.0f/S)
+__device__ __forceinline__ float rr_steps(float inv_s, int i, bool pow2)
+{
+    if (pow2) return rn_mul((float)i, inv_s);   // exact: no rounding ever occurs
+    float t = 0.0f;
+    for (int k = 0; k < i; k++) t = rn_add(t, inv_s);
+    return t;
+}
+
+// two consecutive levels of one sample -> two packed feature pairs
+__device__ __forceinline__ void rr_encode_pair(const LeanLevels& ll, const Levels& lv, const uint32_t* __restrict__ tb, int l,
+                                               float x01, float y01, float z01, uint32_t& f0, uint32_t& f1)
+{
+    f0 = 0u;
+    f1 = 0u;
+    if (ll.ok) {
+        if (l >= ll.n_dense && l + 1 < ll.n_levels) {
+            f0 = encode_hashed_lean(ll.k[l], tb, x01, y01, z01);
+            f1 = encode_hashed_lean(ll.k[l + 1], tb, x01, y01, z01);
+        } else if (l + 1 < ll.n_dense) {
+            f0 = encode_dense_lean(ll.k[l], tb, x01, y01, z01);
+            f1 = encode_dense_lean(ll.k[l + 1], tb, x01, y01, z01);
+        } else {
+            if (l < ll.n_levels)
+                f0 = l < ll.n_dense ? encode_dense_lean(ll.k[l], tb, x01, y01, z01)
+                                    : encode_hashed_lean(ll.k[l], tb, x01, y01, z01);
+            if (l + 1 < ll.n_levels)
+                f1 = l + 1 < ll.n_dense ? encode_dense_lean(ll.k[l + 1], tb, x01, y01, z01)
+                                        : encode_hashed_lean(ll.k[l + 1], tb, x01, y01, z01);
+        }
+    } else {
+        if (l < lv.n_levels) {
+            const __half2 h = encode_level_any(lv, reinterpret_cast<const char*>(tb), l, x01, y01, z01);
+            f0 = *reinterpret_cast<const uint32_t*>(&h);
+        }
+        if (l + 1 < lv.n_levels) {
+            const __half2 h = encode_level_any(lv, reinterpret_cast<const char*>(tb), l + 1, x01, y01, z01);
+            f1 = *reinterpret_cast<const uint32_t*>(&h);
+        }
+    }
+}
+
+// hidden-layer epilogue of one row: 64 fp32 accumulator columns -> ReLU -> fp16 -> 32 A columns
+__device__ __forceinline__ void rr_hidden_epilogue(uint32_t t_d, uint32_t t_a)
+{
+#pragma unroll
+    for (int h = 0; h < NET_W / 32; h++) {
+        uint32_t r0[16], r1[16];
+        tc::tmem_ld_x16(t_d + h * 32, r0);
+        tc::tmem_ld_x16(t_d + h * 32 + 16, r1);
+        tc::tmem_ld_wait();
+        uint32_t pk[16];
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            pk[j] = relu_pack_f16x2(__uint_as_float(r0[2 * j]), __uint_as_float(r0[2 * j + 1]));
+            pk[8 + j] = relu_pack_f16x2(__uint_as_float(r1[2 * j]), __uint_as_float(r1[2 * j + 1]));
+        }
+        tc::tmem_st_x16(t_a + h * 16, pk);
+    }
+    tc::tmem_st_wait();
+}
+
+// one layer with the A operand in TMEM: D[128 x N] = A[128 x K] * W[N x K]^T
+template <int N, int K>
+__device__ __forceinline__ void rr_issue_layer(uint32_t d_tmem, uint32_t a_tmem, uint32_t w_saddr, uint64_t* bar)
+{
+    constexpr uint32_t idesc = tc::idesc_f16_f32(NET_TILE, N);
+    constexpr uint32_t sbo = (K / 8) * 128;
+#pragma unroll
+    for (int ks = 0; ks < K / 16; ks++)
+        tc::mma_f16_ts(d_tmem, a_tmem + ks * 8, tc::smem_desc(w_saddr + ks * 256, 128, sbo), idesc, ks > 0 ? 1u : 0u);
+    tc::mma_commit(bar);
+}
+
+template <bool RENDER>
+__global__ void __launch_bounds__(RR_THREADS, 2)
+rays_roles_kernel(LeanLevels ll, Levels lv, const uint32_t* __restrict__ table32, const uint16_t* __restrict__ weights,
+                  RrArgs a)
+{
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint64_t* enc_ready = reinterpret_cast<uint64_t*>(smem + RrSmem::BAR);
+    uint64_t* enc_free = enc_ready + RR_BUFS;
+    uint64_t* mma_bar = enc_free + RR_BUFS;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(mma_bar + 1);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, wk = warp & 3;
+
+    load_weight_tile(smem + RrSmem::W0, weights, NET_W, NET_IN, tid, RR_THREADS);
+    load_weight_tile(smem + RrSmem::W1, weights + NET_W * NET_IN, NET_W, NET_W, tid, RR_THREADS);
+    load_weight_tile(smem + RrSmem::W2, weights + NET_W * NET_IN + NET_W * NET_W, NET_OUT, NET_W, tid, RR_THREADS);
+    if (tid == 0) {
+        for (int i = 0; i < RR_BUFS; i++) {
+            tc::mbar_init(enc_ready + i, NET_TILE);
+            tc::mbar_init(enc_free + i, 1);
+        }
+        tc::mbar_init(mma_bar, 1);
+        tc::fence_mbar_init();
+    }
+    if (warp == 0) tc::tmem_alloc<RR_TMEM_COLS>(tmem_slot);
+    tc::fence_proxy_async_smem();
+    tc::fence_before_thread_sync();
+    __syncthreads();
+    tc::fence_after_thread_sync();
+    const uint32_t tmem_base = *tmem_slot;
+    const uint32_t lane_sel = (uint32_t)(wk * 32) << 16;     // this warp's TMEM lane quarter
+    const uint32_t* tb = table32;
+    const int S = a.S;
+    const float inv_s = 1.0f / (float)S;
+    const bool pow2 = (S & (S - 1)) == 0;
+    const int log2s = 31 - __clz(S);
+    const int n_groups = (a.n_rays + 31) >> 5;
+    const int g_begin = blockIdx.x * RR_GROUPS_PER_CTA;
+    const int g_end = min(g_begin + RR_GROUPS_PER_CTA, n_groups);
+
+    if (warp >= 4) {
+        // ------------------------------------------------------------------ encoder group e
+        const int e = (warp >> 2) - 1;
+        int t_mod = 0;        // (tiles of the CTA before this ray group) mod RR_ENC_GROUPS
+        int m = 0;            // tiles this group has produced
+        for (int g = g_begin; g < g_end; g++) {
+            const int ray = g * 32 + lane;
+            int ns = 0;
+            long long first = 0;
+            if (ray < a.n_rays) {
+                ns = a.num_hits[ray] * S;
+                first = (long long)a.indices[ray];
+            }
+            int maxn = ns;
+#pragma unroll
+            for (int o = 16; o; o >>= 1) maxn = max(maxn, __shfl_xor_sync(0xffffffffu, maxn, o));
+            const int nt = (maxn + 3) >> 2;
+            int t0 = e - t_mod;
+            if (t0 < 0) t0 += RR_ENC_GROUPS;
+            for (int t = t0; t < nt; t += RR_ENC_GROUPS, m++) {
+                const int b = 2 * e + (m & 1);
+                const int q = 4 * t + wk;
+                const bool valid = q < ns;
+                float x01 = 0.f, y01 = 0.f, z01 = 0.f;
+                long long s = 0;
+                if (valid) {
+                    if (RENDER) {
+                        // sample position, sampler.cu:45-59
+                        const int j = pow2 ? (q >> log2s) : (q / S);
+                        const int i = q - j * S;
+                        const float* sp = a.start_points + 3 * (first + j);
+                        const float* ep = a.end_points + 3 * (first + j);
+                        const float sx = __ldg(sp), sy = __ldg(sp + 1), sz = __ldg(sp + 2);
+                        const float tt = rr_steps(inv_s, i, pow2);
+                        x01 = unit_coord(rn_fma(tt, rn_sub(__ldg(ep), sx), sx));
+                        y01 = unit_coord(rn_fma(tt, rn_sub(__ldg(ep + 1), sy), sy));
+                        z01 = unit_coord(rn_fma(tt, rn_sub(__ldg(ep + 2), sz), sz));
+                    } else {
+                        s = first * S + q;
+                        const float* p = a.samples + s * a.stride;
+                        x01 = unit_coord(ld_stream_f1(p));
+                        y01 = unit_coord(ld_stream_f1(p + 1));
+                        z01 = unit_coord(ld_stream_f1(p + 2));
+                    }
+                }
+                if (m >= 2) {      // the operand buffer is free once layer 0 of its previous tile has completed
+                    tc::mbar_wait(enc_free + b, (uint32_t)(((m >> 1) - 1) & 1));
+                    tc::fence_after_thread_sync();
+                }
+                const uint32_t t_e = tmem_base + lane_sel + (uint32_t)(RR_COL_AE + 16 * b);
+#pragma unroll 1
+                for (int p2 = 0; p2 < NET_IN / 4; p2++) {
+                    uint32_t f0 = 0u, f1 = 0u;
+                    if (valid) {
+                        rr_encode_pair(ll, lv, tb, 2 * p2, x01, y01, z01, f0, f1);
+                        if (!RENDER && a.encoded_out)
+                            *reinterpret_cast<uint2*>(a.encoded_out + s * NET_IN + 4 * p2) = make_uint2(f0, f1);
+                    }
+                    tc::tmem_st_x2(t_e + 2 * p2, f0, f1);
+                }
+                tc::tmem_st_wait();
+                tc::fence_before_thread_sync();
+                tc::mbar_arrive(enc_ready + b);
+            }
+            t_mod = (t_mod + nt) % RR_ENC_GROUPS;
+        }
+    } else {
+        // ------------------------------------------------------------------ MLP group
+        const uint32_t t_d = tmem_base + lane_sel + RR_COL_D;
+        const uint32_t t_ah = tmem_base + lane_sel + RR_COL_AH;
+        const uint32_t s_w0 = tc::smem_u32(smem + RrSmem::W0), s_w1 = tc::smem_u32(smem + RrSmem::W1),
+                       s_w2 = tc::smem_u32(smem + RrSmem::W2);
+        float4* exch = reinterpret_cast<float4*>(smem + RrSmem::EXCH);
+        uint32_t phase = 0;
+        int e = 0, m = 0;     // encoder group and per-group tile count of the next tile
+        int T = 0;
+        for (int g = g_begin; g < g_end; g++) {
+            const int ray = g * 32 + lane;
+            int ns = 0;
+            long long first = 0;
+            if (ray < a.n_rays) {
+                ns = a.num_hits[ray] * S;
+                first = (long long)a.indices[ray];
+            }
+            int maxn = ns;
+#pragma unroll
+            for (int o = 16; o; o >>= 1) maxn = max(maxn, __shfl_xor_sync(0xffffffffu, maxn, o));
+            const int nt = (maxn + 3) >> 2;
+
+            // compositing state of this lane's ray (warp 0), vol_render.cu:32-33
+            float tau = 0.0f, t_prev = 0.0f, ax = 0.0f, ay = 0.0f, az = 0.0f;
+            auto composite4 = [&](int buf, int q0) {
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    const int q = q0 + k;
+                    if (q < ns) {
+                        const float4 c = exch[(buf * 4 + k) * 32 + lane];
+                        const int i = pow2 ? (q & (S - 1)) : (q % S);
+                        const float tv = rn_add(rr_steps(inv_s, i, pow2), inv_s);   // sampler.cu:65-66 t_vals
+                        const float delta = fabsf(tv - t_prev);                       // vol_render.cu:56
+                        t_prev = tv;
+                        const float ds = delta * c.w;
+                        tau += ds;                                                    // :60
+                        const float w = expf(-tau) * (1.0f - expf(-ds));              // :61-63
+                        ax = fmaf(c.x, w, ax);                                        // :65-67
+                        ay = fmaf(c.y, w, ay);
+                        az = fmaf(c.z, w, az);
+                    }
+                }
+            };
+
+            for (int t = 0; t < nt; t++, T++) {
+                const int b = 2 * e + (m & 1);
+                // every row of the previous tile's output has been read (D is free) and, in render
+                // mode, its radiance is parked in exch
+                tc::fence_before_thread_sync();
+                rr_mlp_barrier();
+                if (tid == 0) {
+                    tc::mbar_wait(enc_ready + b, (uint32_t)((m >> 1) & 1));
+                    tc::fence_after_thread_sync();
+                    rr_issue_layer<NET_W, NET_IN>(tmem_base + RR_COL_D, tmem_base + RR_COL_AE + 16 * b, s_w0, mma_bar);
+                }
+                if (RENDER && wk == 0 && t > 0) composite4((T - 1) & 1, 4 * (t - 1));
+                tc::mbar_wait(mma_bar, phase);
+                phase ^= 1;
+                tc::fence_after_thread_sync();
+                if (tid == 0) tc::mbar_arrive(enc_free + b);
+                rr_hidden_epilogue(t_d, t_ah);
+                tc::fence_before_thread_sync();
+                rr_mlp_barrier();
+                if (tid == 0) {
+                    tc::fence_after_thread_sync();
+                    rr_issue_layer<NET_W, NET_W>(tmem_base + RR_COL_D, tmem_base + RR_COL_AH, s_w1, mma_bar);
+                }
+                tc::mbar_wait(mma_bar, phase);
+                phase ^= 1;
+                tc::fence_after_thread_sync();
+                rr_hidden_epilogue(t_d, t_ah);
+                tc::fence_before_thread_sync();
+                rr_mlp_barrier();
+                if (tid == 0) {
+                    tc::fence_after_thread_sync();
+                    rr_issue_layer<NET_OUT, NET_W>(tmem_base + RR_COL_D, tmem_base + RR_COL_AH, s_w2, mma_bar);
+                }
+                tc::mbar_wait(mma_bar, phase);
+                phase ^= 1;
+                tc::fence_after_thread_sync();
+                uint32_t r[16];
+                output_row_load(t_d, r);
+                if (RENDER) {
+                    exch[((T & 1) * 4 + wk) * 32 + lane] = output_row_rgba(r, a.out_activation);
+                } else {
+                    const int q = 4 * t + wk;
+                    if (q < ns) output_row_store(r, a.out_activation, first * S + q, a.out16, a.radiance4);
+                }
+                if (++e == RR_ENC_GROUPS) {
+                    e = 0;
+                    m++;
+                }
+            }
+            if (RENDER) {
+                if (nt > 0) {
+                    tc::fence_before_thread_sync();
+                    rr_mlp_barrier();
+                    tc::fence_after_thread_sync();
+                    if (wk == 0) composite4((T - 1) & 1, 4 * (nt - 1));
+                }
+                if (wk == 0 && ray < a.n_rays) {
+                    float* p = a.pixels + 3 * (long long)ray;     // vol_render.cu:70-72
+                    p[0] = ax;
+                    p[1] = ay;
+                    p[2] = az;
+                }
+            }
+        }
+    }
+    tc::fence_before_thread_sync();
+    __syncthreads();
+    tc::fence_after_thread_sync();
+    if (warp == 0) tc::tmem_dealloc<RR_TMEM_COLS>(tmem_base);
+}
+
+// launch helper shared by the two entry points (render_fused.cu, network_rays.cu)
+int rr_launch(bool render, const rtxnerf_hashgrid* enc, const rtxnerf_mlp* mlp, const Levels& lv, const RrArgs& a,
+              cudaStream_t stream);

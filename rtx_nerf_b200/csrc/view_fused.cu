@@ -159,7 +159,7 @@ view_fused_kernel(Levels lv, const uint32_t* __restrict__ table32, const uint16_
                 const float px = rn_fma(t, rn_sub(__ldg(b), sx), sx);
                 const float py = rn_fma(t, rn_sub(__ldg(b + 1), sy), sy);
                 const float pz = rn_fma(t, rn_sub(__ldg(b + 2), sz), sz);
-                const float x01 = rn_fma(px, 0.5f, 0.5f), y01 = rn_fma(py, 0.5f, 0.5f), z01 = rn_fma(pz, 0.5f, 0.5f);
+                const float x01 = unit_coord(px), y01 = unit_coord(py), z01 = unit_coord(pz);
 #pragma unroll 1
                 for (int c = 0; c < NET_IN / 8; c++) {
                     uint4 f;
@@ -230,10 +230,11 @@ view_fused_kernel(Levels lv, const uint32_t* __restrict__ table32, const uint16_
     if (warp == 0) tc::tmem_dealloc<VF_WGS * NET_TMEM_COLS>(*tmem_slot);
 }
 
-extern "C" int rtxnerf_render_rays_fused(const rtxnerf_hashgrid* enc, const rtxnerf_mlp* mlp,
-                                         const float* d_start_points, const float* d_end_points,
-                                         const int* d_num_hits, const int* d_indices, int n_rays,
-                                         int samples_per_segment, int sample_type, float* d_pixels, void* stream)
+// Round-1 kernel, kept for A/B measurements (RTXNERF_FUSED_V1=1); the product entry point is in
+// render_fused.cu.
+int vf1_render_rays_fused(const rtxnerf_hashgrid* enc, const rtxnerf_mlp* mlp, const float* d_start_points,
+                          const float* d_end_points, const int* d_num_hits, const int* d_indices, int n_rays,
+                          int samples_per_segment, int sample_type, float* d_pixels, void* stream)
 {
     if (!enc || !mlp || !mlp->weights || !d_start_points || !d_end_points || !d_num_hits || !d_indices || !d_pixels)
         return RTXNERF_EINVAL;
@@ -246,12 +247,8 @@ extern "C" int rtxnerf_render_rays_fused(const rtxnerf_hashgrid* enc, const rtxn
     if (rc) return rc;
     if (enc->n_levels * 2 > NET_IN) return RTXNERF_ECONFIG;
     if (n_rays == 0) return RTXNERF_OK;
-    static bool attr = false;
-    if (!attr) {
-        RTX_CUDA_TRY(cudaFuncSetAttribute(view_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                          VfSmem::BYTES));
-        attr = true;
-    }
+    static RtxPerDeviceOnce attr;
+    RTX_CUDA_TRY((cudaError_t)rtx_set_max_smem(attr, view_fused_kernel, VfSmem::BYTES));
     const long long groups = ((long long)n_rays + 31) / 32;
     long long blocks = (groups + VF_WGS - 1) / VF_WGS;
     // Not a resident-only grid: one CTA per VF_WGS groups (up to 64 CTAs per SM, 2 resident) lets the hardware
