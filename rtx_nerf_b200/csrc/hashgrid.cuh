@@ -356,15 +356,25 @@ __device__ __forceinline__ uint32_t encode_hashed_lean(const LevelK& k,
     const uint32_t yz[4] = {hy0 ^ hz0, hy1 ^ hz0, hy0 ^ hz1, hy1 ^ hz1};
     const bool odd00 = ((bx ^ by ^ bz) & 1u) != 0u;   // corner (x0, y0, z0) is the upper entry of its pair
     const bool split = (bx & 1u) != 0u;               // odd gx: x1 lies outside the pair of x0
+    // all eight loads are issued before the first select: with the x1 load written over the
+    // selected half of the pair (one register) ptxas issued it AFTER the pair had arrived, two
+    // dependent round trips per level (ncu source page, profiles/r02_b)
+    uint2 e[4];
+    uint32_t x1[4];
+#pragma unroll
+    for (int q = 0; q < 4; q++) e[q] = __ldg(reinterpret_cast<const uint2*>(entry_addr(lb, (bx ^ yz[q]) & mask_pair)));
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+        x1[q] = 0u;
+        if (split) x1[q] = __ldg(entry_addr(lb, (bx1 ^ yz[q]) & mask));
+    }
     uint32_t v[8];
 #pragma unroll
     for (int q = 0; q < 4; q++) {
-        const uint2 e = __ldg(reinterpret_cast<const uint2*>(entry_addr(lb, (bx ^ yz[q]) & mask_pair)));
         const bool odd = (q == 0 || q == 3) ? odd00 : !odd00;
-        v[2 * q] = odd ? e.y : e.x;
-        uint32_t other = odd ? e.x : e.y;
-        if (split) other = __ldg(entry_addr(lb, (bx1 ^ yz[q]) & mask));
-        v[2 * q + 1] = other;
+        v[2 * q] = odd ? e[q].y : e[q].x;
+        const uint32_t other = odd ? e[q].x : e[q].y;
+        v[2 * q + 1] = split ? x1[q] : other;
     }
     return blend8(v, wx, wy, wz);
 }
@@ -393,15 +403,21 @@ __device__ __forceinline__ uint32_t encode_dense_lean(const LevelK& k,
             v[c] = __ldg(entry_addr(lb, i));
         }
     } else {
+        uint2 e[4];
+        uint32_t x1[4];
+        bool odd[4];
 #pragma unroll
         for (int q = 0; q < 4; q++) {
             const uint32_t* pa = entry_addr(lb, idx[q] & ~1u);
-            const bool odd = (idx[q] & 1u) != 0u;
-            const uint2 e = __ldg(reinterpret_cast<const uint2*>(pa));
-            uint32_t other = e.y;
-            if (odd) other = __ldg(pa + 2);   // x1 opens the next pair
-            v[2 * q] = odd ? e.y : e.x;
-            v[2 * q + 1] = other;
+            odd[q] = (idx[q] & 1u) != 0u;
+            e[q] = __ldg(reinterpret_cast<const uint2*>(pa));
+            x1[q] = 0u;
+            if (odd[q]) x1[q] = __ldg(pa + 2);   // x1 opens the next pair
+        }
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            v[2 * q] = odd[q] ? e[q].y : e[q].x;
+            v[2 * q + 1] = odd[q] ? x1[q] : e[q].y;
         }
     }
     return blend8(v, wx, wy, wz);

@@ -27,9 +27,9 @@
 #include "hashgrid.cuh"
 #include "mlp_tile.cuh"
 
-#define RR_ENC_GROUPS 3
-#define RR_THREADS ((RR_ENC_GROUPS + 1) * NET_TILE)
-#define RR_BUFS (2 * RR_ENC_GROUPS)
+#define RR_MAX_ENC_GROUPS 5                                  // 96 + 2 * 5 * 16 = 256 TMEM columns
+#define RR_THREADS(EG) (((EG) + 1) * NET_TILE)
+#define RR_BUFS(EG) (2 * (EG))
 #define RR_COL_D 0
 #define RR_COL_AH 64
 #define RR_COL_AE 96
@@ -43,8 +43,8 @@ struct RrSmem {
     static constexpr int W1 = W0 + NET_W * NET_IN * 2;
     static constexpr int W2 = W1 + NET_W * NET_W * 2;
     static constexpr int EXCH = W2 + NET_OUT * NET_W * 2;            // [2][4][32] float4
-    static constexpr int BAR = EXCH + 2 * 4 * 32 * 16;               // enc_ready[6], enc_free[6], mma, tmem slot
-    static constexpr int BYTES = BAR + 8 * (2 * RR_BUFS + 1) + 16;
+    static constexpr int BAR = EXCH + 2 * 4 * 32 * 16;               // enc_ready[], enc_free[], mma, tmem slot
+    static constexpr int BYTES = BAR + 8 * (2 * RR_BUFS(RR_MAX_ENC_GROUPS) + 1) + 16;
 };
 
 struct RrArgs {
@@ -62,8 +62,16 @@ struct RrArgs {
     const int* num_hits;
     const int* indices;
     int n_rays, S, out_activation;
+    int wait_ticks;   // > 0: mbarrier waits carry this suspend-time hint (development knob)
+    int dev_skip;     // development only: bit 0 skips the compositing, bit 1 uses __expf in it (timing experiments)
+    int mlp_last;     // 1: the MLP group is the LAST four warps of the CTA (development knob, see rr_launch)
 };
 
+__device__ __forceinline__ void rr_wait(uint64_t* bar, uint32_t parity, int ticks)
+{
+    if (ticks > 0) tc::mbar_wait_sleep(bar, parity, (uint32_t)ticks);
+    else tc::mbar_wait(bar, parity);
+}
 __device__ __forceinline__ void rr_mlp_barrier() { asm volatile("bar.sync 1, %0;" ::"n"(NET_TILE) : "memory"); }
 
 // segment-local sample parameter after i steps of 1/S (sampler.cu:54-66: t += 1.0f/S)
@@ -140,23 +148,26 @@ __device__ __forceinline__ void rr_issue_layer(uint32_t d_tmem, uint32_t a_tmem,
     tc::mma_commit(bar);
 }
 
-template <bool RENDER>
-__global__ void __launch_bounds__(RR_THREADS, 2)
+template <bool RENDER, int EG>
+__global__ void __launch_bounds__(RR_THREADS(EG), 2)
 rays_roles_kernel(LeanLevels ll, Levels lv, const uint32_t* __restrict__ table32, const uint16_t* __restrict__ weights,
                   RrArgs a)
 {
     extern __shared__ __align__(128) uint8_t smem[];
     uint64_t* enc_ready = reinterpret_cast<uint64_t*>(smem + RrSmem::BAR);
-    uint64_t* enc_free = enc_ready + RR_BUFS;
-    uint64_t* mma_bar = enc_free + RR_BUFS;
+    uint64_t* enc_free = enc_ready + RR_BUFS(EG);
+    uint64_t* mma_bar = enc_free + RR_BUFS(EG);
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(mma_bar + 1);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, wk = warp & 3;
+    // role index: 0-3 the MLP group, 4.. the encoder groups
+    const int rw = a.mlp_last ? (warp >= 4 * EG ? warp - 4 * EG : warp + 4) : warp;
+    const bool mma_thread = rw == 0 && lane == 0;
 
-    load_weight_tile(smem + RrSmem::W0, weights, NET_W, NET_IN, tid, RR_THREADS);
-    load_weight_tile(smem + RrSmem::W1, weights + NET_W * NET_IN, NET_W, NET_W, tid, RR_THREADS);
-    load_weight_tile(smem + RrSmem::W2, weights + NET_W * NET_IN + NET_W * NET_W, NET_OUT, NET_W, tid, RR_THREADS);
+    load_weight_tile(smem + RrSmem::W0, weights, NET_W, NET_IN, tid, RR_THREADS(EG));
+    load_weight_tile(smem + RrSmem::W1, weights + NET_W * NET_IN, NET_W, NET_W, tid, RR_THREADS(EG));
+    load_weight_tile(smem + RrSmem::W2, weights + NET_W * NET_IN + NET_W * NET_W, NET_OUT, NET_W, tid, RR_THREADS(EG));
     if (tid == 0) {
-        for (int i = 0; i < RR_BUFS; i++) {
+        for (int i = 0; i < RR_BUFS(EG); i++) {
             tc::mbar_init(enc_ready + i, NET_TILE);
             tc::mbar_init(enc_free + i, 1);
         }
@@ -179,10 +190,10 @@ rays_roles_kernel(LeanLevels ll, Levels lv, const uint32_t* __restrict__ table32
     const int g_begin = blockIdx.x * RR_GROUPS_PER_CTA;
     const int g_end = min(g_begin + RR_GROUPS_PER_CTA, n_groups);
 
-    if (warp >= 4) {
+    if (rw >= 4) {
         // ------------------------------------------------------------------ encoder group e
-        const int e = (warp >> 2) - 1;
-        int t_mod = 0;        // (tiles of the CTA before this ray group) mod RR_ENC_GROUPS
+        const int e = (rw >> 2) - 1;
+        int t_mod = 0;        // (tiles of the CTA before this ray group) mod EG
         int m = 0;            // tiles this group has produced
         for (int g = g_begin; g < g_end; g++) {
             const int ray = g * 32 + lane;
@@ -197,8 +208,8 @@ rays_roles_kernel(LeanLevels ll, Levels lv, const uint32_t* __restrict__ table32
             for (int o = 16; o; o >>= 1) maxn = max(maxn, __shfl_xor_sync(0xffffffffu, maxn, o));
             const int nt = (maxn + 3) >> 2;
             int t0 = e - t_mod;
-            if (t0 < 0) t0 += RR_ENC_GROUPS;
-            for (int t = t0; t < nt; t += RR_ENC_GROUPS, m++) {
+            if (t0 < 0) t0 += EG;
+            for (int t = t0; t < nt; t += EG, m++) {
                 const int b = 2 * e + (m & 1);
                 const int q = 4 * t + wk;
                 const bool valid = q < ns;
@@ -225,7 +236,7 @@ rays_roles_kernel(LeanLevels ll, Levels lv, const uint32_t* __restrict__ table32
                     }
                 }
                 if (m >= 2) {      // the operand buffer is free once layer 0 of its previous tile has completed
-                    tc::mbar_wait(enc_free + b, (uint32_t)(((m >> 1) - 1) & 1));
+                    rr_wait(enc_free + b, (uint32_t)(((m >> 1) - 1) & 1), a.wait_ticks);
                     tc::fence_after_thread_sync();
                 }
                 const uint32_t t_e = tmem_base + lane_sel + (uint32_t)(RR_COL_AE + 16 * b);
@@ -243,7 +254,7 @@ rays_roles_kernel(LeanLevels ll, Levels lv, const uint32_t* __restrict__ table32
                 tc::fence_before_thread_sync();
                 tc::mbar_arrive(enc_ready + b);
             }
-            t_mod = (t_mod + nt) % RR_ENC_GROUPS;
+            t_mod = (t_mod + nt) % EG;
         }
     } else {
         // ------------------------------------------------------------------ MLP group
@@ -282,7 +293,8 @@ rays_roles_kernel(LeanLevels ll, Levels lv, const uint32_t* __restrict__ table32
                         t_prev = tv;
                         const float ds = delta * c.w;
                         tau += ds;                                                    // :60
-                        const float w = expf(-tau) * (1.0f - expf(-ds));              // :61-63
+                        const float w = (a.dev_skip & 2) ? __expf(-tau) * (1.0f - __expf(-ds))
+                                                         : expf(-tau) * (1.0f - expf(-ds));   // :61-63
                         ax = fmaf(c.x, w, ax);                                        // :65-67
                         ay = fmaf(c.y, w, ay);
                         az = fmaf(c.z, w, az);
@@ -296,34 +308,34 @@ rays_roles_kernel(LeanLevels ll, Levels lv, const uint32_t* __restrict__ table32
                 // mode, its radiance is parked in exch
                 tc::fence_before_thread_sync();
                 rr_mlp_barrier();
-                if (tid == 0) {
-                    tc::mbar_wait(enc_ready + b, (uint32_t)((m >> 1) & 1));
+                if (mma_thread) {
+                    rr_wait(enc_ready + b, (uint32_t)((m >> 1) & 1), a.wait_ticks);
                     tc::fence_after_thread_sync();
                     rr_issue_layer<NET_W, NET_IN>(tmem_base + RR_COL_D, tmem_base + RR_COL_AE + 16 * b, s_w0, mma_bar);
                 }
-                if (RENDER && wk == 0 && t > 0) composite4((T - 1) & 1, 4 * (t - 1));
-                tc::mbar_wait(mma_bar, phase);
+                if (RENDER && wk == 0 && t > 0 && !(a.dev_skip & 1)) composite4((T - 1) & 1, 4 * (t - 1));
+                rr_wait(mma_bar, phase, a.wait_ticks);
                 phase ^= 1;
                 tc::fence_after_thread_sync();
-                if (tid == 0) tc::mbar_arrive(enc_free + b);
+                if (mma_thread) tc::mbar_arrive(enc_free + b);
                 rr_hidden_epilogue(t_d, t_ah);
                 tc::fence_before_thread_sync();
                 rr_mlp_barrier();
-                if (tid == 0) {
+                if (mma_thread) {
                     tc::fence_after_thread_sync();
                     rr_issue_layer<NET_W, NET_W>(tmem_base + RR_COL_D, tmem_base + RR_COL_AH, s_w1, mma_bar);
                 }
-                tc::mbar_wait(mma_bar, phase);
+                rr_wait(mma_bar, phase, a.wait_ticks);
                 phase ^= 1;
                 tc::fence_after_thread_sync();
                 rr_hidden_epilogue(t_d, t_ah);
                 tc::fence_before_thread_sync();
                 rr_mlp_barrier();
-                if (tid == 0) {
+                if (mma_thread) {
                     tc::fence_after_thread_sync();
                     rr_issue_layer<NET_OUT, NET_W>(tmem_base + RR_COL_D, tmem_base + RR_COL_AH, s_w2, mma_bar);
                 }
-                tc::mbar_wait(mma_bar, phase);
+                rr_wait(mma_bar, phase, a.wait_ticks);
                 phase ^= 1;
                 tc::fence_after_thread_sync();
                 uint32_t r[16];
@@ -334,7 +346,7 @@ rays_roles_kernel(LeanLevels ll, Levels lv, const uint32_t* __restrict__ table32
                     const int q = 4 * t + wk;
                     if (q < ns) output_row_store(r, a.out_activation, first * S + q, a.out16, a.radiance4);
                 }
-                if (++e == RR_ENC_GROUPS) {
+                if (++e == EG) {
                     e = 0;
                     m++;
                 }
@@ -344,7 +356,7 @@ rays_roles_kernel(LeanLevels ll, Levels lv, const uint32_t* __restrict__ table32
                     tc::fence_before_thread_sync();
                     rr_mlp_barrier();
                     tc::fence_after_thread_sync();
-                    if (wk == 0) composite4((T - 1) & 1, 4 * (nt - 1));
+                    if (wk == 0 && !(a.dev_skip & 1)) composite4((T - 1) & 1, 4 * (nt - 1));
                 }
                 if (wk == 0 && ray < a.n_rays) {
                     float* p = a.pixels + 3 * (long long)ray;     // vol_render.cu:70-72

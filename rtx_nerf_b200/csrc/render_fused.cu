@@ -14,28 +14,44 @@ int vf1_render_rays_fused(const rtxnerf_hashgrid* enc, const rtxnerf_mlp* mlp, c
                           const float* d_end_points, const int* d_num_hits, const int* d_indices, int n_rays,
                           int samples_per_segment, int sample_type, float* d_pixels, void* stream);
 
-int rr_launch(bool render, const rtxnerf_hashgrid* enc, const rtxnerf_mlp* mlp, const Levels& lv, const RrArgs& a,
-              cudaStream_t stream)
+template <bool RENDER, int EG>
+static int rr_launch_t(const LeanLevels& ll, const Levels& lv, const rtxnerf_hashgrid* enc, const rtxnerf_mlp* mlp,
+                       const RrArgs& a, cudaStream_t stream)
 {
-    LeanLevels ll;
-    lean_levels_from(lv, &ll);
-    static RtxPerDeviceOnce attr_render, attr_staged;
-    if (render)
-        RTX_CUDA_TRY((cudaError_t)rtx_set_max_smem(attr_render, rays_roles_kernel<true>, RrSmem::BYTES));
-    else
-        RTX_CUDA_TRY((cudaError_t)rtx_set_max_smem(attr_staged, rays_roles_kernel<false>, RrSmem::BYTES));
+    static RtxPerDeviceOnce attr;
+    RTX_CUDA_TRY((cudaError_t)rtx_set_max_smem(attr, rays_roles_kernel<RENDER, EG>, RrSmem::BYTES));
     const long long groups = ((long long)a.n_rays + 31) / 32;
     // one CTA per RR_GROUPS_PER_CTA consecutive ray groups; 2 CTAs are resident per SM and the
     // hardware scheduler balances the rest
     const long long blocks = (groups + RR_GROUPS_PER_CTA - 1) / RR_GROUPS_PER_CTA;
     if (blocks > 0x7fffffffLL) return RTXNERF_EINVAL;
-    if (render)
-        rays_roles_kernel<true><<<(unsigned)blocks, RR_THREADS, RrSmem::BYTES, stream>>>(
-            ll, lv, reinterpret_cast<const uint32_t*>(enc->table), mlp->weights, a);
-    else
-        rays_roles_kernel<false><<<(unsigned)blocks, RR_THREADS, RrSmem::BYTES, stream>>>(
-            ll, lv, reinterpret_cast<const uint32_t*>(enc->table), mlp->weights, a);
+    rays_roles_kernel<RENDER, EG><<<(unsigned)blocks, RR_THREADS(EG), RrSmem::BYTES, stream>>>(
+        ll, lv, reinterpret_cast<const uint32_t*>(enc->table), mlp->weights, a);
     return rtx_launch_status();
+}
+
+int rr_launch(bool render, const rtxnerf_hashgrid* enc, const rtxnerf_mlp* mlp, const Levels& lv, const RrArgs& a_in,
+              cudaStream_t stream)
+{
+    LeanLevels ll;
+    lean_levels_from(lv, &ll);
+    // encoder groups per CTA (development knob): 3 = 64 registers, 4 = 48, 5 = 40
+    static const int eg = rtx_env_int("RTXNERF_RR_GROUPS", 3);
+    static const int mlp_last = rtx_env_int("RTXNERF_RR_MLP_LAST", 1);
+    RrArgs a = a_in;
+    a.mlp_last = mlp_last;
+    static const int wait_ticks = rtx_env_int("RTXNERF_RR_WAIT_TICKS", 0);
+    a.wait_ticks = wait_ticks;
+    static const int dev_skip = rtx_env_int("RTXNERF_RR_DEV_SKIP", 0);
+    a.dev_skip = dev_skip;
+    if (render) {
+        if (eg == 4) return rr_launch_t<true, 4>(ll, lv, enc, mlp, a, stream);
+        if (eg == 5) return rr_launch_t<true, 5>(ll, lv, enc, mlp, a, stream);
+        return rr_launch_t<true, 3>(ll, lv, enc, mlp, a, stream);
+    }
+    if (eg == 4) return rr_launch_t<false, 4>(ll, lv, enc, mlp, a, stream);
+    if (eg == 5) return rr_launch_t<false, 5>(ll, lv, enc, mlp, a, stream);
+    return rr_launch_t<false, 3>(ll, lv, enc, mlp, a, stream);
 }
 
 extern "C" int rtxnerf_render_rays_fused(const rtxnerf_hashgrid* enc, const rtxnerf_mlp* mlp,

@@ -51,6 +51,23 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity)
         : "memory");
 }
 
+// the same wait with a suspend-time hint: the thread may sleep in hardware up to `ticks` before
+// try_wait returns false, so a long wait costs a handful of issue slots instead of a poll loop
+__device__ __forceinline__ void mbar_wait_sleep(uint64_t* bar, uint32_t parity, uint32_t ticks)
+{
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t"
+        "}" ::"r"(smem_u32(bar)),
+        "r"(parity), "r"(ticks)
+        : "memory");
+}
+
 // ---- descriptors --------------------------------------------------------------------------
 // Shared-memory matrix descriptor, K-major, SWIZZLE_NONE ("interleaved" canonical layout):
 // 8x16-byte core matrices; LBO = byte distance between the two core matrices one MMA consumes
