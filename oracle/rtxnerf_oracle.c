@@ -605,7 +605,12 @@ void orc_hashgrid_encode(int L, int F, const float* scales, const uint32_t* ress
                 frac[k] = pos - fl;
                 g[k] = (uint32_t)(int)fl;
             }
-            float acc[8] = {0};
+            /* tiny-cuda-nn's N-linear interpolation (grid kernel): weight in fp32, cast to the
+             * parameter type, result = fma((T)weight, grid_val, result) in the parameter type
+             * (T = __half), corners in order c = cx | cy<<1 | cz<<2.  fma in fp16 = one rounding
+             * of the exact w*v + acc; a double holds that exactly wherever the rounding to fp16
+             * can depend on it (11-bit operands), so the cast below is the correctly rounded fma. */
+            _Float16 acc[8] = {0};
             for (int c = 0; c < 8; c++) {
                 float w = 1.0f;
                 uint32_t q[3];
@@ -620,9 +625,15 @@ void orc_hashgrid_encode(int L, int F, const float* scales, const uint32_t* ress
                 }
                 uint32_t idx = grid_index(q[0], q[1], q[2], ress[l], sizes[l]);
                 const uint16_t* e = table + ((size_t)offsets[l] + idx) * F;
-                for (int f = 0; f < F; f++) acc[f] = fmaf(w, orc_h2f(e[f]), acc[f]);
+                const _Float16 wh = (_Float16)w;
+                for (int f = 0; f < F; f++)
+                    acc[f] = (_Float16)((double)wh * (double)orc_h2f(e[f]) + (double)acc[f]);
             }
-            for (int f = 0; f < F; f++) encoded[(size_t)s * L * F + (size_t)l * F + f] = orc_f2h(acc[f]);
+            for (int f = 0; f < F; f++) {
+                uint16_t bits;
+                memcpy(&bits, &acc[f], 2);
+                encoded[(size_t)s * L * F + (size_t)l * F + f] = bits;
+            }
         }
     }
 }

@@ -29,6 +29,7 @@
 
 #define RR_MAX_ENC_GROUPS 5                                  // 96 + 2 * 5 * 16 = 256 TMEM columns
 #define RR_THREADS(EG) (((EG) + 1) * NET_TILE)
+#define RR_CTA_THREADS(EG, RENDER) (RR_THREADS(EG) + ((RENDER) ? 32 : 0))   // render mode: + the compositor warp
 #define RR_BUFS(EG) (2 * (EG))
 #define RR_COL_D 0
 #define RR_COL_AH 64
@@ -43,8 +44,8 @@ struct RrSmem {
     static constexpr int W1 = W0 + NET_W * NET_IN * 2;
     static constexpr int W2 = W1 + NET_W * NET_W * 2;
     static constexpr int EXCH = W2 + NET_OUT * NET_W * 2;            // [2][4][32] float4
-    static constexpr int BAR = EXCH + 2 * 4 * 32 * 16;               // enc_ready[], enc_free[], mma, tmem slot
-    static constexpr int BYTES = BAR + 8 * (2 * RR_BUFS(RR_MAX_ENC_GROUPS) + 1) + 16;
+    static constexpr int BAR = EXCH + 2 * 4 * 32 * 16;     // enc_ready[], enc_free[], mma, out_ready[2], out_free[2], tmem slot
+    static constexpr int BYTES = BAR + 8 * (2 * RR_BUFS(RR_MAX_ENC_GROUPS) + 5) + 16;
 };
 
 struct RrArgs {
@@ -63,7 +64,6 @@ struct RrArgs {
     const int* indices;
     int n_rays, S, out_activation;
     int wait_ticks;   // > 0: mbarrier waits carry this suspend-time hint (development knob)
-    int dev_skip;     // development only: bit 0 skips the compositing, bit 1 uses __expf in it (timing experiments)
     int mlp_last;     // 1: the MLP group is the LAST four warps of the CTA (development knob, see rr_launch)
 };
 
@@ -83,37 +83,12 @@ __device__ __forceinline__ float rr_steps(float inv_s, int i, bool pow2)
     return t;
 }
 
-// two consecutive levels of one sample -> two packed feature pairs
-__device__ __forceinline__ void rr_encode_pair(const LeanLevels& ll, const Levels& lv, const uint32_t* __restrict__ tb, int l,
-                                               float x01, float y01, float z01, uint32_t& f0, uint32_t& f1)
+// generic path (configurations the lean paths do not cover): one level through whichever path its mode allows
+__device__ __forceinline__ uint32_t rr_encode_generic(const Levels& lv, const uint32_t* __restrict__ tb, int l, float x01,
+                                                      float y01, float z01)
 {
-    f0 = 0u;
-    f1 = 0u;
-    if (ll.ok) {
-        if (l >= ll.n_dense && l + 1 < ll.n_levels) {
-            f0 = encode_hashed_lean(ll.k[l], tb, x01, y01, z01);
-            f1 = encode_hashed_lean(ll.k[l + 1], tb, x01, y01, z01);
-        } else if (l + 1 < ll.n_dense) {
-            f0 = encode_dense_lean(ll.k[l], tb, x01, y01, z01);
-            f1 = encode_dense_lean(ll.k[l + 1], tb, x01, y01, z01);
-        } else {
-            if (l < ll.n_levels)
-                f0 = l < ll.n_dense ? encode_dense_lean(ll.k[l], tb, x01, y01, z01)
-                                    : encode_hashed_lean(ll.k[l], tb, x01, y01, z01);
-            if (l + 1 < ll.n_levels)
-                f1 = l + 1 < ll.n_dense ? encode_dense_lean(ll.k[l + 1], tb, x01, y01, z01)
-                                        : encode_hashed_lean(ll.k[l + 1], tb, x01, y01, z01);
-        }
-    } else {
-        if (l < lv.n_levels) {
-            const __half2 h = encode_level_any(lv, reinterpret_cast<const char*>(tb), l, x01, y01, z01);
-            f0 = *reinterpret_cast<const uint32_t*>(&h);
-        }
-        if (l + 1 < lv.n_levels) {
-            const __half2 h = encode_level_any(lv, reinterpret_cast<const char*>(tb), l + 1, x01, y01, z01);
-            f1 = *reinterpret_cast<const uint32_t*>(&h);
-        }
-    }
+    const __half2 h = encode_level_any(lv, reinterpret_cast<const char*>(tb), l, x01, y01, z01);
+    return *reinterpret_cast<const uint32_t*>(&h);
 }
 
 // hidden-layer epilogue of one row: 64 fp32 accumulator columns -> ReLU -> fp16 -> 32 A columns
@@ -148,8 +123,11 @@ __device__ __forceinline__ void rr_issue_layer(uint32_t d_tmem, uint32_t a_tmem,
     tc::mma_commit(bar);
 }
 
-template <bool RENDER, int EG>
-__global__ void __launch_bounds__(RR_THREADS(EG), 2)
+// LPI = levels per loop iteration of the encoder (2: two levels' gathers in flight per thread, 1: half the
+// loop body, the instruction cache's share of the stalls goes down); LEAN = the lean encoding paths
+// (dense levels first, hashed power-of-two levels after), else the generic per-level dispatch.
+template <bool RENDER, int EG, int LPI, bool LEAN>
+__global__ void __launch_bounds__(RR_CTA_THREADS(EG, RENDER), 2)
 rays_roles_kernel(LeanLevels ll, Levels lv, const uint32_t* __restrict__ table32, const uint16_t* __restrict__ weights,
                   RrArgs a)
 {
@@ -157,21 +135,27 @@ rays_roles_kernel(LeanLevels ll, Levels lv, const uint32_t* __restrict__ table32
     uint64_t* enc_ready = reinterpret_cast<uint64_t*>(smem + RrSmem::BAR);
     uint64_t* enc_free = enc_ready + RR_BUFS(EG);
     uint64_t* mma_bar = enc_free + RR_BUFS(EG);
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(mma_bar + 1);
+    uint64_t* out_ready = mma_bar + 1;     // MLP group -> compositor: a tile's radiance is parked in exch[buf]
+    uint64_t* out_free = out_ready + 2;    // compositor -> MLP group: exch[buf] has been read
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(out_free + 2);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, wk = warp & 3;
-    // role index: 0-3 the MLP group, 4.. the encoder groups
-    const int rw = a.mlp_last ? (warp >= 4 * EG ? warp - 4 * EG : warp + 4) : warp;
+    // role index: 0-3 the MLP group, 4 .. 4 * EG + 3 the encoder groups, 4 * EG + 4 the compositor (render mode)
+    const int rw = warp >= 4 * (EG + 1) ? warp : (a.mlp_last ? (warp >= 4 * EG ? warp - 4 * EG : warp + 4) : warp);
     const bool mma_thread = rw == 0 && lane == 0;
 
-    load_weight_tile(smem + RrSmem::W0, weights, NET_W, NET_IN, tid, RR_THREADS(EG));
-    load_weight_tile(smem + RrSmem::W1, weights + NET_W * NET_IN, NET_W, NET_W, tid, RR_THREADS(EG));
-    load_weight_tile(smem + RrSmem::W2, weights + NET_W * NET_IN + NET_W * NET_W, NET_OUT, NET_W, tid, RR_THREADS(EG));
+    load_weight_tile(smem + RrSmem::W0, weights, NET_W, NET_IN, tid, RR_CTA_THREADS(EG, RENDER));
+    load_weight_tile(smem + RrSmem::W1, weights + NET_W * NET_IN, NET_W, NET_W, tid, RR_CTA_THREADS(EG, RENDER));
+    load_weight_tile(smem + RrSmem::W2, weights + NET_W * NET_IN + NET_W * NET_W, NET_OUT, NET_W, tid, RR_CTA_THREADS(EG, RENDER));
     if (tid == 0) {
         for (int i = 0; i < RR_BUFS(EG); i++) {
             tc::mbar_init(enc_ready + i, NET_TILE);
             tc::mbar_init(enc_free + i, 1);
         }
         tc::mbar_init(mma_bar, 1);
+        for (int i = 0; i < 2; i++) {
+            tc::mbar_init(out_ready + i, NET_TILE);
+            tc::mbar_init(out_free + i, 1);
+        }
         tc::fence_mbar_init();
     }
     if (warp == 0) tc::tmem_alloc<RR_TMEM_COLS>(tmem_slot);
@@ -190,7 +174,7 @@ rays_roles_kernel(LeanLevels ll, Levels lv, const uint32_t* __restrict__ table32
     const int g_begin = blockIdx.x * RR_GROUPS_PER_CTA;
     const int g_end = min(g_begin + RR_GROUPS_PER_CTA, n_groups);
 
-    if (rw >= 4) {
+    if (rw >= 4 && rw < 4 * (EG + 1)) {
         // ------------------------------------------------------------------ encoder group e
         const int e = (rw >> 2) - 1;
         int t_mod = 0;        // (tiles of the CTA before this ray group) mod EG
@@ -240,21 +224,129 @@ rays_roles_kernel(LeanLevels ll, Levels lv, const uint32_t* __restrict__ table32
                     tc::fence_after_thread_sync();
                 }
                 const uint32_t t_e = tmem_base + lane_sel + (uint32_t)(RR_COL_AE + 16 * b);
+                // feature pair(s) of level(s) l.. -> columns l.. of this row of the operand (and the training copy)
+                auto emit1 = [&](int l, uint32_t f) {
+                    if (!RENDER && a.encoded_out && valid) reinterpret_cast<uint32_t*>(a.encoded_out + s * NET_IN)[l] = f;
+                    tc::tmem_st_x1(t_e + l, f);
+                };
+                auto emit2 = [&](int l, uint32_t f0, uint32_t f1) {
+                    if (!RENDER && a.encoded_out && valid)
+                        *reinterpret_cast<uint2*>(a.encoded_out + s * NET_IN + 2 * l) = make_uint2(f0, f1);
+                    tc::tmem_st_x2(t_e + l, f0, f1);
+                };
+                int l = 0;
+                if (LEAN) {
+                    const int nd = ll.n_dense, nl = ll.n_levels;
+                    if (LPI == 2) {
 #pragma unroll 1
-                for (int p2 = 0; p2 < NET_IN / 4; p2++) {
-                    uint32_t f0 = 0u, f1 = 0u;
-                    if (valid) {
-                        rr_encode_pair(ll, lv, tb, 2 * p2, x01, y01, z01, f0, f1);
-                        if (!RENDER && a.encoded_out)
-                            *reinterpret_cast<uint2*>(a.encoded_out + s * NET_IN + 4 * p2) = make_uint2(f0, f1);
+                        for (; l + 1 < nd; l += 2) {
+                            uint32_t f0 = 0u, f1 = 0u;
+                            if (valid) {
+                                f0 = encode_dense_lean(ll.k[l], tb, x01, y01, z01);
+                                f1 = encode_dense_lean(ll.k[l + 1], tb, x01, y01, z01);
+                            }
+                            emit2(l, f0, f1);
+                        }
+                        if (l < nd) {     // odd number of dense levels: the boundary pair
+                            uint32_t f0 = 0u, f1 = 0u;
+                            if (valid) {
+                                f0 = encode_dense_lean(ll.k[l], tb, x01, y01, z01);
+                                if (l + 1 < nl) f1 = encode_hashed_lean(ll.k[l + 1], tb, x01, y01, z01);
+                            }
+                            emit2(l, f0, f1);
+                            l += 2;
+                        }
+#pragma unroll 1
+                        for (; l + 1 < nl; l += 2) {
+                            uint32_t f0 = 0u, f1 = 0u;
+                            if (valid) {
+                                f0 = encode_hashed_lean(ll.k[l], tb, x01, y01, z01);
+                                f1 = encode_hashed_lean(ll.k[l + 1], tb, x01, y01, z01);
+                            }
+                            emit2(l, f0, f1);
+                        }
+                        if (l < nl) {
+                            uint32_t f0 = 0u;
+                            if (valid) f0 = encode_hashed_lean(ll.k[l], tb, x01, y01, z01);
+                            emit2(l, f0, 0u);
+                            l += 2;
+                        }
+                    } else {
+#pragma unroll 1
+                        for (; l < nd; l++) {
+                            uint32_t f = 0u;
+                            if (valid) f = encode_dense_lean(ll.k[l], tb, x01, y01, z01);
+                            emit1(l, f);
+                        }
+#pragma unroll 1
+                        for (; l < nl; l++) {
+                            uint32_t f = 0u;
+                            if (valid) f = encode_hashed_lean(ll.k[l], tb, x01, y01, z01);
+                            emit1(l, f);
+                        }
                     }
-                    tc::tmem_st_x2(t_e + 2 * p2, f0, f1);
+                } else {
+#pragma unroll 1
+                    for (; l < lv.n_levels; l++) {
+                        uint32_t f = 0u;
+                        if (valid) f = rr_encode_generic(lv, tb, l, x01, y01, z01);
+                        emit1(l, f);
+                    }
                 }
+#pragma unroll 1
+                for (; l < NET_IN / 2; l++) emit1(l, 0u);     // fewer than 16 levels: the rest of the row is zero
                 tc::tmem_st_wait();
                 tc::fence_before_thread_sync();
                 tc::mbar_arrive(enc_ready + b);
             }
             t_mod = (t_mod + nt) % EG;
+        }
+    } else if (rw >= 4 * (EG + 1)) {
+        // ------------------------------------------------------------------ compositor warp (render mode)
+        // lane = ray.  Composites every tile front to back in the reference's own sequential order
+        // (vol_render.cu:55-67: delta carried across segments, tau includes the current sample), off the MLP
+        // group's chain: on that chain it was ~220 dependent instructions per tile on one warp while the other
+        // three waited at a barrier.
+        float4* exch = reinterpret_cast<float4*>(smem + RrSmem::EXCH);
+        int T = 0;
+        for (int g = g_begin; g < g_end; g++) {
+            const int ray = g * 32 + lane;
+            int ns = 0;
+            if (ray < a.n_rays) ns = a.num_hits[ray] * S;
+            int maxn = ns;
+#pragma unroll
+            for (int o = 16; o; o >>= 1) maxn = max(maxn, __shfl_xor_sync(0xffffffffu, maxn, o));
+            const int nt = (maxn + 3) >> 2;
+            float tau = 0.0f, t_prev = 0.0f, ax = 0.0f, ay = 0.0f, az = 0.0f;      // vol_render.cu:32-33
+            for (int t = 0; t < nt; t++, T++) {
+                const int buf = T & 1;
+                rr_wait(out_ready + buf, (uint32_t)((T >> 1) & 1), a.wait_ticks);
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    const int q = 4 * t + k;
+                    if (q < ns) {
+                        const float4 c = exch[(buf * 4 + k) * 32 + lane];
+                        const int i = pow2 ? (q & (S - 1)) : (q % S);
+                        const float tv = rn_add(rr_steps(inv_s, i, pow2), inv_s);   // sampler.cu:65-66 t_vals
+                        const float delta = fabsf(tv - t_prev);                       // vol_render.cu:56
+                        t_prev = tv;
+                        const float ds = delta * c.w;
+                        tau += ds;                                                    // :60
+                        const float w = expf(-tau) * (1.0f - expf(-ds));              // :61-63
+                        ax = fmaf(c.x, w, ax);                                        // :65-67
+                        ay = fmaf(c.y, w, ay);
+                        az = fmaf(c.z, w, az);
+                    }
+                }
+                __syncwarp();
+                if (lane == 0) tc::mbar_arrive(out_free + buf);
+            }
+            if (ray < a.n_rays) {
+                float* p = a.pixels + 3 * (long long)ray;     // vol_render.cu:70-72
+                p[0] = ax;
+                p[1] = ay;
+                p[2] = az;
+            }
         }
     } else {
         // ------------------------------------------------------------------ MLP group
@@ -278,34 +370,9 @@ rays_roles_kernel(LeanLevels ll, Levels lv, const uint32_t* __restrict__ table32
 #pragma unroll
             for (int o = 16; o; o >>= 1) maxn = max(maxn, __shfl_xor_sync(0xffffffffu, maxn, o));
             const int nt = (maxn + 3) >> 2;
-
-            // compositing state of this lane's ray (warp 0), vol_render.cu:32-33
-            float tau = 0.0f, t_prev = 0.0f, ax = 0.0f, ay = 0.0f, az = 0.0f;
-            auto composite4 = [&](int buf, int q0) {
-#pragma unroll
-                for (int k = 0; k < 4; k++) {
-                    const int q = q0 + k;
-                    if (q < ns) {
-                        const float4 c = exch[(buf * 4 + k) * 32 + lane];
-                        const int i = pow2 ? (q & (S - 1)) : (q % S);
-                        const float tv = rn_add(rr_steps(inv_s, i, pow2), inv_s);   // sampler.cu:65-66 t_vals
-                        const float delta = fabsf(tv - t_prev);                       // vol_render.cu:56
-                        t_prev = tv;
-                        const float ds = delta * c.w;
-                        tau += ds;                                                    // :60
-                        const float w = (a.dev_skip & 2) ? __expf(-tau) * (1.0f - __expf(-ds))
-                                                         : expf(-tau) * (1.0f - expf(-ds));   // :61-63
-                        ax = fmaf(c.x, w, ax);                                        // :65-67
-                        ay = fmaf(c.y, w, ay);
-                        az = fmaf(c.z, w, az);
-                    }
-                }
-            };
-
             for (int t = 0; t < nt; t++, T++) {
                 const int b = 2 * e + (m & 1);
-                // every row of the previous tile's output has been read (D is free) and, in render
-                // mode, its radiance is parked in exch
+                // every row of the previous tile's output has been read: D is free
                 tc::fence_before_thread_sync();
                 rr_mlp_barrier();
                 if (mma_thread) {
@@ -313,7 +380,6 @@ rays_roles_kernel(LeanLevels ll, Levels lv, const uint32_t* __restrict__ table32
                     tc::fence_after_thread_sync();
                     rr_issue_layer<NET_W, NET_IN>(tmem_base + RR_COL_D, tmem_base + RR_COL_AE + 16 * b, s_w0, mma_bar);
                 }
-                if (RENDER && wk == 0 && t > 0 && !(a.dev_skip & 1)) composite4((T - 1) & 1, 4 * (t - 1));
                 rr_wait(mma_bar, phase, a.wait_ticks);
                 phase ^= 1;
                 tc::fence_after_thread_sync();
@@ -341,7 +407,10 @@ rays_roles_kernel(LeanLevels ll, Levels lv, const uint32_t* __restrict__ table32
                 uint32_t r[16];
                 output_row_load(t_d, r);
                 if (RENDER) {
-                    exch[((T & 1) * 4 + wk) * 32 + lane] = output_row_rgba(r, a.out_activation);
+                    const int buf = T & 1;
+                    if (T >= 2) rr_wait(out_free + buf, (uint32_t)(((T >> 1) - 1) & 1), a.wait_ticks);
+                    exch[(buf * 4 + wk) * 32 + lane] = output_row_rgba(r, a.out_activation);
+                    tc::mbar_arrive(out_ready + buf);
                 } else {
                     const int q = 4 * t + wk;
                     if (q < ns) output_row_store(r, a.out_activation, first * S + q, a.out16, a.radiance4);
@@ -349,20 +418,6 @@ rays_roles_kernel(LeanLevels ll, Levels lv, const uint32_t* __restrict__ table32
                 if (++e == EG) {
                     e = 0;
                     m++;
-                }
-            }
-            if (RENDER) {
-                if (nt > 0) {
-                    tc::fence_before_thread_sync();
-                    rr_mlp_barrier();
-                    tc::fence_after_thread_sync();
-                    if (wk == 0 && !(a.dev_skip & 1)) composite4((T - 1) & 1, 4 * (nt - 1));
-                }
-                if (wk == 0 && ray < a.n_rays) {
-                    float* p = a.pixels + 3 * (long long)ray;     // vol_render.cu:70-72
-                    p[0] = ax;
-                    p[1] = ay;
-                    p[2] = az;
                 }
             }
         }

@@ -14,20 +14,36 @@ int vf1_render_rays_fused(const rtxnerf_hashgrid* enc, const rtxnerf_mlp* mlp, c
                           const float* d_end_points, const int* d_num_hits, const int* d_indices, int n_rays,
                           int samples_per_segment, int sample_type, float* d_pixels, void* stream);
 
-template <bool RENDER, int EG>
+template <bool RENDER, int EG, int LPI, bool LEAN>
 static int rr_launch_t(const LeanLevels& ll, const Levels& lv, const rtxnerf_hashgrid* enc, const rtxnerf_mlp* mlp,
                        const RrArgs& a, cudaStream_t stream)
 {
     static RtxPerDeviceOnce attr;
-    RTX_CUDA_TRY((cudaError_t)rtx_set_max_smem(attr, rays_roles_kernel<RENDER, EG>, RrSmem::BYTES));
+    RTX_CUDA_TRY((cudaError_t)rtx_set_max_smem(attr, rays_roles_kernel<RENDER, EG, LPI, LEAN>, RrSmem::BYTES));
     const long long groups = ((long long)a.n_rays + 31) / 32;
     // one CTA per RR_GROUPS_PER_CTA consecutive ray groups; 2 CTAs are resident per SM and the
     // hardware scheduler balances the rest
     const long long blocks = (groups + RR_GROUPS_PER_CTA - 1) / RR_GROUPS_PER_CTA;
     if (blocks > 0x7fffffffLL) return RTXNERF_EINVAL;
-    rays_roles_kernel<RENDER, EG><<<(unsigned)blocks, RR_THREADS(EG), RrSmem::BYTES, stream>>>(
+    rays_roles_kernel<RENDER, EG, LPI, LEAN><<<(unsigned)blocks, RR_CTA_THREADS(EG, RENDER), RrSmem::BYTES, stream>>>(
         ll, lv, reinterpret_cast<const uint32_t*>(enc->table), mlp->weights, a);
     return rtx_launch_status();
+}
+
+template <bool RENDER>
+static int rr_dispatch(const LeanLevels& ll, const Levels& lv, const rtxnerf_hashgrid* enc, const rtxnerf_mlp* mlp,
+                       const RrArgs& a, cudaStream_t stream)
+{
+    if (!ll.ok) return rr_launch_t<RENDER, 3, 1, false>(ll, lv, enc, mlp, a, stream);
+    // role layout (development knob RTXNERF_RR_LAYOUT = 10 * encoder groups + levels per iteration):
+    // 3 groups = 64 registers (56 with the compositor warp), 4 = 48
+    static const int layout = rtx_env_int("RTXNERF_RR_LAYOUT", 32);
+    switch (layout) {
+    case 31: return rr_launch_t<RENDER, 3, 1, true>(ll, lv, enc, mlp, a, stream);
+    case 41: return rr_launch_t<RENDER, 4, 1, true>(ll, lv, enc, mlp, a, stream);
+    case 42: return rr_launch_t<RENDER, 4, 2, true>(ll, lv, enc, mlp, a, stream);
+    default: return rr_launch_t<RENDER, 3, 2, true>(ll, lv, enc, mlp, a, stream);
+    }
 }
 
 int rr_launch(bool render, const rtxnerf_hashgrid* enc, const rtxnerf_mlp* mlp, const Levels& lv, const RrArgs& a_in,
@@ -35,23 +51,12 @@ int rr_launch(bool render, const rtxnerf_hashgrid* enc, const rtxnerf_mlp* mlp, 
 {
     LeanLevels ll;
     lean_levels_from(lv, &ll);
-    // encoder groups per CTA (development knob): 3 = 64 registers, 4 = 48, 5 = 40
-    static const int eg = rtx_env_int("RTXNERF_RR_GROUPS", 3);
-    static const int mlp_last = rtx_env_int("RTXNERF_RR_MLP_LAST", 1);
     RrArgs a = a_in;
+    static const int mlp_last = rtx_env_int("RTXNERF_RR_MLP_LAST", 1);
     a.mlp_last = mlp_last;
     static const int wait_ticks = rtx_env_int("RTXNERF_RR_WAIT_TICKS", 0);
     a.wait_ticks = wait_ticks;
-    static const int dev_skip = rtx_env_int("RTXNERF_RR_DEV_SKIP", 0);
-    a.dev_skip = dev_skip;
-    if (render) {
-        if (eg == 4) return rr_launch_t<true, 4>(ll, lv, enc, mlp, a, stream);
-        if (eg == 5) return rr_launch_t<true, 5>(ll, lv, enc, mlp, a, stream);
-        return rr_launch_t<true, 3>(ll, lv, enc, mlp, a, stream);
-    }
-    if (eg == 4) return rr_launch_t<false, 4>(ll, lv, enc, mlp, a, stream);
-    if (eg == 5) return rr_launch_t<false, 5>(ll, lv, enc, mlp, a, stream);
-    return rr_launch_t<false, 3>(ll, lv, enc, mlp, a, stream);
+    return render ? rr_dispatch<true>(ll, lv, enc, mlp, a, stream) : rr_dispatch<false>(ll, lv, enc, mlp, a, stream);
 }
 
 extern "C" int rtxnerf_render_rays_fused(const rtxnerf_hashgrid* enc, const rtxnerf_mlp* mlp,

@@ -171,6 +171,10 @@ __device__ __forceinline__ void tmem_st_x4(uint32_t taddr, uint32_t r0, uint32_t
                  "r"(r3)
                  : "memory");
 }
+__device__ __forceinline__ void tmem_st_x1(uint32_t taddr, uint32_t r0)
+{
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x1.b32 [%0], {%1};" ::"r"(taddr), "r"(r0) : "memory");
+}
 __device__ __forceinline__ void tmem_st_x2(uint32_t taddr, uint32_t r0, uint32_t r1)
 {
     asm volatile("tcgen05.st.sync.aligned.32x32b.x2.b32 [%0], {%1,%2};" ::"r"(taddr), "r"(r0), "r"(r1) : "memory");
