@@ -1,5 +1,5 @@
 #!/bin/bash
-O=gpurun_out/r02_h
+O=gpurun_out/r02_l
 mkdir -p $O
 python scripts/ab_fused.py --tag plain > $O/plain.txt 2>&1 &&
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:rays_roles -s 6 -c 1 -o $O/rr_full -f \
