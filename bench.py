@@ -34,6 +34,35 @@ WORKLOAD = dict(workload="configs[1]: one 800x800 view per step per GPU, 128^3 l
 FLOP_PER_SAMPLE = 14336          # 2*(32*64 + 64*64 + 64*16)
 
 
+def kernel_sources_sha16():
+    """Hash of the CUDA sources the .so is built from: ties an ncu capture to the kernels it measured."""
+    import glob
+    import hashlib
+    h = hashlib.sha256()
+    for f in sorted(glob.glob(os.path.join(ROOT, "rtx_nerf_b200", "csrc", "*.cu")) +
+                    glob.glob(os.path.join(ROOT, "rtx_nerf_b200", "csrc", "*.cuh"))):
+        h.update(os.path.basename(f).encode())
+        h.update(open(f, "rb").read())
+    return h.hexdigest()[:16]
+
+
+def ncu_traffic(stage):
+    """dram bytes per launch of `stage`'s kernel from the committed `ncu --set full` capture
+    (profiles/ncu_traffic.json, written by scripts/update_traffic.py from a capture of THIS round).  A capture
+    taken before the kernels last changed is refused loudly: (None, why)."""
+    tpath = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    if not os.path.exists(tpath):
+        return None, "no profiles/ncu_traffic.json"
+    d = json.load(open(tpath))
+    if d.get("sources_sha16") != kernel_sources_sha16():
+        why = ("STALE: profiles/ncu_traffic.json was captured for kernel sources %s (%s), the tree is at %s — "
+               "re-run scripts/update_traffic.py on a fresh capture" % (d.get("sources_sha16"), d.get("round"),
+                                                                        kernel_sources_sha16()))
+        sys.stderr.write("bench.py: roofline.traffic " + why + "\n")
+        return None, why
+    return d.get("traffic", {}).get(stage), "ncu --set full, %s" % d.get("capture")
+
+
 def peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -98,8 +127,9 @@ def scene():
 
 # ------------------------------------------------------------------------------------------- CPU arm
 def cpu_path(sample_rays, poses, nthreads, repeats=1):
-    """The hot path on host cores: oracle restatement (march via the exact DDA sweep, hash-grid +
-    MLP), with the reference's own host-compiled sampler / vol_render when oracle/_ref is present.
+    """The hot path on host cores: oracle restatement (march via the exact DDA sweep, sampler, hash-grid +
+    MLP) and the REFERENCE'S OWN host-compiled vol_render (oracle/_ref, any S) when it is present.  The
+    sample is a band of rows through the image centre (the top rows of a view mostly miss the scene).
     Returns (rays_per_s, samples_per_s, description)."""
     from oracle import oracle as orc
     from rtx_nerf_b200 import synth
@@ -111,20 +141,24 @@ def cpu_path(sample_rays, poses, nthreads, repeats=1):
     for i in range(repeats):
         pose = poses[i % len(poses)]
         t0 = time.perf_counter()
-        m = orc.ray_march_dda(pose, focal, W / H, W, H, occ, G, max_hits=HM, csr=True, rays=(0, sample_rays),
+        rb = max(0, (H // 2) * W - sample_rays // 2)
+        re = min(W * H, rb + sample_rays)
+        m = orc.ray_march_dda(pose, focal, W / H, W, H, occ, G, max_hits=HM, csr=True, rays=(rb, re),
                               nthreads=nthreads)
-        nh, idx = m.num_hits[:sample_rays], m.indices[:sample_rays]
-        s, t = orc.sampler(m.start_points, m.end_points, m.view_dirs[:sample_rays], nh, idx, S, 0, nthreads=nthreads)
+        nh, idx = m.num_hits[rb:re], m.indices[rb:re]
+        s, t = orc.sampler(m.start_points, m.end_points, m.view_dirs[rb:re], nh, idx, S, 0, nthreads=nthreads)
         enc = orc.hashgrid_encode(levels, table, s, nthreads=nthreads)
         _, rad = orc.mlp_forward(weights, 32, 64, 2, 1, enc, nthreads=nthreads)
-        if have_ref and S == 32:
-            orc.ref_volrender(rad, nh, idx, t, S)
+        if have_ref:
+            orc.ref_volrender(rad, nh, idx, t, S)      # vol_render.cu:19-73 compiled for the host
         else:
             orc.volrender(rad, nh, idx, t, S, nthreads=nthreads)
         t_total += time.perf_counter() - t0
         rays += sample_rays
         samples += s.shape[0]
-    return rays / t_total, samples / t_total, "first %d rays of an 800x800 view x %d" % (sample_rays, repeats)
+    return rays / t_total, samples / t_total, ("%d rays through the centre of an 800x800 view x %d%s"
+                                               % (sample_rays, repeats, "; compositing = the reference's own "
+                                                  "vol_render.cu on the host" if have_ref else ""))
 
 
 def run_reference(args):
@@ -150,9 +184,9 @@ def run_reference(args):
                 ms_per_step=1e3 * float(np.mean(t_steps)), higher_is_better=True, scaling="weak", vs_baseline=None,
                 dtype="f32", data="synthetic", impl="reference", config=WORKLOAD, samples_per_s=float(np.mean(samp_s)),
                 cpu_baseline=dict(value=v, unit="rays/s", cores=nthreads, kind="port",
-                                  sample="each step = first %d rays of one 800x800 view (CPU oracle: exact-DDA march, "
-                                         "sampler, hash-grid + MLP, compositing); OptiX / tiny-cuda-nn are unavailable "
-                                         "on this box so the reference's own march/MLP cannot run" % sample),
+                                  sample="each step = %s (CPU oracle: exact-DDA march, sampler, hash-grid + MLP); "
+                                         "OptiX / tiny-cuda-nn are unavailable on this box so the reference's own "
+                                         "march/MLP cannot run" % desc),
                 e2e=dict(value=v, unit="rays/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0), gpu_launches=0)
     print(json.dumps(line))
     return 0
@@ -316,6 +350,45 @@ def run_ours(args):
                       stages_ms=dict(march=ms2[0], sampler=ms2[1], network=ms2[2], composite=ms2[3]))
         del r2, fnet
 
+    # ---- BASELINE configs[4] (stress): 1920x1080 view, 512^3 grid at 10 % occupancy, up to 256 samples/ray
+    # (S = 4 x H_max = 64), through the network on the fused render path; N = 1 only, a short run
+    cfg5 = None
+    if not args.no_config5 and world == 1:
+        G5, W5, H5, S5, HM5 = 512, 1920, 1080, 4, 64
+        occ5 = synth.occupancy_bernoulli(G5, 0.10, seed=1)
+        grid5 = api.OccupancyGrid.from_occupancy(occ5, G5)
+        r5 = pipeline.ViewRenderer(grid5, W5, H5, focal, W5 / H5, S5, HM5, pipeline.NetworkRadiance(net))
+        for k in range(2):
+            r5.render_device(poses_dev[k % len(poses_dev)])
+        torch.cuda.synchronize()
+        n5 = 4
+        st5 = r5.stages(fused=True)
+        ev5 = [[torch.cuda.Event(enable_timing=True) for _ in range(len(st5) + 1)] for _ in range(n5)]
+        hits5 = 0
+        for k in range(n5):
+            r5.pose_dev.copy_(poses_dev[(args.warmup + k) % len(poses_dev)], non_blocking=True)
+            ev5[k][0].record()
+            for i, (_, fn) in enumerate(st5):
+                fn()
+                ev5[k][i + 1].record()
+            torch.cuda.synchronize()
+            hits5 += r5.total_hits()
+        ms5 = [float(np.mean([ev5[k][i].elapsed_time(ev5[k][i + 1]) for k in range(n5)])) for i in range(len(st5))]
+        R5, H5h = W5 * H5, hits5 / n5
+        N5 = H5h * S5
+        cfg5 = dict(workload="configs[4]: one 1920x1080 view, 512^3 Bernoulli(0.10) grid, S=4 x H_max=64 (<= 256 "
+                             "samples/ray), 16-level hash-grid + 2x64 fused MLP, fused render path",
+                    ms_per_view=sum(ms5), rays_per_s=R5 / (sum(ms5) * 1e-3), samples_per_s=N5 / (sum(ms5) * 1e-3),
+                    rays=R5, hits_per_ray=H5h / R5, samples=N5,
+                    stages={nme: dict(ms=ms) for (nme, _), ms in zip(st5, ms5)})
+        gb5 = (28 * R5 + 32 * H5h + G5 ** 3 / 8 + 64) / (ms5[0] * 1e-3) / 1e9
+        cfg5["stages"]["march"].update(bound="hbm", achieved=gb5, peak=pk["hbm"], unit="GB/s", frac=gb5 / pk["hbm"])
+        tf5 = FLOP_PER_SAMPLE * N5 / (ms5[1] * 1e-3) / 1e12
+        cfg5["stages"][st5[1][0]].update(bound="tensor", achieved=tf5, peak=pk["tf"], unit="TFLOP/s",
+                                         frac=tf5 / pk["tf"], samples_per_s=N5 / (ms5[1] * 1e-3))
+        del r5, grid5, occ5
+        torch.cuda.empty_cache()
+
     # ---- training step (BASELINE configs[3]): 2^18 rays x (S=4, H_max=32), fwd + bwd + Adam,
     # NCCL all-reduce of the flat fp32 gradient buffer when N > 1; a short run, reported beside
     # the headline
@@ -428,14 +501,12 @@ def run_ours(args):
         dom = max(stages, key=lambda k: stages[k]["ms"])
         d = stages[dom]
         # dram bytes per launch of the dominant kernel from the committed ncu --set full capture
-        traffic = None
-        tpath = os.path.join(ROOT, "profiles", "ncu_traffic.json")
-        if os.path.exists(tpath):
-            traffic = json.load(open(tpath)).get(dom)
+        traffic, traffic_src = ncu_traffic(dom)
         roofline = dict(kernel=dom, bound=d["bound"], achieved=d["achieved"], peak=d["peak"], unit=d["unit"],
-                        frac=d["frac"], traffic=traffic, peak_source=pk["src"],
+                        frac=d["frac"], traffic=traffic, traffic_source=traffic_src, peak_source=pk["src"],
                         note="achieved = algorithmic work per launch (SURVEY 8d) / mean CUDA-event duration of that "
-                             "stage inside the timed region; kernel share of the step = %.2f" % (d["ms"] / sum(stage_ms)))
+                             "stage in a separate eager (un-graphed) pass over %d views just before the timed "
+                             "region; kernel share of that pass = %.2f" % (n_stage_steps, d["ms"] / sum(stage_ms)))
         line = dict(metric="rays/s", value=value, unit="rays/s", n_gpus=world, steps=args.steps, warmup=args.warmup,
                     ms_per_step=ms_total / args.steps, higher_is_better=True, scaling="weak", vs_baseline=None,
                     dtype="f16 tensor-core MLP (fp32 accumulate), f32 march/sampler/compositing", data="synthetic",
@@ -451,7 +522,13 @@ def run_ours(args):
                     per_rank_ms=dict(timed=[round(x[0], 4) for x in per_rank], last_rehearsal=[round(x[1], 4) for x in per_rank]))
         if refnet:
             line["reference_network"] = refnet
+        if cfg5:
+            line["config5"] = cfg5
         if train:
+            # top level, so that the driver's per-N table carries the path that HAS a collective
+            line["train_step_ms"] = train["ms"]
+            line["train_step_store_fed_ms"] = train["shuffled_ms"]
+            line["train_rays_per_s"] = train["rays"] * world / (train["shuffled_ms"] * 1e-3)
             line["train_step"] = dict(
                 workload="configs[3]: 2^18 rays per GPU per step, S=4 x H_max=32 (128 samples/ray), network fwd+bwd, "
                          "compositing fwd+bwd, L2 loss, Adam; NCCL all-reduce(sum) of the fp32 gradient buffer",
@@ -485,6 +562,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     ap.add_argument("--no-train", action="store_true", help="skip the training-step leg (profiling runs)")
     ap.add_argument("--no-refnet", action="store_true", help="skip the Frequency + 8x128 network leg")
+    ap.add_argument("--no-config5", action="store_true", help="skip the 1920x1080 / 512^3 stress-configuration leg")
     ap.add_argument("--spinup", type=float, default=1.5, help="seconds of untimed load before the timed steps")
     ap.add_argument("--staged", action="store_true",
                     help="render through the separate sampler / network / compositing entry points instead of the "

@@ -30,15 +30,34 @@ class ViewRenderer:
                                    want_origins=False)
         N = self.cap * self.S
         self.N_cap = N
-        self.t_vals = torch.empty(N, dtype=torch.float32, device=dev)
-        self.samples = torch.empty((N, 5), dtype=torch.float32, device=dev)
-        self.radiance = torch.empty((N, 4), dtype=torch.float32, device=dev)
+        self._dev = dev
+        # the staged path's per-sample buffers (40 B per sample: 21 GB at config 5) are allocated on first use:
+        # the fused render path never touches them
+        self._t_vals = self._samples = self._radiance = None
         self.pixels = torch.empty((self.R, 3), dtype=torch.float32, device=dev)
         self.pose_dev = torch.empty(16, dtype=torch.float32, device=dev)
         self.pose_pinned = torch.empty(16, dtype=torch.float32).pin_memory()
         self.pixels_pinned = torch.empty((self.R, 3), dtype=torch.float32).pin_memory()
         march = 1 if max_hits <= 32 else 3
         self.launches_per_view = (march + 1) if self.can_fuse else (march + 1 + radiance.launches + 1)
+
+    @property
+    def t_vals(self):
+        if self._t_vals is None:
+            self._t_vals = torch.empty(self.N_cap, dtype=torch.float32, device=self._dev)
+        return self._t_vals
+
+    @property
+    def samples(self):
+        if self._samples is None:
+            self._samples = torch.empty((self.N_cap, 5), dtype=torch.float32, device=self._dev)
+        return self._samples
+
+    @property
+    def radiance(self):
+        if self._radiance is None:
+            self._radiance = torch.empty((self.N_cap, 4), dtype=torch.float32, device=self._dev)
+        return self._radiance
 
     # --- stages (all asynchronous on the current stream) -------------------------------
     def stage_march(self):

@@ -16,12 +16,12 @@ timeout 300 python scripts/freqnet_bench.py > $O/freqnet_bench.txt 2>&1
 timeout 300 python scripts/batch_bench.py > $O/batch_bench.txt 2>&1; echo "batch-bench rc=$?" | tee -a $O/rc.txt
 if [ "$2" != "noprof" ]; then
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/launches.csv \
-  python bench.py --steps 2 --warmup 3 --no-cpu --spinup 0 > $O/ncu_launch.log 2>&1; echo "ncu-list rc=$?" | tee -a $O/rc.txt
+  python bench.py --steps 2 --warmup 3 --no-cpu --no-config5 --spinup 0 > $O/ncu_launch.log 2>&1; echo "ncu-list rc=$?" | tee -a $O/rc.txt
 # full captures: one launch of each product kernel in the view (skip warm-up launches with -s)
 timeout 900 ncu --set full --clock-control none --import-source on -s 8 -c 4 -o $O/view_full -f \
-  python bench.py --steps 2 --warmup 3 --no-cpu --no-train --no-refnet --spinup 0 > $O/ncu_full.log 2>&1; echo "ncu-full rc=$?" | tee -a $O/rc.txt
+  python bench.py --steps 2 --warmup 3 --no-cpu --no-train --no-refnet --no-config5 --spinup 0 > $O/ncu_full.log 2>&1; echo "ncu-full rc=$?" | tee -a $O/rc.txt
 timeout 900 ncu --set full --clock-control none --import-source on -s 12 -c 4 -o $O/view_staged_full -f \
-  python bench.py --steps 2 --warmup 3 --no-cpu --no-train --no-refnet --spinup 0 --staged > $O/ncu_staged.log 2>&1; echo "ncu-staged rc=$?" | tee -a $O/rc.txt
+  python bench.py --steps 2 --warmup 3 --no-cpu --no-train --no-refnet --no-config5 --spinup 0 --staged > $O/ncu_staged.log 2>&1; echo "ncu-staged rc=$?" | tee -a $O/rc.txt
 timeout 900 ncu --set full --clock-control none --import-source on -s 24 -c 14 -o $O/train_full -f \
   python scripts/train_bench.py --steps 1 > $O/ncu_train.log 2>&1; echo "ncu-train rc=$?" | tee -a $O/rc.txt
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:batch_ -s 30 -c 3 -o $O/batch_full -f \

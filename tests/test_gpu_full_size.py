@@ -77,6 +77,41 @@ def test_config2_full_view_march_and_render(cuda_api, orc):
     fused = r.render_host(pose, fused=True)
     assert float((fused - staged).abs().max()) <= 4e-6
     assert float(staged.min()) >= 0.0 and float(staged.max()) <= 1.0 + 1e-5 and float(staged.std()) > 1e-3
+    # the same three 4096-ray bands through the ORACLE's network and compositing: the benchmarked view, fused
+    # and staged, against orc.hashgrid_encode -> mlp_forward -> volrender at north_star's 1e-3 (fp32 RGB)
+    fused_np, staged_np = fused.numpy(), staged.numpy()
+    w = synth.mlp_weights(seed=2)
+    for b in (0, 317 * W + 5, W * H - 4096):
+        o = orc.ray_march_dda(pose, focal, 1.0, W, H, occ, G, max_hits=HM, csr=True, rays=(b, b + 4096))
+        onh, oidx = o.num_hits[b:b + 4096], o.indices[b:b + 4096]
+        so, to = orc.sampler(o.start_points, o.end_points, o.view_dirs[b:b + 4096], onh, oidx, S)
+        _, rad = orc.mlp_forward(w, 32, 64, 2, 1, orc.hashgrid_encode(lv, table, so))
+        pxo = orc.volrender(rad, onh, oidx, to, S)
+        assert np.abs(fused_np[b:b + 4096] - pxo).max() < 1e-3, "fused render differs from the oracle on band %d" % b
+        assert np.abs(staged_np[b:b + 4096] - pxo).max() < 1e-3, "staged render differs from the oracle on band %d" % b
+
+
+def test_config2_full_view_reference_network_bands(cuda_api, orc):
+    """The same view through the reference's literal network (Frequency + 8 x 128, main.cu:47-68), ray-ordered:
+    three 4096-ray bands against orc.frequency_encode -> mlp_forward -> volrender.  Tolerance 2e-3: eight
+    fp16 hidden layers and a MUFU sine against the oracle's double-precision one (tests/test_gpu_freqnet.py)."""
+    from rtx_nerf_b200 import pipeline
+    api = cuda_api
+    G, W, H, S, HM = 128, 800, 800, 4, 16
+    occ = synth.occupancy_lego(G, seed=0)
+    grid = api.OccupancyGrid.from_occupancy(occ, G)
+    pose, focal = synth.poses(3, seed=123)[2], synth.focal_length()
+    fw = synth.mlp_weights(112, 128, 8, 16, seed=4)
+    fnet = api.FrequencyNetwork(fw)
+    r = pipeline.ViewRenderer(grid, W, H, focal, 1.0, S, HM, pipeline.FrequencyNetworkRadiance(fnet))
+    px = r.render_host(pose).numpy().copy()
+    for b in (0, 317 * W + 5, W * H - 4096):
+        o = orc.ray_march_dda(pose, focal, 1.0, W, H, occ, G, max_hits=HM, csr=True, rays=(b, b + 4096))
+        onh, oidx = o.num_hits[b:b + 4096], o.indices[b:b + 4096]
+        so, to = orc.sampler(o.start_points, o.end_points, o.view_dirs[b:b + 4096], onh, oidx, S)
+        _, rad = orc.mlp_forward(fw, 112, 128, 8, 1, orc.frequency_encode(so))
+        pxo = orc.volrender(rad, onh, oidx, to, S)
+        assert np.abs(px[b:b + 4096] - pxo).max() < 2e-3, "reference-network render differs on band %d" % b
 
 
 def test_config4_shape_one_pass_equals_two_pass_records(cuda_api, orc):

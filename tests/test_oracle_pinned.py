@@ -184,3 +184,48 @@ def test_live_reference_if_present(orc):
     assert np.array_equal(ref.num_hits, mine.num_hits)
     m = np.arange(3 * G)[None, :] < ref.num_hits[:, None]
     np.testing.assert_allclose(mine.t_end.reshape(144, -1)[m], ref.t_end.reshape(144, -1)[m], rtol=RTOL_T, atol=1e-6)
+
+
+def test_dda_equals_brute_sparse_128_lego(orc):
+    """the DDA oracle every 128^3 test trusts, against the all-primitives marcher on the
+    benchmark's own sparse 128^3 lego grid (~1e5 AABBs), bit for bit."""
+    G = 128
+    occ = synth.occupancy_lego(G, seed=0)
+    prim_ids = np.flatnonzero(occ).astype(np.int32)
+    aabb = orc.make_grid(G)[prim_ids]
+    focal = synth.focal_length()
+    pose = synth.poses(3, seed=123)[2]
+    W = H = 32
+    brute = orc.ray_march_brute(pose, focal, 1.0, W, H, aabb, prim_ids=prim_ids, arr_size=3 * G)
+    dda = orc.ray_march_dda(pose, focal, 1.0, W, H, occ, G)
+    assert brute.num_hits.sum() > 10 * W * H / 4
+    assert np.array_equal(brute.num_hits, dda.num_hits)
+    assert np.array_equal(brute.hit_prims, dda.hit_prims)
+    for k in ("t_start", "t_end", "start_points", "end_points"):
+        assert np.array_equal(getattr(brute, k), getattr(dda, k), equal_nan=True), k
+
+
+def test_live_reference_sparse_128_lego(orc):
+    """The reference's OWN optixPrograms.cu (host build, oracle/_ref) marching the sparse 128^3 lego grid
+    against the DDA oracle: hit counts exact; t / points to 1e-5 relative or 5e-6 absolute — g++ contracts
+    (plane - o) / d differently from nvcc, an ulp of the ~0.5 coordinates (6e-8) over a direction component of
+    ~0.02 is 3e-6, which is most of a t of 7e-5 across a cell corner."""
+    if orc.ref_host() is None:
+        pytest.skip("oracle/_ref/libref_host.so not built")
+    G = 128
+    occ = synth.occupancy_lego(G, seed=0)
+    prim_ids = np.flatnonzero(occ).astype(np.int32)
+    aabb = orc.make_grid(G)[prim_ids]
+    focal = synth.focal_length()
+    pose = synth.poses(3, seed=123)[2]
+    W = H = 24
+    arr = 3 * G
+    ref = orc.ref_ray_march(pose, focal, 1.0, W, H, G, aabb, arr)
+    mine = orc.ray_march_dda(pose, focal, 1.0, W, H, occ, G)
+    assert ref.num_hits.sum() > 0
+    assert np.array_equal(ref.num_hits, mine.num_hits)
+    m = np.arange(arr)[None, :] < ref.num_hits[:, None]
+    for k, c in (("t_start", 1), ("t_end", 1), ("start_points", 3), ("end_points", 3)):
+        a = getattr(mine, k).reshape(W * H, arr, c)[m]
+        b = getattr(ref, k).reshape(W * H, arr, c)[m]
+        np.testing.assert_allclose(a, b, rtol=RTOL_T, atol=5e-6, err_msg=k)
