@@ -28,7 +28,8 @@ extern "C" {
 
 enum {
     RTXNERF_OK = 0,
-    RTXNERF_EINVAL = -1,   /* null pointer / bad size */
+    RTXNERF_EINVAL = -1,   /* null pointer / bad size / a buffer that breaks the vector alignment its layout implies
+                              (16 bytes for [N][4] fp32 rows and sample rows, 8 for float2 / four-fp16 rows) */
     RTXNERF_EGRID = -2,    /* grid resolution not a power of two in [2, 1024] */
     RTXNERF_ECAPACITY = -3,/* caller-provided capacity too small */
     RTXNERF_ENOMEM = -4,
@@ -342,6 +343,13 @@ int rtxnerf_l2_loss(const float* d_pred, const float* d_target, long long n, flo
 int rtxnerf_adam_step(long long n, float* d_master, uint16_t* d_params, float* d_grads, float* d_m1,
                       float* d_m2, float grad_scale, float lr, float beta1, float beta2, float eps,
                       int step, void* stream);
+/* The same with tiny-cuda-nn's treatment of encoding parameters: the first n_encoding parameters (the hash
+ * table in this repo's [table | weights] layout) are left untouched — weight and both moments — in a step
+ * where their gradient is exactly zero, i.e. when no sample of the batch touched the entry; the remaining
+ * (matrix) parameters always take the update.  n_encoding = 0 is rtxnerf_adam_step. */
+int rtxnerf_adam_step_sparse(long long n, long long n_encoding, float* d_master, uint16_t* d_params,
+                             float* d_grads, float* d_m1, float* d_m2, float grad_scale, float lr, float beta1,
+                             float beta2, float eps, int step, void* stream);
 
 /* ------------------------------------------------------------------------------------
  * Seeded ray shuffle + batch assembly — replaces the front end of the reference's training

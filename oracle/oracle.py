@@ -337,14 +337,22 @@ def l2_loss(pred, target, loss_scale=1.0):
     return values, grads, float(values.astype(np.float64).sum())
 
 
-def adam_step(master, grads, m1, m2, grad_scale, lr, beta1, beta2, eps, step):
-    """tcnn Adam as configured at main.cu:40-46; returns (master, fp16 params, m1, m2)."""
-    g = np.asarray(grads, np.float32) * np.float32(grad_scale)
-    m1 = np.float32(beta1) * m1 + np.float32(1 - beta1) * g
-    m2 = np.float32(beta2) * m2 + np.float32(1 - beta2) * g * g
+def adam_step(master, grads, m1, m2, grad_scale, lr, beta1, beta2, eps, step, n_encoding=0):
+    """tcnn Adam as configured at main.cu:40-46; returns (master, fp16 params, m1, m2).  The first n_encoding
+    parameters are encoding parameters: tiny-cuda-nn's adam_step returns early for them when their gradient is
+    exactly zero (weight and both moments untouched)."""
+    g_raw = np.asarray(grads, np.float32)
+    g = g_raw * np.float32(grad_scale)
+    n1 = np.float32(beta1) * m1 + np.float32(1 - beta1) * g
+    n2 = np.float32(beta2) * m2 + np.float32(1 - beta2) * g * g
     lr_t = np.float32(lr * np.sqrt(1.0 - beta2 ** step) / (1.0 - beta1 ** step))
-    master = (master - lr_t * m1 / (np.sqrt(m2) + np.float32(eps))).astype(np.float32)
-    return master, master.astype(np.float16), m1.astype(np.float32), m2.astype(np.float32)
+    new = (master - lr_t * n1 / (np.sqrt(n2) + np.float32(eps))).astype(np.float32)
+    skip = np.zeros(g_raw.shape, bool)
+    skip[:n_encoding] = g_raw[:n_encoding] == 0
+    new = np.where(skip, np.asarray(master, np.float32), new).astype(np.float32)
+    n1 = np.where(skip, m1, n1).astype(np.float32)
+    n2 = np.where(skip, m2, n2).astype(np.float32)
+    return new, new.astype(np.float16), n1, n2
 
 
 # --------------------------------------------------------------------------- the reference itself, on the host

@@ -575,6 +575,35 @@ static inline uint32_t grid_index(uint32_t x, uint32_t y, uint32_t z, uint32_t r
     return idx % size;
 }
 
+/* fp16 fused multiply-add with one rounding, for operands that are fp16 values held in floats
+ * (HFMA2's per-lane semantics).  a*b is exact in fp32 (two 11-bit significands); the sum with c
+ * is rounded to fp32 TO ODD (TwoSum gives the exact error, the sticky bit goes into the last
+ * place), and a value rounded to odd at 24 bits rounds to fp16's 11 bits exactly as the
+ * infinitely precise one does.  Same results as (_Float16)((double)a*b + c) at a tenth of the
+ * cost: double -> fp16 is a library call on x86, fp32 -> fp16 is one F16C instruction. */
+static inline _Float16 hfma_rn(float a, float b, float c)
+{
+    const float p = a * b; /* exact */
+    const float s = p + c;
+    const float bv = s - p;
+    const float err = (p - (s - bv)) + (c - bv); /* TwoSum: p + c = s + err exactly */
+    uint32_t bits;
+    memcpy(&bits, &s, 4);
+    if (err != 0.0f && !(bits & 1u) && s == s && (bits & 0x7f800000u) != 0x7f800000u) {
+        const int same_sign = (err > 0.0f) == (s > 0.0f || (s == 0.0f && err > 0.0f));
+        if (s == 0.0f) {
+            /* |true value| = |err| > 0 below the smallest fp32 subnormal step of s: not reachable for fp16 inputs */
+        } else if (same_sign) {
+            bits |= 1u;
+        } else {
+            bits -= 1u;
+        }
+    }
+    float so;
+    memcpy(&so, &bits, 4);
+    return (_Float16)so;
+}
+
 /* [-1,1] -> [0,1] with the clamp of fma.rn.sat.f32 (hashgrid.cuh unit_coord): a position outside
  * the cube takes the features of its nearest face, a NaN those of 0, and no corner index can leave
  * its level (tiny-cuda-nn keeps indices in range with its modulo; this is the cheaper guard). */
@@ -607,9 +636,8 @@ void orc_hashgrid_encode(int L, int F, const float* scales, const uint32_t* ress
             }
             /* tiny-cuda-nn's N-linear interpolation (grid kernel): weight in fp32, cast to the
              * parameter type, result = fma((T)weight, grid_val, result) in the parameter type
-             * (T = __half), corners in order c = cx | cy<<1 | cz<<2.  fma in fp16 = one rounding
-             * of the exact w*v + acc; a double holds that exactly wherever the rounding to fp16
-             * can depend on it (11-bit operands), so the cast below is the correctly rounded fma. */
+             * (T = __half), corners in order c = cx | cy<<1 | cz<<2.  fma in fp16 = ONE rounding
+             * of the exact w*v + acc (hfma_rn above). */
             _Float16 acc[8] = {0};
             for (int c = 0; c < 8; c++) {
                 float w = 1.0f;
@@ -625,9 +653,8 @@ void orc_hashgrid_encode(int L, int F, const float* scales, const uint32_t* ress
                 }
                 uint32_t idx = grid_index(q[0], q[1], q[2], ress[l], sizes[l]);
                 const uint16_t* e = table + ((size_t)offsets[l] + idx) * F;
-                const _Float16 wh = (_Float16)w;
-                for (int f = 0; f < F; f++)
-                    acc[f] = (_Float16)((double)wh * (double)orc_h2f(e[f]) + (double)acc[f]);
+                const float wh = (float)(_Float16)w;
+                for (int f = 0; f < F; f++) acc[f] = hfma_rn(wh, orc_h2f(e[f]), (float)acc[f]);
             }
             for (int f = 0; f < F; f++) {
                 uint16_t bits;

@@ -113,6 +113,8 @@ SIGNATURES = {
     "rtxnerf_l2_loss": (c_int, [c_void_p, c_void_p, c_ll, c_float, c_void_p, c_void_p, c_void_p, c_void_p]),
     "rtxnerf_adam_step": (c_int, [c_ll, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_float, c_float,
                                   c_float, c_float, c_int, c_void_p]),
+    "rtxnerf_adam_step_sparse": (c_int, [c_ll, c_ll, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_float,
+                                         c_float, c_float, c_float, c_int, c_void_p]),
     "rtxnerf_ray_permutation": (c_int, [c_ll, C.c_ulonglong, c_int, c_ll, c_ll, c_void_p, c_void_p]),
     "rtxnerf_batch_workspace_bytes": (c_size_t, [c_ll]),
     "rtxnerf_batch_assemble": (c_int, [C.POINTER(RayStore), C.c_ulonglong, c_int, c_ll, c_ll, C.POINTER(Hits),

@@ -568,10 +568,12 @@ def l2_loss(pred, target, loss_scale, gradients, values=None, loss_sum=None, str
 
 
 def adam_step(master, params, grads, m1, m2, grad_scale, step, lr=1e-3, beta1=0.9, beta2=0.999, eps=1e-8,
-              stream=None):
-    """optimizer->step (main.cu:787) with the Adam config of main.cu:40-46; zeroes grads."""
+              stream=None, n_encoding=0):
+    """optimizer->step (main.cu:787) with the Adam config of main.cu:40-46; zeroes grads.  n_encoding: the first
+    n_encoding parameters are encoding (hash-table) entries, skipped in a step where their gradient is exactly
+    zero (tiny-cuda-nn's Adam)."""
     n = master.numel()
-    _lib.check(_lib.load().rtxnerf_adam_step(int(n), _p(master), _p(params), _p(grads), _p(m1), _p(m2),
-                                             float(grad_scale), float(lr), float(beta1), float(beta2), float(eps),
-                                             int(step), _stream_ptr(stream)), "adam_step")
+    _lib.check(_lib.load().rtxnerf_adam_step_sparse(int(n), int(n_encoding), _p(master), _p(params), _p(grads), _p(m1),
+                                                    _p(m2), float(grad_scale), float(lr), float(beta1), float(beta2),
+                                                    float(eps), int(step), _stream_ptr(stream)), "adam_step")
     _lib.count_launches(1 if n > 0 else 0)

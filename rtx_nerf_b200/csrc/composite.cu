@@ -151,6 +151,7 @@ extern "C" int rtxnerf_launch_volrender(const float* network_inputs, const float
     (void)network_inputs;  // unused by the reference too (vol_render.cu:20)
     if (!network_outputs || !num_hits || !indices || !ray_hit || !pixels) return RTXNERF_EINVAL;
     if (batch_size < 0 || num_samples_per_hit < 1) return RTXNERF_EINVAL;
+    if ((uintptr_t)network_outputs & 15u) return RTXNERF_EINVAL;     // read as float4 (r,g,b,sigma)
     if (batch_size == 0) return RTXNERF_OK;
     volrender_kernel<<<ray_warp_blocks(batch_size), COMP_WARPS * 32, 0, (cudaStream_t)stream>>>(
         network_outputs, num_hits, indices, ray_hit, batch_size, num_samples_per_hit, pixels);
@@ -167,6 +168,8 @@ extern "C" int rtxnerf_launch_volrender_backward(const float* loss_values, const
     if (!loss_gradients || !sampled_points_radiance || !t_hit || !num_hits || !indices || !radiance_gradients)
         return RTXNERF_EINVAL;
     if (batch_size < 0 || num_samples_per_hit < 1) return RTXNERF_EINVAL;
+    // float4 reads of the radiance, 8-byte stores of the four fp16 gradients
+    if (((uintptr_t)sampled_points_radiance & 15u) || ((uintptr_t)radiance_gradients & 7u)) return RTXNERF_EINVAL;
     if (batch_size == 0) return RTXNERF_OK;
     volrender_backward_kernel<<<ray_warp_blocks(batch_size), COMP_WARPS * 32, 0, (cudaStream_t)stream>>>(
         reinterpret_cast<const __half*>(loss_gradients), sampled_points_radiance, t_hit, num_hits, indices,
@@ -179,6 +182,7 @@ extern "C" int rtxnerf_cell_radiance(const int* d_hit_cells, const long long* d_
                                      const float* d_cell_rgbs4, float* d_radiance, void* stream)
 {
     if (!d_hit_cells || !d_total_hits || !d_cell_rgbs4 || !d_radiance) return RTXNERF_EINVAL;
+    if (((uintptr_t)d_cell_rgbs4 & 15u) || ((uintptr_t)d_radiance & 15u)) return RTXNERF_EINVAL;
     if (capacity_hits < 0 || samples_per_segment < 1) return RTXNERF_EINVAL;
     if (capacity_hits == 0) return RTXNERF_OK;
     cell_radiance_kernel<<<RTX_NUM_SMS * 8, 256, 0, (cudaStream_t)stream>>>(

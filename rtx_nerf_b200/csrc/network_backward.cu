@@ -469,13 +469,18 @@ __device__ __forceinline__ float adam_one(float g_raw, float& m1, float& m2, flo
     return __fsub_rn(w, __fdiv_rn(__fmul_rn(lr_t, a), __fadd_rn(__fsqrt_rn(b), eps)));
 }
 
-__global__ void adam_step_kernel(long long n, float* __restrict__ master, __half* __restrict__ params,
+// n_skip: the first n_skip elements (of this launch) are ENCODING parameters, which tiny-cuda-nn's Adam leaves
+// untouched — weight and both moments — in a step where their gradient is exactly zero (a hash-table entry no
+// sample of the batch touched); matrix weights always take the update.
+__global__ void adam_step_kernel(long long n, long long n_skip, float* __restrict__ master, __half* __restrict__ params,
                                  float* __restrict__ grads, float* __restrict__ m1, float* __restrict__ m2,
                                  float grad_scale, float lr_t, float beta1, float beta2, float eps)
 {
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
         float a = m1[i], b = m2[i];
-        const float w = adam_one(grads[i], a, b, master[i], grad_scale, lr_t, beta1, beta2, eps);
+        const float g = grads[i];
+        if (i < n_skip && g == 0.0f) continue;
+        const float w = adam_one(g, a, b, master[i], grad_scale, lr_t, beta1, beta2, eps);
         grads[i] = 0.0f;
         m1[i] = a;
         m2[i] = b;
@@ -488,16 +493,18 @@ __global__ void adam_step_kernel(long long n, float* __restrict__ master, __half
 // array is touched exactly once per step): the scalar loop above ran at 0.7 TB/s (0.62 ms for 12.2 M
 // parameters; every warp stalled on its loads, DRAM at 7 %), this one takes 0.19 ms.  Same adam_one
 // per element, so the same bits.
-__device__ __forceinline__ void adam_four(long long i, const float4& g, float4& a, float4& b, float4& w,
+__device__ __forceinline__ void adam_four(long long i, long long n_skip, const float4& g, float4& a, float4& b, float4& w,
                                           float4* __restrict__ master, uint2* __restrict__ params,
                                           float4* __restrict__ grads, float4* __restrict__ m1, float4* __restrict__ m2,
                                           float grad_scale, float lr_t, float beta1, float beta2, float eps)
 {
+    const long long e = 4 * i;       // first element of this group; elements below n_skip skip on a zero gradient
+    if (e + 3 < n_skip && g.x == 0.0f && g.y == 0.0f && g.z == 0.0f && g.w == 0.0f) return;   // nothing changes
     __stcs(grads + i, make_float4(0.0f, 0.0f, 0.0f, 0.0f));
-    w.x = adam_one(g.x, a.x, b.x, w.x, grad_scale, lr_t, beta1, beta2, eps);
-    w.y = adam_one(g.y, a.y, b.y, w.y, grad_scale, lr_t, beta1, beta2, eps);
-    w.z = adam_one(g.z, a.z, b.z, w.z, grad_scale, lr_t, beta1, beta2, eps);
-    w.w = adam_one(g.w, a.w, b.w, w.w, grad_scale, lr_t, beta1, beta2, eps);
+    if (!(e < n_skip && g.x == 0.0f)) w.x = adam_one(g.x, a.x, b.x, w.x, grad_scale, lr_t, beta1, beta2, eps);
+    if (!(e + 1 < n_skip && g.y == 0.0f)) w.y = adam_one(g.y, a.y, b.y, w.y, grad_scale, lr_t, beta1, beta2, eps);
+    if (!(e + 2 < n_skip && g.z == 0.0f)) w.z = adam_one(g.z, a.z, b.z, w.z, grad_scale, lr_t, beta1, beta2, eps);
+    if (!(e + 3 < n_skip && g.w == 0.0f)) w.w = adam_one(g.w, a.w, b.w, w.w, grad_scale, lr_t, beta1, beta2, eps);
     __stcs(m1 + i, a);
     __stcs(m2 + i, b);
     __stcs(master + i, w);
@@ -506,7 +513,7 @@ __device__ __forceinline__ void adam_four(long long i, const float4& g, float4& 
 }
 
 __global__ void __launch_bounds__(256)
-adam_step_vec4_kernel(long long n4, float4* __restrict__ master, uint2* __restrict__ params, float4* __restrict__ grads,
+adam_step_vec4_kernel(long long n4, long long n_skip, float4* __restrict__ master, uint2* __restrict__ params, float4* __restrict__ grads,
                       float4* __restrict__ m1, float4* __restrict__ m2, float grad_scale, float lr_t, float beta1,
                       float beta2, float eps)
 {
@@ -524,8 +531,8 @@ adam_step_vec4_kernel(long long n4, float4* __restrict__ master, uint2* __restri
         float4 a1 = two ? __ldcs(m1 + j) : z;
         float4 b1 = two ? __ldcs(m2 + j) : z;
         float4 w1 = two ? __ldcs(master + j) : z;
-        adam_four(i, g0, a0, b0, w0, master, params, grads, m1, m2, grad_scale, lr_t, beta1, beta2, eps);
-        if (two) adam_four(j, g1, a1, b1, w1, master, params, grads, m1, m2, grad_scale, lr_t, beta1, beta2, eps);
+        adam_four(i, n_skip, g0, a0, b0, w0, master, params, grads, m1, m2, grad_scale, lr_t, beta1, beta2, eps);
+        if (two) adam_four(j, n_skip, g1, a1, b1, w1, master, params, grads, m1, m2, grad_scale, lr_t, beta1, beta2, eps);
     }
 }
 
@@ -585,7 +592,16 @@ extern "C" int rtxnerf_adam_step(long long n, float* d_master, uint16_t* d_param
                                  float* d_m2, float grad_scale, float lr, float beta1, float beta2, float eps,
                                  int step, void* stream)
 {
+    return rtxnerf_adam_step_sparse(n, 0, d_master, d_params, d_grads, d_m1, d_m2, grad_scale, lr, beta1, beta2, eps,
+                                    step, stream);
+}
+
+extern "C" int rtxnerf_adam_step_sparse(long long n, long long n_encoding, float* d_master, uint16_t* d_params,
+                                        float* d_grads, float* d_m1, float* d_m2, float grad_scale, float lr,
+                                        float beta1, float beta2, float eps, int step, void* stream)
+{
     if (!d_master || !d_params || !d_grads || !d_m1 || !d_m2 || n < 0 || step < 1) return RTXNERF_EINVAL;
+    if (n_encoding < 0 || n_encoding > n) return RTXNERF_EINVAL;
     if (n == 0) return RTXNERF_OK;
     const float lr_t = lr * sqrtf(1.0f - powf(beta2, (float)step)) / (1.0f - powf(beta1, (float)step));
     static const int adam_scalar = rtx_env_int("RTXNERF_ADAM_SCALAR", 0);   // development knob
@@ -599,7 +615,7 @@ extern "C" int rtxnerf_adam_step(long long n, float* d_master, uint16_t* d_param
         long long blocks = (n4 + 255) / 256;
         if (blocks > RTX_NUM_SMS * 8) blocks = RTX_NUM_SMS * 8;
         adam_step_vec4_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(
-            n4, reinterpret_cast<float4*>(d_master), reinterpret_cast<uint2*>(d_params), reinterpret_cast<float4*>(d_grads),
+            n4, n_encoding, reinterpret_cast<float4*>(d_master), reinterpret_cast<uint2*>(d_params), reinterpret_cast<float4*>(d_grads),
             reinterpret_cast<float4*>(d_m1), reinterpret_cast<float4*>(d_m2), grad_scale, lr_t, beta1, beta2, eps);
         launched++;
     }
@@ -608,7 +624,7 @@ extern "C" int rtxnerf_adam_step(long long n, float* d_master, uint16_t* d_param
         long long blocks = (rest + 255) / 256;
         if (blocks > RTX_NUM_SMS * 16) blocks = RTX_NUM_SMS * 16;
         adam_step_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(
-            rest, d_master + done, reinterpret_cast<__half*>(d_params) + done, d_grads + done, d_m1 + done, d_m2 + done,
+            rest, n_encoding > done ? n_encoding - done : 0, d_master + done, reinterpret_cast<__half*>(d_params) + done, d_grads + done, d_m1 + done, d_m2 + done,
             grad_scale, lr_t, beta1, beta2, eps);
         launched++;
     }

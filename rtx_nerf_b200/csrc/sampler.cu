@@ -153,6 +153,9 @@ extern "C" int rtxnerf_launch_sampler_seeded(const float* d_start_points, const 
         !d_indices)
         return RTXNERF_EINVAL;
     if (batch_size < 0 || samples_per_segment < 1 || sample_type < 0 || sample_type > 2) return RTXNERF_EINVAL;
+    // the kernel moves whole 16-byte vectors (sample rows) and 8-byte view directions: a sub-buffer that breaks
+    // that alignment is refused here instead of faulting on the device
+    if (((uintptr_t)d_sampled_points & 15u) || ((uintptr_t)d_view_dirs & 7u)) return RTXNERF_EINVAL;
     if (batch_size == 0) return RTXNERF_OK;
     long long blocks = ((long long)batch_size + SAMPLER_WARPS - 1) / SAMPLER_WARPS;
     const long long max_blocks = (long long)RTX_NUM_SMS * 64;

@@ -263,7 +263,7 @@ class Trainer:
         self.step_count += 1
         api.adam_step(self.master, self.net.params, self.grads, self.m1, self.m2,
                       parallel.grad_scale(self.loss_scale, self.pg) if self.world > 1 else 1.0 / self.loss_scale,
-                      self.step_count, lr=self.lr)
+                      self.step_count, lr=self.lr, n_encoding=self.n_table)
 
     def step(self, pose_dev, ray_begin, target_dev):
         """pose (16 floats) and target pixels [n_rays][3] already on the device."""

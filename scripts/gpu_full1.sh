@@ -1,5 +1,5 @@
 #!/bin/bash
-O=gpurun_out/r02_m
+O=gpurun_out/r02_n
 mkdir -p $O
 timeout 1200 python -m pytest tests -m gpu -x -q > $O/pytest.log 2>&1; echo "pytest rc=$?" | tee -a $O/rc.txt
 timeout 300 python -c 'import __graft_entry__ as g; g.smoke()' > $O/smoke.log 2>&1; echo "smoke rc=$?" | tee -a $O/rc.txt

@@ -59,6 +59,12 @@ def test_argument_errors_need_no_gpu():
     assert lib.rtxnerf_grid_create(bits, 10, C.byref(h)) == -2
     assert lib.rtxnerf_launch_sampler(None, None, None, None, None, 4, 8, None, None, 0, 32, None) == -1
     assert lib.rtxnerf_launch_volrender(None, None, None, None, None, 4, 32, None, None) == -1
+    # a sub-buffer that breaks the vector alignment of its layout is refused on the host (never a device fault):
+    # addresses below are never dereferenced, the check precedes every CUDA call
+    ok, odd = 0x10000, 0x10004
+    assert lib.rtxnerf_launch_volrender(ok, odd, ok, ok, ok, 4, 32, ok, None) == -1          # [N][4] fp32 at +4
+    assert lib.rtxnerf_launch_sampler(ok, ok, ok, ok, odd, 4, 8, ok, ok, 0, 32, None) == -1   # sample rows at +4
+    assert lib.rtxnerf_launch_volrender_backward(ok, ok, ok, ok, ok, ok, 4, 32, odd, None) == -1
 
 
 def test_product_never_imports_oracle():

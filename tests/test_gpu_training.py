@@ -104,6 +104,31 @@ def test_l2_loss_and_adam_vs_oracle(cuda_api, orc):
         np.testing.assert_allclose(dm.cpu().numpy(), master, rtol=0, atol=2e-6)
         assert np.all(dg.cpu().numpy() == 0.0), "Adam must zero the gradient buffer"
         np.testing.assert_allclose(dp.cpu().numpy().astype(np.float32), p16.astype(np.float32), rtol=0, atol=2e-3)
+    # tiny-cuda-nn's treatment of encoding parameters: the first n_encoding entries skip the step (weight AND
+    # moments) when their gradient is exactly zero; n is odd-sized so that both kernels (vec4 body, scalar tail)
+    # and a group straddling n_encoding are exercised
+    n, n_enc = 4099, 2050
+    master = rng.normal(0, 0.1, n).astype(np.float32)
+    m1 = rng.normal(0, 0.01, n).astype(np.float32)
+    m2 = np.abs(rng.normal(0, 0.01, n)).astype(np.float32)
+    dm, dp = _t(master), torch.zeros(n, dtype=torch.float16, device="cuda")
+    d1, d2 = _t(m1), _t(m2)
+    for step in (1, 2):
+        g = (rng.normal(0, 1, n) * 64).astype(np.float32)
+        g[rng.random(n) < 0.6] = 0.0
+        dg = _t(g)
+        api.adam_step(dm, dp, dg, d1, d2, 1.0 / 128.0, step, n_encoding=n_enc)
+        torch.cuda.synchronize()
+        old = master.copy()
+        master, p16, m1, m2 = orc.adam_step(master, g, m1, m2, 1.0 / 128.0, 1e-3, 0.9, 0.999, 1e-8, step, n_encoding=n_enc)
+        got = dm.cpu().numpy()
+        np.testing.assert_allclose(got, master, rtol=0, atol=2e-6)
+        skipped = np.flatnonzero(g[:n_enc] == 0)
+        assert np.array_equal(got[skipped], old[skipped]), "skipped entries must keep their bits"
+        assert np.array_equal(d1.cpu().numpy()[skipped], m1[skipped]) and np.array_equal(d2.cpu().numpy()[skipped], m2[skipped])
+        moved = n_enc + np.flatnonzero(g[n_enc:] == 0)
+        assert np.all(got[moved] != old[moved]), "matrix weights take the step on stale momentum even at zero gradient"
+        assert np.all(dg.cpu().numpy() == 0.0)
 
 
 def test_trainer_step_gradients_vs_oracle_and_loss_decreases(cuda_api, orc):
