@@ -197,6 +197,18 @@ int rtxnerf_launch_volrender_backward(const float* loss_values, const uint16_t* 
                                       int num_samples_per_hit, uint16_t* radiance_gradients,
                                       void* stream);
 
+/* The same with an explicit gradient mode.  RTXNERF_BACKWARD_REFERENCE (0, what the entry point above runs) is
+ * the reference's own formula, vol_render.cu:118-135, kept bit for bit although it is NOT the gradient of the
+ * forward pass.  RTXNERF_BACKWARD_ANALYTIC (1) is the exact gradient of vol_render.cu:55-67
+ *   dL/dc_k = g w_k,   dL/dsigma_k = delta_k [exp(-tau_k - delta_k sigma_k) (g.c_k) - sum_{j>=k} w_j (g.c_j)],
+ * for callers that want the training step to descend the loss it reports.  Same buffers and layouts. */
+enum { RTXNERF_BACKWARD_REFERENCE = 0, RTXNERF_BACKWARD_ANALYTIC = 1 };
+int rtxnerf_launch_volrender_backward_mode(const float* loss_values, const uint16_t* loss_gradients,
+                                           const float* sampled_points_radiance, const float* t_hit,
+                                           const int* num_hits, const int* indices, int batch_size,
+                                           int num_samples_per_hit, uint16_t* radiance_gradients,
+                                           int backward_mode, void* stream);
+
 /* Config-1 stand-in for the network (BASELINE.json configs[0]): every sample takes the
  * fixed (r,g,b,sigma) of the cell its segment lies in.  n_hits is read from the device
  * scalar d_total_hits; at most capacity_hits segments are processed. */

@@ -92,6 +92,8 @@ SIGNATURES = {
                                          c_void_p, c_void_p]),
     "rtxnerf_launch_volrender_backward": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                                   c_int, c_int, c_void_p, c_void_p]),
+    "rtxnerf_launch_volrender_backward_mode": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                                       c_int, c_int, c_void_p, c_int, c_void_p]),
     "rtxnerf_cell_radiance": (c_int, [c_void_p, c_void_p, c_ll, c_int, c_void_p, c_void_p, c_void_p]),
     "rtxnerf_hashgrid_encode": (c_int, [C.POINTER(HashGrid), c_void_p, c_int, c_void_p, c_ll, c_ll, c_void_p,
                                         c_void_p]),

@@ -75,19 +75,26 @@ def launch_volrender_cuda(network_inputs, network_outputs, num_hits, indices, ra
     _lib.count_launches(1 if batch_size > 0 else 0)
 
 
+BACKWARD_REFERENCE, BACKWARD_ANALYTIC = 0, 1
+
+
 def launch_volrender_backward_cuda(loss_values, loss_gradients, sampled_points_radiance, t_hit, num_hits,
-                                   indices, batch_size, num_samples_per_hit, radiance_gradients, stream=None):
-    """vol_render/vol_render.h:15-25 (loss_values is unused, as in the reference)."""
+                                   indices, batch_size, num_samples_per_hit, radiance_gradients, stream=None,
+                                   backward_mode=BACKWARD_REFERENCE):
+    """vol_render/vol_render.h:15-25 (loss_values is unused, as in the reference).  backward_mode:
+    BACKWARD_REFERENCE = the reference's own formula (vol_render.cu:118-135, the default, parity mode);
+    BACKWARD_ANALYTIC = the exact gradient of the forward pass."""
     for t, dt, n in ((loss_gradients, torch.float16, "loss_gradients"),
                      (sampled_points_radiance, torch.float32, "sampled_points_radiance"),
                      (t_hit, torch.float32, "t_hit"), (num_hits, torch.int32, "num_hits"),
                      (indices, torch.int32, "indices"), (radiance_gradients, torch.float16, "radiance_gradients")):
         _chk_dev(t, dt, n)
     lib = _lib.load()
-    _lib.check(lib.rtxnerf_launch_volrender_backward(_p(loss_values), _p(loss_gradients),
-                                                     _p(sampled_points_radiance), _p(t_hit), _p(num_hits),
-                                                     _p(indices), int(batch_size), int(num_samples_per_hit),
-                                                     _p(radiance_gradients), _stream_ptr(stream)),
+    _lib.check(lib.rtxnerf_launch_volrender_backward_mode(_p(loss_values), _p(loss_gradients),
+                                                          _p(sampled_points_radiance), _p(t_hit), _p(num_hits),
+                                                          _p(indices), int(batch_size), int(num_samples_per_hit),
+                                                          _p(radiance_gradients), int(backward_mode),
+                                                          _stream_ptr(stream)),
                "launch_volrender_backward_cuda")
     _lib.count_launches(1 if batch_size > 0 else 0)
 

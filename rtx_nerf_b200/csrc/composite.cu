@@ -122,6 +122,97 @@ volrender_backward_kernel(const __half* __restrict__ loss_gradients, const float
     }
 }
 
+// ---------------------------------------------------------------------------------------
+// ANALYTIC backward (explicit, flagged mode; SURVEY Q16: vol_render.cu:118-135 is not the gradient
+// of :55-67, so a model trained with it need not converge).  The exact gradient of the forward above,
+//   tau_k = sum_{j<=k} delta_j sigma_j,  w_k = exp(-tau_k) (1 - exp(-delta_k sigma_k)),  C = sum_k w_k c_k:
+//   dL/dc_k     = g w_k
+//   dL/dsigma_k = delta_k [ exp(-tau_k - delta_k sigma_k) (g.c_k)  -  sum_{j>=k} w_j (g.c_j) ]
+// (sigma_k enters every later transmittance, and its own opacity term).  One warp per ray, two sweeps
+// over its samples: the first forms T = sum_j w_j (g.c_j), the second carries the exclusive prefix so
+// that the suffix sum is T - prefix.  Same I/O as the reference-mode kernel: fp16 loss gradients in,
+// four fp16 per sample out.  Bytes: 2 x 20 B/sample read + 8 B written.
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(COMP_WARPS * 32)
+volrender_backward_analytic_kernel(const __half* __restrict__ loss_gradients, const float* __restrict__ radiance,
+                                   const float* __restrict__ t_hit, const int* __restrict__ num_hits,
+                                   const int* __restrict__ indices, int batch_size, int S,
+                                   __half* __restrict__ radiance_gradients)
+{
+    const unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int warps_total = gridDim.x * COMP_WARPS;
+    for (int ray = blockIdx.x * COMP_WARPS + warp; ray < batch_size; ray += warps_total) {
+        const long long n = (long long)num_hits[ray] * S;
+        if (n <= 0) continue;
+        const long long base = (long long)indices[ray] * S;
+        const float4* rad = reinterpret_cast<const float4*>(radiance) + base;
+        const float* tv = t_hit + base;
+        uint2* out = reinterpret_cast<uint2*>(radiance_gradients) + base;
+        const float gx = __half2float(loss_gradients[3 * (long long)ray]);
+        const float gy = __half2float(loss_gradients[3 * (long long)ray + 1]);
+        const float gz = __half2float(loss_gradients[3 * (long long)ray + 2]);
+        float total = 0.0f;
+#pragma unroll 1
+        for (int sweep = 0; sweep < 2; sweep++) {
+            float carry_tau = 0.0f, carry_t = 0.0f, carry_a = 0.0f, acc = 0.0f;
+            for (long long q0 = 0; q0 < n; q0 += 32) {
+                const long long q = q0 + lane;
+                const bool valid = q < n;
+                float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
+                float t = carry_t;
+                if (valid) {
+                    c = __ldg(rad + q);          // read twice: keep the ray's samples in L1 for the second sweep
+                    t = __ldg(tv + q);
+                }
+                float t_prev = __shfl_up_sync(FULL, t, 1);
+                if (lane == 0) t_prev = carry_t;
+                const float delta = valid ? fabsf(t - t_prev) : 0.0f;
+                const float ds = delta * c.w;
+                float tau = ds;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const float nb = __shfl_up_sync(FULL, tau, o);
+                    if (lane >= o) tau += nb;
+                }
+                tau += carry_tau;
+                const float e_tau = expf(-tau), e_ds = expf(-ds);
+                const float w = e_tau * (1.0f - e_ds);
+                const float gc = gx * c.x + gy * c.y + gz * c.z;
+                const float a = w * gc;                       // this sample's share of g.C
+                if (sweep == 0) {
+                    acc += a;
+                } else {
+                    float pre = a;                            // inclusive prefix of a within the chunk
+#pragma unroll
+                    for (int o = 1; o < 32; o <<= 1) {
+                        const float nb = __shfl_up_sync(FULL, pre, o);
+                        if (lane >= o) pre += nb;
+                    }
+                    const float suffix = total - (carry_a + pre - a);     // sum_{j >= k} w_j (g.c_j)
+                    carry_a += __shfl_sync(FULL, pre, 31);
+                    if (valid) {
+                        const float dsig = delta * (e_tau * e_ds * gc - suffix);
+                        __half2 lo = __floats2half2_rn(gx * w, gy * w);
+                        __half2 hi = __floats2half2_rn(gz * w, dsig);
+                        uint2 pk;
+                        pk.x = *reinterpret_cast<unsigned*>(&lo);
+                        pk.y = *reinterpret_cast<unsigned*>(&hi);
+                        out[q] = pk;
+                    }
+                }
+                carry_tau = __shfl_sync(FULL, tau, 31);
+                carry_t = __shfl_sync(FULL, t, 31);
+            }
+            if (sweep == 0) {
+#pragma unroll
+                for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(FULL, acc, o);
+                total = acc;
+            }
+        }
+    }
+}
+
 __global__ void __launch_bounds__(256)
 cell_radiance_kernel(const int* __restrict__ hit_cells, const long long* __restrict__ total_hits,
                      long long capacity_hits, int S, const float4* __restrict__ cell_rgbs,
@@ -164,16 +255,33 @@ extern "C" int rtxnerf_launch_volrender_backward(const float* loss_values, const
                                                  int num_samples_per_hit, uint16_t* radiance_gradients,
                                                  void* stream)
 {
+    return rtxnerf_launch_volrender_backward_mode(loss_values, loss_gradients, sampled_points_radiance, t_hit, num_hits,
+                                                  indices, batch_size, num_samples_per_hit, radiance_gradients,
+                                                  RTXNERF_BACKWARD_REFERENCE, stream);
+}
+
+extern "C" int rtxnerf_launch_volrender_backward_mode(const float* loss_values, const uint16_t* loss_gradients,
+                                                      const float* sampled_points_radiance, const float* t_hit,
+                                                      const int* num_hits, const int* indices, int batch_size,
+                                                      int num_samples_per_hit, uint16_t* radiance_gradients,
+                                                      int backward_mode, void* stream)
+{
     (void)loss_values;  // unused by the reference too (vol_render.cu:76)
     if (!loss_gradients || !sampled_points_radiance || !t_hit || !num_hits || !indices || !radiance_gradients)
         return RTXNERF_EINVAL;
     if (batch_size < 0 || num_samples_per_hit < 1) return RTXNERF_EINVAL;
+    if (backward_mode != RTXNERF_BACKWARD_REFERENCE && backward_mode != RTXNERF_BACKWARD_ANALYTIC) return RTXNERF_EINVAL;
     // float4 reads of the radiance, 8-byte stores of the four fp16 gradients
     if (((uintptr_t)sampled_points_radiance & 15u) || ((uintptr_t)radiance_gradients & 7u)) return RTXNERF_EINVAL;
     if (batch_size == 0) return RTXNERF_OK;
-    volrender_backward_kernel<<<ray_warp_blocks(batch_size), COMP_WARPS * 32, 0, (cudaStream_t)stream>>>(
-        reinterpret_cast<const __half*>(loss_gradients), sampled_points_radiance, t_hit, num_hits, indices,
-        batch_size, num_samples_per_hit, reinterpret_cast<__half*>(radiance_gradients));
+    if (backward_mode == RTXNERF_BACKWARD_ANALYTIC)
+        volrender_backward_analytic_kernel<<<ray_warp_blocks(batch_size), COMP_WARPS * 32, 0, (cudaStream_t)stream>>>(
+            reinterpret_cast<const __half*>(loss_gradients), sampled_points_radiance, t_hit, num_hits, indices,
+            batch_size, num_samples_per_hit, reinterpret_cast<__half*>(radiance_gradients));
+    else
+        volrender_backward_kernel<<<ray_warp_blocks(batch_size), COMP_WARPS * 32, 0, (cudaStream_t)stream>>>(
+            reinterpret_cast<const __half*>(loss_gradients), sampled_points_radiance, t_hit, num_hits, indices,
+            batch_size, num_samples_per_hit, reinterpret_cast<__half*>(radiance_gradients));
     return rtx_launch_status();
 }
 

@@ -212,10 +212,12 @@ class Trainer:
     summed gradient — the all-reduce is the only exchange."""
 
     def __init__(self, grid, network, width, height, focal_length, aspect_ratio, samples_per_segment, max_hits,
-                 n_rays, loss_scale=128.0, lr=1e-3, process_group=None, device="cuda"):
+                 n_rays, loss_scale=128.0, lr=1e-3, process_group=None, device="cuda",
+                 backward_mode=api.BACKWARD_REFERENCE):
         self.net, self.S, self.R = network, int(samples_per_segment), int(n_rays)
         self.loss_scale, self.lr = float(loss_scale), float(lr)
         self.pg = process_group
+        self.backward_mode = int(backward_mode)     # compositing backward: the reference's formula or the exact gradient
         self.world = 1
         if process_group is not None:
             import torch.distributed as dist
@@ -250,7 +252,7 @@ class Trainer:
         v, h = self.view, self.view.hits
         api.l2_loss(v.pixels, self.target, self.loss_scale, self.loss_grad, loss_sum=self.loss_sum)
         api.launch_volrender_backward_cuda(None, self.loss_grad, v.radiance, v.t_vals, h.num_hits, h.indices,
-                                           self.R, self.S, self.radiance_grad)
+                                           self.R, self.S, self.radiance_grad, backward_mode=self.backward_mode)
         self.net.backward_rays(None, v.samples, self.encoded, self.radiance_grad, h.num_hits, h.indices, self.R,
                                self.S, h.total_hits, v.N_cap, self.dencoded, self.grads[:self.n_table],
                                self.grads[self.n_table:])
