@@ -63,6 +63,7 @@ struct RrArgs {
     const int* num_hits;
     const int* indices;
     int n_rays, S, out_activation;
+    int groups_per_cta;   // consecutive 32-ray groups one CTA walks
     int wait_ticks;   // > 0: mbarrier waits carry this suspend-time hint (development knob)
     int mlp_last;     // 1: the MLP group is the LAST four warps of the CTA (development knob, see rr_launch)
 };
@@ -171,8 +172,8 @@ rays_roles_kernel(LeanLevels ll, Levels lv, const uint32_t* __restrict__ table32
     const bool pow2 = (S & (S - 1)) == 0;
     const int log2s = 31 - __clz(S);
     const int n_groups = (a.n_rays + 31) >> 5;
-    const int g_begin = blockIdx.x * RR_GROUPS_PER_CTA;
-    const int g_end = min(g_begin + RR_GROUPS_PER_CTA, n_groups);
+    const int g_begin = blockIdx.x * a.groups_per_cta;
+    const int g_end = min(g_begin + a.groups_per_cta, n_groups);
 
     if (rw >= 4 && rw < 4 * (EG + 1)) {
         // ------------------------------------------------------------------ encoder group e

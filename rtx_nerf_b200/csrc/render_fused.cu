@@ -23,7 +23,7 @@ static int rr_launch_t(const LeanLevels& ll, const Levels& lv, const rtxnerf_has
     const long long groups = ((long long)a.n_rays + 31) / 32;
     // one CTA per RR_GROUPS_PER_CTA consecutive ray groups; 2 CTAs are resident per SM and the
     // hardware scheduler balances the rest
-    const long long blocks = (groups + RR_GROUPS_PER_CTA - 1) / RR_GROUPS_PER_CTA;
+    const long long blocks = (groups + a.groups_per_cta - 1) / a.groups_per_cta;
     if (blocks > 0x7fffffffLL) return RTXNERF_EINVAL;
     rays_roles_kernel<RENDER, EG, LPI, LEAN><<<(unsigned)blocks, RR_CTA_THREADS(EG, RENDER), RrSmem::BYTES, stream>>>(
         ll, lv, reinterpret_cast<const uint32_t*>(enc->table), mlp->weights, a);
@@ -54,6 +54,8 @@ int rr_launch(bool render, const rtxnerf_hashgrid* enc, const rtxnerf_mlp* mlp, 
     RrArgs a = a_in;
     static const int mlp_last = rtx_env_int("RTXNERF_RR_MLP_LAST", 1);
     a.mlp_last = mlp_last;
+    static const int gpc = rtx_env_int("RTXNERF_RR_GROUPS_PER_CTA", RR_GROUPS_PER_CTA);
+    a.groups_per_cta = gpc > 0 ? gpc : RR_GROUPS_PER_CTA;
     static const int wait_ticks = rtx_env_int("RTXNERF_RR_WAIT_TICKS", 0);
     a.wait_ticks = wait_ticks;
     return render ? rr_dispatch<true>(ll, lv, enc, mlp, a, stream) : rr_dispatch<false>(ll, lv, enc, mlp, a, stream);

@@ -1,8 +1,6 @@
 #!/bin/bash
-O=gpurun_out/r02_k
+O=gpurun_out/r02_r
 mkdir -p $O
-for cfg in 32 31 42; do
-  RTXNERF_RR_LAYOUT=$cfg timeout 300 python scripts/ab_fused.py --tag "layout$cfg" 2>&1 | grep -E "layout|fused |network|vs staged" | tee -a $O/sweep.txt
+for g in 2 4 8 16; do
+  RTXNERF_RR_GROUPS_PER_CTA=$g timeout 300 python scripts/ab_fused.py --tag "gpc$g" 2>&1 | grep -E "gpc|fused |network" | tee -a $O/sweep.txt
 done
-timeout 900 python -m pytest tests/test_gpu_network.py tests/test_gpu_full_size.py -x -q > $O/pytest.log 2>&1; echo "pytest rc=$?" | tee -a $O/rc.txt
-tail -5 $O/pytest.log
