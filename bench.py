@@ -204,6 +204,8 @@ def run_ours(args):
     assert torch.cuda.is_available(), "bench.py needs a GPU (no CPU fallback)"
     torch.cuda.set_device(local)
     if world > 1:
+        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"       # the version banner goes to stdout, where ONE JSON line is expected
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     _lib.load()
     pk = peaks()

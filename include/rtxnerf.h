@@ -345,6 +345,16 @@ int rtxnerf_network_backward_rays(const rtxnerf_hashgrid* enc, const rtxnerf_mlp
                                   const long long* d_count, long long n_max, uint16_t* d_dencoded,
                                   float* d_grad_table, float* d_grad_weights, void* stream);
 
+/* The same two kernels as separate calls (rtxnerf_network_backward_rays = the first, then the second on the same
+ * stream).  d_count * count_scale (capped at n_max) is the number of sample rows; a data-parallel caller
+ * all-reduces the MLP weight gradients after the first call, under the scatter of the second. */
+int rtxnerf_mlp_backward(const rtxnerf_mlp* mlp, const uint16_t* d_encoded, const uint16_t* d_dl_dradiance,
+                         const long long* d_count, long long count_scale, long long n_max, uint16_t* d_dencoded,
+                         float* d_grad_weights, void* stream);
+int rtxnerf_hashgrid_backward_rays(const rtxnerf_hashgrid* enc, const float* d_samples, int sample_stride,
+                                   const uint16_t* d_dencoded, const int* d_num_hits, const int* d_indices,
+                                   int n_rays, int samples_per_segment, float* d_grad_table, void* stream);
+
 /* values[i] = (pred-target)^2 / n (optional), gradients[i] = fp16(loss_scale * 2 (pred-target) / n),
  * *d_loss_sum += sum(values) (optional, caller-zeroed).  n = batch_size * 3. */
 int rtxnerf_l2_loss(const float* d_pred, const float* d_target, long long n, float loss_scale,

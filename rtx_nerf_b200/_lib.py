@@ -112,6 +112,10 @@ SIGNATURES = {
     "rtxnerf_network_backward_rays": (c_int, [C.POINTER(HashGrid), C.POINTER(Mlp), c_void_p, c_int, c_void_p,
                                               c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_ll, c_void_p,
                                               c_void_p, c_void_p, c_void_p]),
+    "rtxnerf_mlp_backward": (c_int, [C.POINTER(Mlp), c_void_p, c_void_p, c_void_p, c_ll, c_ll, c_void_p, c_void_p,
+                                     c_void_p]),
+    "rtxnerf_hashgrid_backward_rays": (c_int, [C.POINTER(HashGrid), c_void_p, c_int, c_void_p, c_void_p, c_void_p,
+                                               c_int, c_int, c_void_p, c_void_p]),
     "rtxnerf_l2_loss": (c_int, [c_void_p, c_void_p, c_ll, c_float, c_void_p, c_void_p, c_void_p, c_void_p]),
     "rtxnerf_adam_step": (c_int, [c_ll, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_float, c_float,
                                   c_float, c_float, c_int, c_void_p]),

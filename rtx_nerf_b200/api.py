@@ -566,6 +566,27 @@ class Network:
         _lib.count_launches(2 if n_rays > 0 and n_max > 0 else 0)
 
 
+def _network_stage_methods():
+    def mlp_backward(self, stream, encoded, dl_dradiance, samples_per_segment, d_count, n_max, dencoded, grad_weights):
+        """First stage of backward_rays alone: MLP dgrad + weight gradients (fp32, accumulated)."""
+        _lib.check(_lib.load().rtxnerf_mlp_backward(C.byref(self._mlp), _p(encoded), _p(dl_dradiance), _p(d_count),
+                                                    int(samples_per_segment), int(n_max), _p(dencoded),
+                                                    _p(grad_weights), _stream_ptr(stream)), "mlp_backward")
+
+    def hashgrid_backward_rays(self, stream, samples, dencoded, num_hits, indices, n_rays, samples_per_segment,
+                               grad_table):
+        """Second stage of backward_rays alone: dL/d features scattered into the table gradient."""
+        _lib.check(_lib.load().rtxnerf_hashgrid_backward_rays(
+            C.byref(self._hg), _p(samples), samples.shape[1], _p(dencoded), _p(num_hits), _p(indices), int(n_rays),
+            int(samples_per_segment), _p(grad_table), _stream_ptr(stream)), "hashgrid_backward_rays")
+
+    Network.mlp_backward = mlp_backward
+    Network.hashgrid_backward_rays = hashgrid_backward_rays
+
+
+_network_stage_methods()
+
+
 def l2_loss(pred, target, loss_scale, gradients, values=None, loss_sum=None, stream=None):
     """loss->evaluate + reduce_sum (main.cu:755-760): fp16 gradients, optional values / running sum."""
     n = pred.numel()

@@ -537,33 +537,38 @@ adam_step_vec4_kernel(long long n4, long long n_skip, float4* __restrict__ maste
 }
 
 // ------------------------------------------------------------------------------------ host ABI
-extern "C" int rtxnerf_network_backward_rays(const rtxnerf_hashgrid* enc, const rtxnerf_mlp* mlp,
-                                             const float* d_samples, int sample_stride, const uint16_t* d_encoded,
-                                             const uint16_t* d_dl_dradiance, const int* d_num_hits,
-                                             const int* d_indices, int n_rays, int samples_per_segment,
-                                             const long long* d_count, long long n_max, uint16_t* d_dencoded,
-                                             float* d_grad_table, float* d_grad_weights, void* stream)
+// The two stages of the network backward as separate entry points: a data-parallel caller issues the all-reduce
+// of the (28 KB) MLP weight gradients as soon as the first has finished, under the scatter of the second.
+extern "C" int rtxnerf_mlp_backward(const rtxnerf_mlp* mlp, const uint16_t* d_encoded, const uint16_t* d_dl_dradiance,
+                                    const long long* d_count, long long count_scale, long long n_max,
+                                    uint16_t* d_dencoded, float* d_grad_weights, void* stream)
 {
-    if (!enc || !mlp || !mlp->weights || !d_samples || !d_encoded || !d_dl_dradiance || !d_num_hits || !d_indices ||
-        !d_dencoded || !d_grad_table || !d_grad_weights)
-        return RTXNERF_EINVAL;
-    if (n_rays < 0 || samples_per_segment < 1 || sample_stride < 3 || n_max < 0) return RTXNERF_EINVAL;
+    if (!mlp || !mlp->weights || !d_encoded || !d_dl_dradiance || !d_dencoded || !d_grad_weights) return RTXNERF_EINVAL;
+    if (n_max < 0 || count_scale < 1) return RTXNERF_EINVAL;
     if (mlp->in_dim != NET_IN || mlp->width != NET_W || mlp->n_hidden != 2) return RTXNERF_ECONFIG;
     if (mlp->out_activation != 0 && mlp->out_activation != 1) return RTXNERF_ECONFIG;
+    if (n_max == 0) return RTXNERF_OK;
+    static RtxPerDeviceOnce attr_set;
+    RTX_CUDA_TRY((cudaError_t)rtx_set_max_smem(attr_set, mlp_backward_kernel, NbSmem::BYTES));
+    const long long tiles = (n_max + NET_TILE - 1) / NET_TILE;
+    const long long resident = (long long)RTX_NUM_SMS * 2;   // 2 CTAs per SM: 2 x 256 TMEM columns, 2 x 75 KB
+    mlp_backward_kernel<<<(unsigned)(tiles < resident ? tiles : resident), NET_TILE, NbSmem::BYTES, (cudaStream_t)stream>>>(
+        mlp->weights, d_encoded, d_dl_dradiance, mlp->out_activation, d_count, count_scale, n_max, d_dencoded,
+        d_grad_weights);
+    return rtx_launch_status();
+}
+
+extern "C" int rtxnerf_hashgrid_backward_rays(const rtxnerf_hashgrid* enc, const float* d_samples, int sample_stride,
+                                              const uint16_t* d_dencoded, const int* d_num_hits, const int* d_indices,
+                                              int n_rays, int samples_per_segment, float* d_grad_table, void* stream)
+{
+    if (!enc || !d_samples || !d_dencoded || !d_num_hits || !d_indices || !d_grad_table) return RTXNERF_EINVAL;
+    if (n_rays < 0 || samples_per_segment < 1 || sample_stride < 3) return RTXNERF_EINVAL;
     Levels lv;
     int rc = levels_from(enc, &lv);
     if (rc) return rc;
     if (enc->n_levels * 2 > NET_IN) return RTXNERF_ECONFIG;
-    if (n_rays == 0 || n_max == 0) return RTXNERF_OK;
-    static RtxPerDeviceOnce attr_set;
-    RTX_CUDA_TRY((cudaError_t)rtx_set_max_smem(attr_set, mlp_backward_kernel, NbSmem::BYTES));
-    cudaStream_t s = (cudaStream_t)stream;
-    const long long tiles = (n_max + NET_TILE - 1) / NET_TILE;
-    const long long resident = (long long)RTX_NUM_SMS * 2;   // 2 CTAs per SM: 2 x 256 TMEM columns, 2 x 75 KB
-    mlp_backward_kernel<<<(unsigned)(tiles < resident ? tiles : resident), NET_TILE, NbSmem::BYTES, s>>>(
-        mlp->weights, d_encoded, d_dl_dradiance, mlp->out_activation, d_count, samples_per_segment, n_max, d_dencoded,
-        d_grad_weights);
-    RTX_CUDA_TRY(cudaGetLastError());
+    if (n_rays == 0) return RTXNERF_OK;
     const long long groups = ((long long)n_rays + 31) / 32;
     // one CTA per 32-ray group up to 64 per SM: the hardware scheduler balances the groups (their sample counts
     // differ); a static grid-stride split over 8 CTAs per SM measured 2 % slower (10.61 -> 10.38 ms at 2^18 rays)
@@ -571,9 +576,32 @@ extern "C" int rtxnerf_network_backward_rays(const rtxnerf_hashgrid* enc, const 
 #define HB_BLOCKS_PER_SM 64
 #endif
     const long long max_blocks = (long long)RTX_NUM_SMS * HB_BLOCKS_PER_SM;
-    hashgrid_backward_kernel<<<(unsigned)(groups < max_blocks ? groups : max_blocks), HB_WARPS * 32, 0, s>>>(
-        lv, d_samples, sample_stride, d_dencoded, d_num_hits, d_indices, n_rays, samples_per_segment, d_grad_table);
-    return rtx_launch_status(2);
+    hashgrid_backward_kernel<<<(unsigned)(groups < max_blocks ? groups : max_blocks), HB_WARPS * 32, 0,
+                               (cudaStream_t)stream>>>(lv, d_samples, sample_stride, d_dencoded, d_num_hits, d_indices,
+                                                       n_rays, samples_per_segment, d_grad_table);
+    return rtx_launch_status();
+}
+
+extern "C" int rtxnerf_network_backward_rays(const rtxnerf_hashgrid* enc, const rtxnerf_mlp* mlp,
+                                             const float* d_samples, int sample_stride, const uint16_t* d_encoded,
+                                             const uint16_t* d_dl_dradiance, const int* d_num_hits,
+                                             const int* d_indices, int n_rays, int samples_per_segment,
+                                             const long long* d_count, long long n_max, uint16_t* d_dencoded,
+                                             float* d_grad_table, float* d_grad_weights, void* stream)
+{
+    if (!enc || !mlp || !d_samples || !d_num_hits || !d_indices || !d_grad_table) return RTXNERF_EINVAL;
+    if (n_rays < 0 || samples_per_segment < 1 || sample_stride < 3 || n_max < 0) return RTXNERF_EINVAL;
+    if (n_rays == 0 || n_max == 0) {      // argument errors are still reported for an empty batch
+        Levels lv;
+        if (!mlp->weights || !d_encoded || !d_dl_dradiance || !d_dencoded || !d_grad_weights) return RTXNERF_EINVAL;
+        if (mlp->in_dim != NET_IN || mlp->width != NET_W || mlp->n_hidden != 2) return RTXNERF_ECONFIG;
+        return levels_from(enc, &lv);
+    }
+    int rc = rtxnerf_mlp_backward(mlp, d_encoded, d_dl_dradiance, d_count, samples_per_segment, n_max, d_dencoded,
+                                  d_grad_weights, stream);
+    if (rc) return rc;
+    return rtxnerf_hashgrid_backward_rays(enc, d_samples, sample_stride, d_dencoded, d_num_hits, d_indices, n_rays,
+                                          samples_per_segment, d_grad_table, stream);
 }
 
 extern "C" int rtxnerf_l2_loss(const float* d_pred, const float* d_target, long long n, float loss_scale,

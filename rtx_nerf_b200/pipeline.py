@@ -217,6 +217,7 @@ class Trainer:
         self.net, self.S, self.R = network, int(samples_per_segment), int(n_rays)
         self.loss_scale, self.lr = float(loss_scale), float(lr)
         self.pg = process_group
+        self.overlap, self._side, self._reduced = True, None, False     # piecewise all-reduce on a side stream
         self.backward_mode = int(backward_mode)     # compositing backward: the reference's formula or the exact gradient
         self.world = 1
         if process_group is not None:
@@ -249,17 +250,45 @@ class Trainer:
         v.stage_composite()
 
     def backward(self):
+        """Loss, compositing backward, network backward.  With more than one rank the all-reduce is issued HERE,
+        piecewise on a side stream: the MLP weight gradients (28 KB) as soon as mlp_backward has finished, under
+        the scatter; the table gradient after the scatter.  allreduce() then only joins the side stream."""
         v, h = self.view, self.view.hits
         api.l2_loss(v.pixels, self.target, self.loss_scale, self.loss_grad, loss_sum=self.loss_sum)
         api.launch_volrender_backward_cuda(None, self.loss_grad, v.radiance, v.t_vals, h.num_hits, h.indices,
                                            self.R, self.S, self.radiance_grad, backward_mode=self.backward_mode)
-        self.net.backward_rays(None, v.samples, self.encoded, self.radiance_grad, h.num_hits, h.indices, self.R,
-                               self.S, h.total_hits, v.N_cap, self.dencoded, self.grads[:self.n_table],
-                               self.grads[self.n_table:])
+        if self.world == 1 or not self.overlap:
+            self.net.backward_rays(None, v.samples, self.encoded, self.radiance_grad, h.num_hits, h.indices, self.R,
+                                   self.S, h.total_hits, v.N_cap, self.dencoded, self.grads[:self.n_table],
+                                   self.grads[self.n_table:])
+            self._reduced = False
+            return
+        main = torch.cuda.current_stream()
+        if self._side is None:
+            self._side = torch.cuda.Stream()
+        self.net.mlp_backward(None, self.encoded, self.radiance_grad, self.S, h.total_hits, v.N_cap, self.dencoded,
+                              self.grads[self.n_table:])
+        ev = torch.cuda.Event()
+        ev.record(main)
+        self._side.wait_event(ev)
+        with torch.cuda.stream(self._side):
+            parallel.allreduce_sum_(self.grads[self.n_table:], self.pg)
+        self.net.hashgrid_backward_rays(None, v.samples, self.dencoded, h.num_hits, h.indices, self.R, self.S,
+                                        self.grads[:self.n_table])
+        ev2 = torch.cuda.Event()
+        ev2.record(main)
+        self._side.wait_event(ev2)
+        with torch.cuda.stream(self._side):
+            parallel.allreduce_sum_(self.grads[:self.n_table], self.pg)
+        self._reduced = True
 
     def allreduce(self):
         if self.world > 1:
-            parallel.allreduce_sum_(self.grads, self.pg)
+            if getattr(self, "_reduced", False):
+                torch.cuda.current_stream().wait_stream(self._side)     # issued in backward()
+                self._reduced = False
+            else:
+                parallel.allreduce_sum_(self.grads, self.pg)
 
     def optimizer_step(self):
         self.step_count += 1
