@@ -314,6 +314,15 @@ int rtxnerf_freqnet_forward(const rtxnerf_freqnet* net, const float* d_samples, 
                             const long long* d_count, long long count_scale, long long n_max,
                             uint16_t* d_out16, float* d_radiance4, void* stream);
 
+/* Backward of that network (network->backward, main.cu:781): fp32 gradients of the row-major weights (the
+ * layout of rtxnerf_freqnet_pack's input), ACCUMULATED into d_grad_weights (caller-zeroed; rtxnerf_adam_step
+ * re-zeroes).  The Frequency encoding has no parameters, so nothing else is produced.  d_dl_dradiance: fp16
+ * [n][4] as launch_volrender_backward_cuda writes it.  The forward is recomputed from d_samples per 128-row
+ * tile.  Rows as rtxnerf_freqnet_forward.  PARITY UNPINNED (tiny-cuda-nn absent). */
+int rtxnerf_freqnet_backward(const uint16_t* d_weights, int out_activation, const float* d_samples,
+                             int sample_stride, const uint16_t* d_dl_dradiance, const long long* d_count,
+                             long long count_scale, long long n_max, float* d_grad_weights, void* stream);
+
 /* Render path in ONE kernel: REGULAR sampling of the CSR segments (launchSampler,
  * sampler/sampler.cu:14-131), encoding + MLP forward (main.cu:715-728) and front-to-back
  * compositing (launch_volrender_cuda, vol_render/vol_render.cu:19-73) without the samples /

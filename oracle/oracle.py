@@ -308,6 +308,17 @@ def mlp_backward(weights_h, out_activation, enc_h, dl_dradiance_h):
     return d_enc.view(np.float16), gw
 
 
+def freqnet_backward(weights_h, out_activation, enc_h, dl_dradiance_h):
+    """-> grad_w float64 [131072] for the Frequency + 8 x 128 network (enc: fp16 [n][112])."""
+    w = np.ascontiguousarray(weights_h, np.float16).view(np.uint16)
+    enc = np.ascontiguousarray(enc_h, np.float16).view(np.uint16)
+    g = np.ascontiguousarray(dl_dradiance_h, np.float16).view(np.uint16)
+    gw = np.zeros(w.size, np.float64)
+    lib().orc_freqnet_backward(_ptr(w, _u16p), C.c_int(out_activation), _ptr(enc, _u16p), _ptr(g, _u16p),
+                               C.c_longlong(enc.shape[0]), _ptr(gw, C.POINTER(C.c_double)))
+    return gw
+
+
 def hashgrid_backward(levels, samples, d_enc_h):
     """-> grad_table float64 [n_entries][2]."""
     L = levels["n_levels"]

@@ -811,6 +811,76 @@ void orc_mlp_backward(const uint16_t* weights, int out_activation, const uint16_
     free(wf);
 }
 
+/* Backward of the reference's literal network (Composite Frequency -> 8 x 128 ReLU -> 16, main.cu:47-68,781),
+ * weight gradients only (the encoding has no parameters).  Same rounding points as the CUDA path:
+ * fp16 activations, fp16 dOut, fp16 activation gradients after the ReLU mask, wide accumulation.
+ * weights: row-major [128][112], 7 x [128][128], [16][128]; enc: [n][112] fp16 (orc_frequency_encode).
+ * PARITY UNPINNED (tiny-cuda-nn absent); pinned to fp64 autograd in tests/test_oracle_autograd.py. */
+void orc_freqnet_backward(const uint16_t* weights, int out_activation, const uint16_t* enc,
+                          const uint16_t* dl_dradiance, long long n, double* grad_w)
+{
+    enum { IN = 112, W = 128, H = 8, OUT = 16 };
+    const size_t wsz = (size_t)W * IN + (size_t)(H - 1) * W * W + (size_t)OUT * W;
+    float* wf = (float*)malloc(sizeof(float) * wsz);
+    for (size_t i = 0; i < wsz; i++) wf[i] = orc_h2f(weights[i]);
+    size_t off[H + 1];
+    off[0] = 0;
+    off[1] = (size_t)W * IN;
+    for (int l = 2; l <= H; l++) off[l] = off[l - 1] + (size_t)W * W;
+    memset(grad_w, 0, sizeof(double) * wsz);
+    float (*x)[W] = malloc(sizeof(float) * W * (H + 1));
+    for (long long s = 0; s < n; s++) {
+        /* forward: x[0] = encoding (112), x[l+1] = fp16(relu(W_l x[l])) */
+        for (int k = 0; k < IN; k++) x[0][k] = orc_h2f(enc[(size_t)s * IN + k]);
+        for (int l = 0; l < H; l++) {
+            const int K = l == 0 ? IN : W;
+            const float* w = wf + off[l];
+            for (int r = 0; r < W; r++) {
+                double acc = 0.0;
+                for (int k = 0; k < K; k++) acc += (double)w[(size_t)r * K + k] * x[l][k];
+                float v = (float)acc;
+                x[l + 1][r] = orc_h2f(orc_f2h(v > 0.f ? v : 0.f));
+            }
+        }
+        float dz[W], dprev[W], dout[OUT];
+        const float* w8 = wf + off[H];
+        for (int r = 0; r < OUT; r++) {
+            dout[r] = 0.f;
+            if (r >= 4) continue;
+            double acc = 0.0;
+            for (int k = 0; k < W; k++) acc += (double)w8[(size_t)r * W + k] * x[H][k];
+            float da = 1.0f;
+            if (out_activation == 1) {
+                float sg = 1.0f / (1.0f + expf(-(float)acc));
+                da = sg * (1.0f - sg);
+            }
+            dout[r] = orc_h2f(orc_f2h(orc_h2f(dl_dradiance[(size_t)s * 4 + r]) * da));
+        }
+        for (int r = 0; r < OUT; r++)
+            for (int k = 0; k < W; k++) grad_w[off[H] + (size_t)r * W + k] += (double)dout[r] * x[H][k];
+        for (int k = 0; k < W; k++) {
+            double acc = 0.0;
+            for (int r = 0; r < OUT; r++) acc += (double)dout[r] * w8[(size_t)r * W + k];
+            dz[k] = orc_h2f(orc_f2h(x[H][k] > 0.f ? (float)acc : 0.f));      /* dZ_7 */
+        }
+        for (int l = H - 1; l >= 0; l--) {
+            const int K = l == 0 ? IN : W;
+            const float* w = wf + off[l];
+            for (int r = 0; r < W; r++)
+                for (int k = 0; k < K; k++) grad_w[off[l] + (size_t)r * K + k] += (double)dz[r] * x[l][k];
+            if (l == 0) break;
+            for (int k = 0; k < W; k++) {
+                double acc = 0.0;
+                for (int r = 0; r < W; r++) acc += (double)dz[r] * w[(size_t)r * K + k];
+                dprev[k] = orc_h2f(orc_f2h(x[l][k] > 0.f ? (float)acc : 0.f));
+            }
+            memcpy(dz, dprev, sizeof(dz));
+        }
+    }
+    free(x);
+    free(wf);
+}
+
 /* dL/d table: every sample adds w_corner * dEnc[level] to its 8 corner entries (F = 2). */
 void orc_hashgrid_backward(int L, const float* scales, const uint32_t* ress, const uint32_t* sizes,
                            const long long* offsets, const float* samples, int sample_stride,

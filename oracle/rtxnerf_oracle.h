@@ -153,6 +153,8 @@ void orc_mlp_forward(const uint16_t* weights, int in_dim, int width, int n_hidde
  * caller-zeroed (accumulates). */
 void orc_mlp_backward(const uint16_t* weights, int out_activation, const uint16_t* enc,
                       const uint16_t* dl_dradiance, long long n, uint16_t* d_enc, double* grad_w);
+void orc_freqnet_backward(const uint16_t* weights, int out_activation, const uint16_t* enc,
+                          const uint16_t* dl_dradiance, long long n, double* grad_w);
 void orc_hashgrid_backward(int L, const float* scales, const uint32_t* ress, const uint32_t* sizes,
                            const long long* offsets, const float* samples, int sample_stride,
                            long long n, const uint16_t* d_enc, double* grad_table);

@@ -109,6 +109,8 @@ SIGNATURES = {
     "rtxnerf_freqnet_encode": (c_int, [c_void_p, c_int, c_ll, c_void_p, c_void_p]),
     "rtxnerf_freqnet_forward": (c_int, [C.POINTER(FreqNet), c_void_p, c_int, c_void_p, c_ll, c_ll, c_void_p, c_void_p,
                                         c_void_p]),
+    "rtxnerf_freqnet_backward": (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p, c_ll, c_ll, c_void_p,
+                                         c_void_p]),
     "rtxnerf_network_backward_rays": (c_int, [C.POINTER(HashGrid), C.POINTER(Mlp), c_void_p, c_int, c_void_p,
                                               c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_ll, c_void_p,
                                               c_void_p, c_void_p, c_void_p]),

@@ -469,6 +469,22 @@ class FrequencyNetwork:
         return output if output is not None else radiance
 
 
+def _freqnet_backward_method():
+    def backward(self, stream, input, dl_dradiance, grad_weights, n=None, d_count=None, count_scale=1):
+        """network->backward (main.cu:781) for the Frequency + 8 x 128 network: fp32 weight gradients
+        accumulated into grad_weights [n_params]; input as forward(), dl_dradiance fp16 [N][4]."""
+        n_max = input.shape[0] if n is None else n
+        _lib.check(_lib.load().rtxnerf_freqnet_backward(_p(self.weights), self.out_activation, _p(input),
+                                                        input.shape[1], _p(dl_dradiance), _p(d_count),
+                                                        int(count_scale), int(n_max), _p(grad_weights),
+                                                        _stream_ptr(stream)), "freqnet_backward")
+
+    FrequencyNetwork.backward = backward
+
+
+_freqnet_backward_method()
+
+
 class Network:
     """Encoding + fully fused MLP: the object the reference gets from tcnn::create_from_config
     (main.cu:325) and drives with network->forward(stream, input, &output) (main.cu:721).

@@ -439,3 +439,314 @@ extern "C" int rtxnerf_freqnet_forward(const rtxnerf_freqnet* net, const float* 
         count_scale, n_max, d_out16, d_radiance4);
     return rtx_launch_status();
 }
+
+// =========================================================================================
+// Backward of the reference's literal network (main.cu:781 network->backward): the weight
+// gradients of the 8 x 128 MLP over the Frequency encoding (the encoding has no parameters, so nothing
+// flows below layer 0).  tiny-cuda-nn is absent from the archive: PARITY UNPINNED, the algorithm is
+// restated (oracle: orc_freqnet_backward; independent autograd pin: tests/test_oracle_autograd.py).
+//   dOut_j = g_j * sigmoid'(out_j);  dZ_{l-1} = (dZ_l . W_l) masked by ReLU'(X_l);  dW_l += dZ_l^T . X_l
+// The forward is recomputed per 128-sample tile (keeping the activations would cost 2 KB per sample).
+// The nine weight-gradient accumulators are 9 x 128 fp32 TMEM columns — more than the 512 an SM has next
+// to the 128 of the working accumulator — so the kernel is launched THREE times, each launch recomputing
+// the forward and the dgrad chain and accumulating the gradients of three layers in TMEM over all of its
+// tiles (one flush of fp32 atomics per CTA at the end): 63 layer products per tile instead of 27.
+// Operand tiles live in shared memory in the no-swizzle core-matrix layout, which the tensor cores read in
+// both majors (tcgen05.cuh): X_l [sample][feature] is the K-major A of the forward layer and the MN-major
+// B of dW_l; dZ_l is the K-major A of the dgrad and the MN-major A of dW_l; W_l [out][in] is the K-major B
+// of the forward and the MN-major B of the dgrad.  Weights stream from L2 into a two-slot ring by plain
+// loads issued under the running MMA.  First version: one tile per CTA, serial phases — correctness first;
+// the measured rate is in DESIGN.md.
+// =========================================================================================
+#define FB_THREADS NET_TILE
+#define FB_TILE_BYTES (NET_TILE * FN_W * 2)                 // 32 KB: [128][128] fp16
+struct FbSmem {
+    static constexpr int WB = 0;                             // two weight slots
+    static constexpr int XK = WB + 2 * FB_TILE_BYTES;        // inputs X_l of the three layers of this launch
+    static constexpr int WORK = XK + 3 * FB_TILE_BYTES;      // current X_l, then current dZ_l
+    static constexpr int DOUT = WORK + FB_TILE_BYTES;        // [128][16] dOut
+    static constexpr int BAR = DOUT + NET_TILE * NET_OUT * 2;
+    static constexpr int BYTES = BAR + 16;
+};
+#define FB_COL_D 0
+#define FB_COL_G(i) (128 + 128 * (i))
+
+// row-major [rows][K] fp16 layer -> core-matrix tile with 128 columns (columns >= K are zero)
+__device__ __forceinline__ void fb_load_weights(uint8_t* tile, const uint16_t* __restrict__ w, int l, int tid)
+{
+    const int rows = fn_layer_n(l), K = fn_layer_k(l);
+    const uint16_t* src = w + fn_layer_src(l);
+#pragma unroll 4
+    for (int i = tid; i < rows * 16; i += FB_THREADS) {
+        const int r = i >> 4, c = i & 15;
+        uint4 v = make_uint4(0u, 0u, 0u, 0u);
+        if (c * 8 < K) v = __ldg(reinterpret_cast<const uint4*>(src + (size_t)r * K + c * 8));
+        *reinterpret_cast<uint4*>(tile + tile_chunk_off(r, c, FN_W)) = v;
+    }
+}
+
+struct SmemRowSink {       // frequency_row -> this thread's row of a [128][128] core-matrix tile
+    uint8_t* tile;
+    int row;
+    __device__ __forceinline__ void operator()(int base, const uint32_t (&c)[16]) const
+    {
+#pragma unroll
+        for (int i = 0; i < 4; i++)
+            *reinterpret_cast<uint4*>(tile + tile_chunk_off(row, base / 4 + i, FN_W)) =
+                make_uint4(c[4 * i], c[4 * i + 1], c[4 * i + 2], c[4 * i + 3]);
+    }
+    __device__ __forceinline__ void tail(int base, const uint32_t (&c)[16]) const { (*this)(base, c); }
+};
+
+// D[128 x N] = A[128 x 128] (K-major) . B[N x 128]^T (K-major)
+template <int N>
+__device__ __forceinline__ void fb_mma_fwd(uint32_t d, uint32_t a, uint32_t w)
+{
+    constexpr uint32_t id = tc::idesc_f16_f32_major(NET_TILE, N, 0, 0);
+#pragma unroll
+    for (int ks = 0; ks < FN_W / 16; ks++)
+        tc::mma_f16_ss(d, tc::smem_desc(a + ks * 256, 128, FN_W * 16), tc::smem_desc(w + ks * 256, 128, FN_W * 16), id,
+                       ks > 0 ? 1u : 0u);
+}
+// D[128 x 128] = dZ[128 x K_OUT] (K-major, tile of K_OUT columns) . W[K_OUT out][128 in] (MN-major)
+template <int K_OUT>
+__device__ __forceinline__ void fb_mma_dgrad(uint32_t d, uint32_t dz, uint32_t w)
+{
+    constexpr uint32_t id = tc::idesc_f16_f32_major(NET_TILE, FN_W, 0, 1);
+#pragma unroll
+    for (int ks = 0; ks < K_OUT / 16; ks++)
+        tc::mma_f16_ss(d, tc::smem_desc(dz + ks * 256, 128, K_OUT * 16),
+                       tc::smem_desc(w + ks * 2 * (FN_W * 16), FN_W * 16, 128), id, ks > 0 ? 1u : 0u);
+}
+// G[128 x N] (+)= X[128 samples][128]^T . Y[128 samples][N]   (both MN-major, K = samples)
+template <int N>
+__device__ __forceinline__ void fb_mma_wgrad(uint32_t g, uint32_t x, uint32_t y, bool accumulate)
+{
+    constexpr uint32_t id = tc::idesc_f16_f32_major(NET_TILE, N, 1, 1);
+#pragma unroll
+    for (int ks = 0; ks < NET_TILE / 16; ks++)
+        tc::mma_f16_ss(g, tc::smem_desc(x + ks * 2 * (FN_W * 16), FN_W * 16, 128),
+                       tc::smem_desc(y + ks * 2 * (N * 16), N * 16, 128), id, (accumulate || ks > 0) ? 1u : 0u);
+}
+
+// forward epilogue of one row: 128 fp32 -> ReLU -> fp16 -> this row of dst; mask = (activation > 0) per column
+__device__ __forceinline__ void fb_relu_row(uint32_t t_row, uint8_t* dst, int row, uint32_t (&mask)[4])
+{
+#pragma unroll
+    for (int q = 0; q < FN_W / 16; q++) {
+        uint32_t r[16];
+        tc::tmem_ld_x16(t_row + q * 16, r);
+        tc::tmem_ld_wait();
+        uint32_t pk[8], m = 0u;
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            pk[j] = relu_pack_f16x2(__uint_as_float(r[2 * j]), __uint_as_float(r[2 * j + 1]));
+            m |= ((pk[j] & 0xffffu) ? 1u : 0u) << (2 * j);
+            m |= ((pk[j] >> 16) ? 1u : 0u) << (2 * j + 1);
+        }
+        if (q & 1) mask[q >> 1] |= m << 16;
+        else mask[q >> 1] = m;
+        *reinterpret_cast<uint4*>(dst + tile_chunk_off(row, 2 * q, FN_W)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+        *reinterpret_cast<uint4*>(dst + tile_chunk_off(row, 2 * q + 1, FN_W)) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+    }
+}
+// dgrad epilogue of one row: 128 fp32 -> masked -> fp16 -> this row of dst
+__device__ __forceinline__ void fb_masked_row(uint32_t t_row, uint8_t* dst, int row, const uint32_t (&mask)[4])
+{
+#pragma unroll
+    for (int q = 0; q < FN_W / 16; q++) {
+        uint32_t r[16];
+        tc::tmem_ld_x16(t_row + q * 16, r);
+        tc::tmem_ld_wait();
+        const uint32_t m = (q & 1) ? (mask[q >> 1] >> 16) : (mask[q >> 1] & 0xffffu);
+        uint32_t pk[8];
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            const float a = ((m >> (2 * j)) & 1u) ? __uint_as_float(r[2 * j]) : 0.0f;
+            const float b = ((m >> (2 * j + 1)) & 1u) ? __uint_as_float(r[2 * j + 1]) : 0.0f;
+            const __half2 v = __floats2half2_rn(a, b);
+            pk[j] = *reinterpret_cast<const uint32_t*>(&v);
+        }
+        *reinterpret_cast<uint4*>(dst + tile_chunk_off(row, 2 * q, FN_W)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+        *reinterpret_cast<uint4*>(dst + tile_chunk_off(row, 2 * q + 1, FN_W)) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+    }
+}
+
+__global__ void __launch_bounds__(FB_THREADS, 1)
+freqnet_backward_kernel(const uint16_t* __restrict__ weights, const float* __restrict__ samples, int stride,
+                        int out_activation, const uint16_t* __restrict__ dl_dradiance,
+                        const long long* __restrict__ d_count, long long count_scale, long long n_max, int l0,
+                        float* __restrict__ grad_weights)
+{
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint64_t* bar = reinterpret_cast<uint64_t*>(smem + FbSmem::BAR);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + FbSmem::BAR + 8);
+    const int tid = threadIdx.x, warp = tid >> 5;
+    if (tid == 0) {
+        tc::mbar_init(bar, 1);
+        tc::fence_mbar_init();
+    }
+    if (warp == 0) tc::tmem_alloc<512>(tmem_slot);
+    fb_load_weights(smem + FbSmem::WB, weights, 0, tid);
+    tc::fence_proxy_async_smem();
+    tc::fence_before_thread_sync();
+    __syncthreads();
+    tc::fence_after_thread_sync();
+    const uint32_t tm = *tmem_slot;
+    const uint32_t t_row = tm + ((uint32_t)(warp * 32) << 16);
+    uint8_t* wb0 = smem + FbSmem::WB;
+    uint8_t* wb1 = smem + FbSmem::WB + FB_TILE_BYTES;
+    uint8_t* work = smem + FbSmem::WORK;
+    uint8_t* dout = smem + FbSmem::DOUT;
+    uint32_t phase = 0;
+    bool have = false;      // the three gradient accumulators hold at least one tile
+
+    // publish this phase's shared-memory tile, run the MMAs, do UNDER while they run, wait for them
+    // (a macro, not a lambda: by-reference captures pushed the mask registers into local memory)
+#define FB_RUN(ISSUE, UNDER)                        \
+    do {                                            \
+        tc::fence_proxy_async_smem();               \
+        tc::fence_before_thread_sync();             \
+        __syncthreads();                            \
+        if (tid == 0) {                             \
+            tc::fence_after_thread_sync();          \
+            ISSUE;                                  \
+            tc::mma_commit(bar);                    \
+        }                                           \
+        UNDER;                                      \
+        tc::mbar_wait(bar, phase);                  \
+        phase ^= 1;                                 \
+        tc::fence_after_thread_sync();              \
+    } while (0)
+#define FB_KEEP(l) ((l) >= l0 && (l) < l0 + 3)
+#define FB_X(l) (FB_KEEP(l) ? smem + FbSmem::XK + ((l) - l0) * FB_TILE_BYTES : work)
+
+    long long n = n_max;
+    if (d_count) {
+        const long long c = *d_count * count_scale;
+        n = c < n_max ? c : n_max;
+    }
+    const long long n_tiles = (n + NET_TILE - 1) / NET_TILE;
+    for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const long long s = tile * NET_TILE + tid;
+        const bool valid = s < n;
+        uint32_t mask[FN_HIDDEN][4];        // mask[l] = (X_{l+1} > 0), one bit per column of this row
+        frequency_row(samples + (valid ? s : 0) * stride, valid, SmemRowSink{FB_X(0), tid});
+        // ---- forward recompute: X_{l+1} = relu(X_l . W_l^T); W_{l+1} is loaded under the MMA of layer l
+#pragma unroll
+        for (int l = 0; l < FN_HIDDEN; l++) {
+            uint8_t* xc = FB_X(l);
+            uint8_t* xn = FB_X(l + 1);
+            uint8_t* wc = (l & 1) ? wb1 : wb0;
+            uint8_t* wn = (l & 1) ? wb0 : wb1;
+            FB_RUN(fb_mma_fwd<FN_W>(tm + FB_COL_D, tc::smem_u32(xc), tc::smem_u32(wc)),
+                   fb_load_weights(wn, weights, l + 1, tid));
+            fb_relu_row(t_row + FB_COL_D, xn, tid, mask[l]);
+        }
+        uint8_t* x8 = FB_X(FN_HIDDEN);
+        FB_RUN(fb_mma_fwd<NET_OUT>(tm + FB_COL_D, tc::smem_u32(x8), tc::smem_u32(wb0)), (void)0);
+        {   // dOut = g * act'(out) on (r,g,b,sigma); the 12 padding outputs carry no gradient
+            uint32_t r[16];
+            output_row_load(t_row + FB_COL_D, r);
+            float d[4] = {0.f, 0.f, 0.f, 0.f};
+            if (valid) {
+                const uint2 gb = __ldg(reinterpret_cast<const uint2*>(dl_dradiance + s * 4));
+                const float2 g01 = __half22float2(*reinterpret_cast<const __half2*>(&gb.x));
+                const float2 g23 = __half22float2(*reinterpret_cast<const __half2*>(&gb.y));
+                const float g[4] = {g01.x, g01.y, g23.x, g23.y};
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    float da = 1.0f;
+                    if (out_activation == 1) {
+                        const float sg = __fdividef(1.0f, 1.0f + __expf(-__uint_as_float(r[j])));
+                        da = sg * (1.0f - sg);
+                    }
+                    d[j] = g[j] * da;
+                }
+            }
+            const __half2 d01 = __floats2half2_rn(d[0], d[1]), d23 = __floats2half2_rn(d[2], d[3]);
+            *reinterpret_cast<uint4*>(dout + tile_chunk_off(tid, 0, NET_OUT)) =
+                make_uint4(*reinterpret_cast<const uint32_t*>(&d01), *reinterpret_cast<const uint32_t*>(&d23), 0u, 0u);
+            *reinterpret_cast<uint4*>(dout + tile_chunk_off(tid, 1, NET_OUT)) = make_uint4(0u, 0u, 0u, 0u);
+        }
+        // ---- output layer: dW_8^T [in][out] += X_8^T . dOut ;  D = dOut . W_8   (W_7 is still in the other slot)
+        FB_RUN({
+            if (FB_KEEP(FN_HIDDEN))
+                fb_mma_wgrad<NET_OUT>(tm + FB_COL_G(FN_HIDDEN - l0), tc::smem_u32(x8), tc::smem_u32(dout), have);
+            fb_mma_dgrad<NET_OUT>(tm + FB_COL_D, tc::smem_u32(dout), tc::smem_u32(wb0));
+        }, (void)0);
+        fb_masked_row(t_row + FB_COL_D, work, tid, mask[FN_HIDDEN - 1]);        // dZ_7
+        // ---- hidden layers 7 .. 1: dW_l += dZ_l^T . X_l ;  D = dZ_l . W_l ;  dZ_{l-1} = D masked by (X_l > 0).
+        // W_{l-1} is loaded under the MMAs into the slot of W_{l+1} (done with); for l = 1 that fetches W_0 for
+        // the next tile's forward
+#pragma unroll
+        for (int l = FN_HIDDEN - 1; l >= 1; l--) {
+            uint8_t* wc = (l & 1) ? wb1 : wb0;
+            uint8_t* wn = (l & 1) ? wb0 : wb1;
+            FB_RUN({
+                if (FB_KEEP(l))
+                    fb_mma_wgrad<FN_W>(tm + FB_COL_G(l - l0), tc::smem_u32(work), tc::smem_u32(FB_X(l)), have);
+                fb_mma_dgrad<FN_W>(tm + FB_COL_D, tc::smem_u32(work), tc::smem_u32(wc));
+            }, fb_load_weights(wn, weights, l - 1, tid));
+            fb_masked_row(t_row + FB_COL_D, work, tid, mask[l - 1]);             // dZ_{l-1}
+        }
+        // ---- layer 0: dW_0 += dZ_0^T . X_0 (nothing flows into the parameter-free encoding)
+        if (FB_KEEP(0))
+            FB_RUN(fb_mma_wgrad<FN_W>(tm + FB_COL_G(0 - l0), tc::smem_u32(work), tc::smem_u32(FB_X(0)), have), (void)0);
+        have = true;
+    }
+    // ---- the three weight-gradient accumulators leave TMEM once (M = 128: row r in TMEM lane r)
+    tc::fence_before_thread_sync();
+    __syncthreads();
+    tc::fence_after_thread_sync();
+    if (have) {
+#pragma unroll 1
+        for (int i = 0; i < 3; i++) {
+            const int l = l0 + i;
+            if (l > FN_HIDDEN) break;
+            float* gw = grad_weights + fn_layer_src(l);
+            if (l == FN_HIDDEN) {        // transposed accumulator [in = tid][out j]
+                uint32_t r[16];
+                tc::tmem_ld_x16(t_row + FB_COL_G(i), r);
+                tc::tmem_ld_wait();
+#pragma unroll
+                for (int j = 0; j < NET_OUT; j++) atomicAdd(gw + j * FN_W + tid, __uint_as_float(r[j]));
+            } else {
+                const int K = fn_layer_k(l);
+#pragma unroll 1
+                for (int q = 0; q < FN_W / 16; q++) {
+                    uint32_t r[16];
+                    tc::tmem_ld_x16(t_row + FB_COL_G(i) + q * 16, r);
+                    tc::tmem_ld_wait();
+#pragma unroll
+                    for (int j = 0; j < 16; j++)
+                        if (q * 16 + j < K) atomicAdd(gw + (size_t)tid * K + q * 16 + j, __uint_as_float(r[j]));
+                }
+            }
+        }
+    }
+    tc::fence_before_thread_sync();
+    __syncthreads();
+    tc::fence_after_thread_sync();
+    if (warp == 0) tc::tmem_dealloc<512>(tm);
+}
+
+extern "C" int rtxnerf_freqnet_backward(const uint16_t* d_weights, int out_activation, const float* d_samples,
+                                        int sample_stride, const uint16_t* d_dl_dradiance, const long long* d_count,
+                                        long long count_scale, long long n_max, float* d_grad_weights, void* stream)
+{
+    if (!d_weights || !d_samples || !d_dl_dradiance || !d_grad_weights) return RTXNERF_EINVAL;
+    if (n_max < 0 || sample_stride < 5 || count_scale < 1) return RTXNERF_EINVAL;
+    if (out_activation != 0 && out_activation != 1) return RTXNERF_ECONFIG;
+    if (((uintptr_t)d_weights & 15u) || ((uintptr_t)d_dl_dradiance & 7u)) return RTXNERF_EINVAL;
+    if (n_max == 0) return RTXNERF_OK;
+    static RtxPerDeviceOnce attr;
+    RTX_CUDA_TRY((cudaError_t)rtx_set_max_smem(attr, freqnet_backward_kernel, FbSmem::BYTES));
+    const long long tiles = (n_max + NET_TILE - 1) / NET_TILE;
+    const long long blocks = tiles < RTX_NUM_SMS ? tiles : RTX_NUM_SMS;      // one CTA per SM owns all 512 TMEM columns
+    for (int l0 = 0; l0 < FN_LAYERS; l0 += 3)
+        freqnet_backward_kernel<<<(unsigned)blocks, FB_THREADS, FbSmem::BYTES, (cudaStream_t)stream>>>(
+            d_weights, d_samples, sample_stride, out_activation, d_dl_dradiance, d_count, count_scale, n_max, l0,
+            d_grad_weights);
+    return rtx_launch_status(3);
+}

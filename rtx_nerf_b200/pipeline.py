@@ -223,21 +223,27 @@ class Trainer:
         if process_group is not None:
             import torch.distributed as dist
             self.world = dist.get_world_size(process_group)
+        # the reference's literal network (Frequency + 8 x 128, main.cu:47-68) trains through the same step: its
+        # backward recomputes the forward per tile, so no features are kept, and it has no encoding parameters
+        self.literal = isinstance(network, api.FrequencyNetwork)
+        stage = FrequencyNetworkRadiance(network) if self.literal else _EncodedNetworkRadiance(self)
         self.view = ViewRenderer(grid, width, height, focal_length, aspect_ratio, samples_per_segment, max_hits,
-                                 _EncodedNetworkRadiance(self), n_rays=n_rays, ray_begin=0, device=device)
+                                 stage, n_rays=n_rays, ray_begin=0, device=device)
         v = self.view
         dev = torch.device(device)
         N = v.N_cap
-        self.encoded = torch.empty((N, 32), dtype=torch.float16, device=dev)
-        self.dencoded = torch.empty((N, 32), dtype=torch.float16, device=dev)
+        if not self.literal:
+            self.encoded = torch.empty((N, 32), dtype=torch.float16, device=dev)
+            self.dencoded = torch.empty((N, 32), dtype=torch.float16, device=dev)
         self.radiance_grad = torch.empty((N, 4), dtype=torch.float16, device=dev)
         self.target = torch.empty((self.R, 3), dtype=torch.float32, device=dev)
         self.loss_grad = torch.empty((self.R, 3), dtype=torch.float16, device=dev)
         self.loss_sum = torch.zeros(1, dtype=torch.float32, device=dev)
-        n_params = network.params.numel()
-        self.n_table = network.table.numel()
+        self.params = network.weights if self.literal else network.params         # the flat fp16 parameter buffer
+        n_params = self.params.numel()
+        self.n_table = 0 if self.literal else network.table.numel()
         self.grads = torch.zeros(n_params, dtype=torch.float32, device=dev)      # [table | weights], all-reduced
-        self.master = network.params.float()                                       # fp32 master (main.cu:331)
+        self.master = self.params.float()                                          # fp32 master (main.cu:331)
         self.m1 = torch.zeros(n_params, dtype=torch.float32, device=dev)
         self.m2 = torch.zeros(n_params, dtype=torch.float32, device=dev)
         self.step_count = 0
@@ -257,6 +263,11 @@ class Trainer:
         api.l2_loss(v.pixels, self.target, self.loss_scale, self.loss_grad, loss_sum=self.loss_sum)
         api.launch_volrender_backward_cuda(None, self.loss_grad, v.radiance, v.t_vals, h.num_hits, h.indices,
                                            self.R, self.S, self.radiance_grad, backward_mode=self.backward_mode)
+        if self.literal:
+            self.net.backward(None, v.samples, self.radiance_grad, self.grads, n=v.N_cap, d_count=h.total_hits,
+                              count_scale=self.S)
+            self._reduced = False
+            return
         if self.world == 1 or not self.overlap:
             self.net.backward_rays(None, v.samples, self.encoded, self.radiance_grad, h.num_hits, h.indices, self.R,
                                    self.S, h.total_hits, v.N_cap, self.dencoded, self.grads[:self.n_table],
@@ -292,9 +303,11 @@ class Trainer:
 
     def optimizer_step(self):
         self.step_count += 1
-        api.adam_step(self.master, self.net.params, self.grads, self.m1, self.m2,
+        api.adam_step(self.master, self.params, self.grads, self.m1, self.m2,
                       parallel.grad_scale(self.loss_scale, self.pg) if self.world > 1 else 1.0 / self.loss_scale,
                       self.step_count, lr=self.lr, n_encoding=self.n_table)
+        if self.literal:
+            self.net.repack()          # row-major fp16 weights -> the forward kernel's operand layout
 
     def step(self, pose_dev, ray_begin, target_dev):
         """pose (16 floats) and target pixels [n_rays][3] already on the device."""

@@ -111,3 +111,91 @@ def test_freqnet_renders_config1_shape(cuda_api, orc):
     _, rado = orc.mlp_forward(w, 112, 128, 8, 1, orc.frequency_encode(so))
     pxo = orc.volrender(rado, ora.num_hits, ora.indices, to, S)
     np.testing.assert_allclose(px, pxo, rtol=0, atol=2e-3)
+
+
+@pytest.mark.parametrize("n,act", [(128, 1), (1000, 1), (2500, 0)])
+def test_freqnet_backward_vs_oracle(cuda_api, orc, n, act):
+    """network->backward (main.cu:781) of the literal network: weight gradients from freqnet_backward_kernel
+    (forward recomputed per tile, three launches of three layers) against orc_freqnet_backward run on the
+    KERNEL'S OWN encoded features (isolates the MUFU sine).  Tolerance: fp32 tensor-core sums against double
+    sums over fp16 operands, with every activation gradient rounded to fp16 on the way down (a different last
+    bit wherever the two sums straddle a rounding boundary: ~1e-3 relative per element after eight layers):
+    the median entry within 0.1 % of the layer's largest entry.  A hidden unit whose pre-activation rounds to the
+    other side of zero in fp32 than in double flips its ReLU for one sample, and that sample's rank-one
+    contribution then differs in every layer below (seen: one sample in 1000, 1 % of the largest entry), so
+    the maximum is held to 3 %.  Ragged row counts through d_count; gradients accumulate."""
+    import torch
+    w = synth.mlp_weights(112, 128, 8, 16, seed=3)
+    net = cuda_api.FrequencyNetwork(w, out_activation=act)
+    s = _rows(n + 37, n)
+    g = (np.random.default_rng(n).uniform(-1, 1, (n + 37, 4)) * 0.5).astype(np.float16)
+    ds = _t(s)
+    gw = torch.zeros(net.n_params(), dtype=torch.float32, device="cuda")
+    cnt = torch.tensor([n], dtype=torch.int64, device="cuda")
+    net.backward(None, ds, _t(g), gw, d_count=cnt)                  # rows past *d_count are ignored
+    torch.cuda.synchronize()
+    enc = net.encode(ds).cpu().numpy()[:n]
+    ref = orc.freqnet_backward(w, act, enc, g[:n])
+    got = gw.cpu().numpy().astype(np.float64)
+    o = 0
+    for (a, b) in [(128, 112)] + [(128, 128)] * 7 + [(16, 128)]:
+        x, y = got[o:o + a * b], ref[o:o + a * b]
+        o += a * b
+        assert np.abs(y).max() > 0
+        d = np.abs(x - y) / np.abs(y).max()
+        assert np.quantile(d, 0.5) < 1e-3 and d.max() < 3e-2, "layer at offset %d: %g %g" % (o - a * b, np.quantile(d, 0.5), d.max())
+    assert np.all(got[-12 * 128:] == 0)
+    net.backward(None, ds, _t(g), gw, d_count=cnt)
+    torch.cuda.synchronize()
+    np.testing.assert_allclose(gw.cpu().numpy(), 2 * got, rtol=0, atol=1e-3 * np.abs(got).max())
+
+
+def test_trainer_with_literal_network_trains(cuda_api, orc):
+    """pipeline.Trainer on the reference's literal network (main.cu:47-68 trained at :781,787): one
+    step's weight gradient against the oracle chain, then 150 Adam steps with the analytic compositing backward
+    against a synthetic target must raise the PSNR."""
+    import torch
+    from rtx_nerf_b200 import pipeline
+    api = cuda_api
+    G, W, H, S, HM = 64, 48, 32, 4, 8
+    R = W * H
+    occ = synth.occupancy_lego(G)
+    grid = api.OccupancyGrid.from_occupancy(occ, G)
+    focal = synth.focal_length()
+    pose = synth.poses(1, seed=4)[0]
+    w = synth.mlp_weights(112, 128, 8, 16, seed=6)
+    net = api.FrequencyNetwork(w)
+    tr = pipeline.Trainer(grid, net, W, H, focal, W / H, S, HM, R, loss_scale=128.0, lr=2e-3,
+                          backward_mode=api.BACKWARD_ANALYTIC)
+    yy, xx = np.mgrid[0:H, 0:W]
+    target = np.stack([xx / W, yy / H, 0.5 + 0.4 * np.sin(xx / 4.0)], -1).reshape(-1, 3).astype(np.float32)
+    v = tr.view
+    v.pose_dev.copy_(_t(pose.reshape(16)))
+    v.ray_begin = 0
+    tr.target.copy_(_t(target))
+    tr.forward()
+    tr.backward()
+    torch.cuda.synchronize()
+    hit = v.hits.num_hits.cpu().numpy() > 0
+    n = int(v.hits.total_hits.item()) * S
+    # the oracle's backward on the kernel's own features / radiance / compositing gradient
+    enc = net.encode(v.samples[:n]).cpu().numpy()
+    ref = orc.freqnet_backward(w, 1, enc, tr.radiance_grad[:n].cpu().numpy())
+    got = tr.grads.cpu().numpy().astype(np.float64)
+    d = np.abs(got - ref) / np.abs(ref).max()
+    assert np.abs(ref).max() > 0 and np.quantile(d, 0.5) < 1e-3 and d.max() < 3e-2, (np.quantile(d, 0.5), d.max())
+    rs = pipeline.ViewRenderer(grid, W, H, focal, W / H, S, HM, pipeline.FrequencyNetworkRadiance(net))
+
+    def psnr():
+        px = rs.render_host(pose).numpy()
+        return float(-10.0 * np.log10(np.mean((px[hit] - target[hit]) ** 2)))
+
+    tr.grads.zero_()
+    p0 = psnr()
+    pose_dev, tgt = _t(pose.reshape(16)), _t(target)
+    for _ in range(150):
+        tr.step(pose_dev, 0, tgt)
+    torch.cuda.synchronize()
+    p1 = psnr()
+    print("literal network: PSNR %.2f -> %.2f dB in 150 steps" % (p0, p1))
+    assert torch.isfinite(tr.master).all() and p1 > p0 + 3.0, (p0, p1)
