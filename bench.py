@@ -350,6 +350,43 @@ def run_ours(args):
                       ms_per_view=sum(ms2), rays_per_s=W * H / (sum(ms2) * 1e-3), samples_per_s=n_s2 / (sum(ms2) * 1e-3),
                       network_ms=ms2[2], network_tflops=tf2, peak_tflops=pk["tf"], frac_of_peak=tf2 / pk["tf"],
                       stages_ms=dict(march=ms2[0], sampler=ms2[1], network=ms2[2], composite=ms2[3]))
+        if world == 1 and not args.no_train:
+            # the training step of configs[3] through this network: 2^18 rays, S=4 x H_max=32
+            TR2, TS2, THM2 = 1 << 18, 4, 32
+            tr2 = pipeline.Trainer(grid, fnet, W, H, focal, W / H, TS2, THM2, TR2)
+            tgt2 = torch.rand((TR2, 3), device="cuda")
+            for k in range(2):
+                tr2.step(poses_dev[k % len(poses_dev)], (k * 7919) % (W * H - TR2), tgt2)
+            torch.cuda.synchronize()
+            ea, eb, ec = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+            n3, bw_ms = 3, 0.0
+            ea.record()
+            for k in range(n3):
+                v2 = tr2.view
+                v2.pose_dev.copy_(poses_dev[(2 + k) % len(poses_dev)], non_blocking=True)
+                v2.ray_begin = ((2 + k) * 7919) % (W * H - TR2)
+                tr2.target.copy_(tgt2, non_blocking=True)
+                tr2.forward()
+                tr2.backward()
+                tr2.optimizer_step()
+            eb.record()
+            torch.cuda.synchronize()
+            n_s3 = float(tr2.view.hits.total_hits.item()) * TS2
+            ms3 = ea.elapsed_time(eb) / n3
+            # backward alone (three launches of freqnet_backward_kernel)
+            ea.record()
+            tr2.net.backward(None, tr2.view.samples, tr2.radiance_grad, tr2.grads, n=tr2.view.N_cap,
+                             d_count=tr2.view.hits.total_hits, count_scale=TS2)
+            ec.record()
+            torch.cuda.synchronize()
+            bw_ms = ea.elapsed_time(ec)
+            tf3 = 63 * 2.0 * 128 * 128 * 128 * (n_s3 / 128) / (bw_ms * 1e-3) / 1e12    # 63 layer products per tile
+            refnet["train_step"] = dict(
+                workload="configs[3] shape through the literal network: 2^18 rays, S=4 x H_max=32, forward, loss, "
+                         "compositing backward, weight-gradient backward (forward recomputed, 3 launches), Adam, repack",
+                ms_per_step=ms3, rays_per_s=TR2 / (ms3 * 1e-3), samples_per_s=n_s3 / (ms3 * 1e-3),
+                backward_ms=bw_ms, backward_tflops_executed=tf3, frac_of_peak=tf3 / pk["tf"])
+            del tr2
         del r2, fnet
 
     # ---- BASELINE configs[4] (stress): 1920x1080 view, 512^3 grid at 10 % occupancy, up to 256 samples/ray

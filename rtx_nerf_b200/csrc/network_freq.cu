@@ -458,7 +458,7 @@ extern "C" int rtxnerf_freqnet_forward(const rtxnerf_freqnet* net, const float* 
 // loads issued under the running MMA.  First version: one tile per CTA, serial phases — correctness first;
 // the measured rate is in DESIGN.md.
 // =========================================================================================
-#define FB_THREADS NET_TILE
+#define FB_THREADS (2 * NET_TILE)          // two threads per sample row: each owns 64 of the 128 columns
 #define FB_TILE_BYTES (NET_TILE * FN_W * 2)                 // 32 KB: [128][128] fp16
 struct FbSmem {
     static constexpr int WB = 0;                             // two weight slots
@@ -476,11 +476,13 @@ __device__ __forceinline__ void fb_load_weights(uint8_t* tile, const uint16_t* _
 {
     const int rows = fn_layer_n(l), K = fn_layer_k(l);
     const uint16_t* src = w + fn_layer_src(l);
-#pragma unroll 4
+#pragma unroll 8
     for (int i = tid; i < rows * 16; i += FB_THREADS) {
         const int r = i >> 4, c = i & 15;
         uint4 v = make_uint4(0u, 0u, 0u, 0u);
-        if (c * 8 < K) v = __ldg(reinterpret_cast<const uint4*>(src + (size_t)r * K + c * 8));
+        // a volatile load: as plain read-only loads the compiler moved the copies of several phases above their
+        // barriers to hide latency and ran out of registers (255 + 2 KB of spill)
+        if (c * 8 < K) v = ld_stream_u4(reinterpret_cast<const uint4*>(src + (size_t)r * K + c * 8));
         *reinterpret_cast<uint4*>(tile + tile_chunk_off(r, c, FN_W)) = v;
     }
 }
@@ -498,9 +500,12 @@ struct SmemRowSink {       // frequency_row -> this thread's row of a [128][128]
     __device__ __forceinline__ void tail(int base, const uint32_t (&c)[16]) const { (*this)(base, c); }
 };
 
+// The three issue helpers are NOT inlined: inlined into the 17 unrolled phases, their ~250 64-bit matrix
+// descriptors (all derived from a few shared-memory bases) were computed ahead and kept live by every thread
+// of the kernel — 255 registers and 2.8 KB of spill — although only thread 0 issues.
 // D[128 x N] = A[128 x 128] (K-major) . B[N x 128]^T (K-major)
 template <int N>
-__device__ __forceinline__ void fb_mma_fwd(uint32_t d, uint32_t a, uint32_t w)
+__device__ __noinline__ void fb_mma_fwd(uint32_t d, uint32_t a, uint32_t w)
 {
     constexpr uint32_t id = tc::idesc_f16_f32_major(NET_TILE, N, 0, 0);
 #pragma unroll
@@ -510,7 +515,7 @@ __device__ __forceinline__ void fb_mma_fwd(uint32_t d, uint32_t a, uint32_t w)
 }
 // D[128 x 128] = dZ[128 x K_OUT] (K-major, tile of K_OUT columns) . W[K_OUT out][128 in] (MN-major)
 template <int K_OUT>
-__device__ __forceinline__ void fb_mma_dgrad(uint32_t d, uint32_t dz, uint32_t w)
+__device__ __noinline__ void fb_mma_dgrad(uint32_t d, uint32_t dz, uint32_t w)
 {
     constexpr uint32_t id = tc::idesc_f16_f32_major(NET_TILE, FN_W, 0, 1);
 #pragma unroll
@@ -520,7 +525,7 @@ __device__ __forceinline__ void fb_mma_dgrad(uint32_t d, uint32_t dz, uint32_t w
 }
 // G[128 x N] (+)= X[128 samples][128]^T . Y[128 samples][N]   (both MN-major, K = samples)
 template <int N>
-__device__ __forceinline__ void fb_mma_wgrad(uint32_t g, uint32_t x, uint32_t y, bool accumulate)
+__device__ __noinline__ void fb_mma_wgrad(uint32_t g, uint32_t x, uint32_t y, bool accumulate)
 {
     constexpr uint32_t id = tc::idesc_f16_f32_major(NET_TILE, N, 1, 1);
 #pragma unroll
@@ -529,11 +534,12 @@ __device__ __forceinline__ void fb_mma_wgrad(uint32_t g, uint32_t x, uint32_t y,
                        tc::smem_desc(y + ks * 2 * (N * 16), N * 16, 128), id, (accumulate || ks > 0) ? 1u : 0u);
 }
 
-// forward epilogue of one row: 128 fp32 -> ReLU -> fp16 -> this row of dst; mask = (activation > 0) per column
-__device__ __forceinline__ void fb_relu_row(uint32_t t_row, uint8_t* dst, int row, uint32_t (&mask)[4])
+// forward epilogue of one half row (columns 64 * half ..): fp32 -> ReLU -> fp16 -> dst; mask = (activation > 0)
+__device__ __forceinline__ void fb_relu_row(uint32_t t_row, uint8_t* dst, int row, int half, uint32_t (&mask)[2])
 {
 #pragma unroll
-    for (int q = 0; q < FN_W / 16; q++) {
+    for (int qq = 0; qq < FN_W / 32; qq++) {
+        const int q = 4 * half + qq;
         uint32_t r[16];
         tc::tmem_ld_x16(t_row + q * 16, r);
         tc::tmem_ld_wait();
@@ -544,21 +550,22 @@ __device__ __forceinline__ void fb_relu_row(uint32_t t_row, uint8_t* dst, int ro
             m |= ((pk[j] & 0xffffu) ? 1u : 0u) << (2 * j);
             m |= ((pk[j] >> 16) ? 1u : 0u) << (2 * j + 1);
         }
-        if (q & 1) mask[q >> 1] |= m << 16;
-        else mask[q >> 1] = m;
+        if (qq & 1) mask[qq >> 1] |= m << 16;
+        else mask[qq >> 1] = m;
         *reinterpret_cast<uint4*>(dst + tile_chunk_off(row, 2 * q, FN_W)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
         *reinterpret_cast<uint4*>(dst + tile_chunk_off(row, 2 * q + 1, FN_W)) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
     }
 }
-// dgrad epilogue of one row: 128 fp32 -> masked -> fp16 -> this row of dst
-__device__ __forceinline__ void fb_masked_row(uint32_t t_row, uint8_t* dst, int row, const uint32_t (&mask)[4])
+// dgrad epilogue of one half row: fp32 -> masked -> fp16 -> dst
+__device__ __forceinline__ void fb_masked_row(uint32_t t_row, uint8_t* dst, int row, int half, const uint32_t (&mask)[2])
 {
 #pragma unroll
-    for (int q = 0; q < FN_W / 16; q++) {
+    for (int qq = 0; qq < FN_W / 32; qq++) {
+        const int q = 4 * half + qq;
         uint32_t r[16];
         tc::tmem_ld_x16(t_row + q * 16, r);
         tc::tmem_ld_wait();
-        const uint32_t m = (q & 1) ? (mask[q >> 1] >> 16) : (mask[q >> 1] & 0xffffu);
+        const uint32_t m = (qq & 1) ? (mask[qq >> 1] >> 16) : (mask[qq >> 1] & 0xffffu);
         uint32_t pk[8];
 #pragma unroll
         for (int j = 0; j < 8; j++) {
@@ -582,6 +589,7 @@ freqnet_backward_kernel(const uint16_t* __restrict__ weights, const float* __res
     uint64_t* bar = reinterpret_cast<uint64_t*>(smem + FbSmem::BAR);
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + FbSmem::BAR + 8);
     const int tid = threadIdx.x, warp = tid >> 5;
+    const int row = tid & (NET_TILE - 1), half = tid >> 7;      // this thread's sample row and column half
     if (tid == 0) {
         tc::mbar_init(bar, 1);
         tc::fence_mbar_init();
@@ -593,11 +601,7 @@ freqnet_backward_kernel(const uint16_t* __restrict__ weights, const float* __res
     __syncthreads();
     tc::fence_after_thread_sync();
     const uint32_t tm = *tmem_slot;
-    const uint32_t t_row = tm + ((uint32_t)(warp * 32) << 16);
-    uint8_t* wb0 = smem + FbSmem::WB;
-    uint8_t* wb1 = smem + FbSmem::WB + FB_TILE_BYTES;
-    uint8_t* work = smem + FbSmem::WORK;
-    uint8_t* dout = smem + FbSmem::DOUT;
+    const uint32_t t_row = tm + ((uint32_t)((warp & 3) * 32) << 16);     // TMEM lane quarter = warp % 4
     uint32_t phase = 0;
     bool have = false;      // the three gradient accumulators hold at least one tile
 
@@ -619,7 +623,7 @@ freqnet_backward_kernel(const uint16_t* __restrict__ weights, const float* __res
         tc::fence_after_thread_sync();              \
     } while (0)
 #define FB_KEEP(l) ((l) >= l0 && (l) < l0 + 3)
-#define FB_X(l) (FB_KEEP(l) ? smem + FbSmem::XK + ((l) - l0) * FB_TILE_BYTES : work)
+#define FB_X(l) (FB_KEEP(l) ? sm + FbSmem::XK + ((l) - l0) * FB_TILE_BYTES : work)
 
     long long n = n_max;
     if (d_count) {
@@ -628,10 +632,19 @@ freqnet_backward_kernel(const uint16_t* __restrict__ weights, const float* __res
     }
     const long long n_tiles = (n + NET_TILE - 1) / NET_TILE;
     for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-        const long long s = tile * NET_TILE + tid;
+        // every operand address of the tile derives from `sm`, opaque per iteration: left alone, the compiler
+        // hoists the ~250 loop-invariant 64-bit matrix descriptors of the 17 phases out of the tile loop and
+        // spills them (255 registers, 2.8 KB of stack)
+        uint8_t* sm = smem;
+        asm volatile("" : "+l"(sm));
+        uint8_t* wb0 = sm + FbSmem::WB;
+        uint8_t* wb1 = sm + FbSmem::WB + FB_TILE_BYTES;
+        uint8_t* work = sm + FbSmem::WORK;
+        uint8_t* dout = sm + FbSmem::DOUT;
+        const long long s = tile * NET_TILE + row;
         const bool valid = s < n;
-        uint32_t mask[FN_HIDDEN][4];        // mask[l] = (X_{l+1} > 0), one bit per column of this row
-        frequency_row(samples + (valid ? s : 0) * stride, valid, SmemRowSink{FB_X(0), tid});
+        uint32_t mask[FN_HIDDEN][2];        // mask[l] = (X_{l+1} > 0), one bit per column of this thread's half row
+        if (half == 0) frequency_row(samples + (valid ? s : 0) * stride, valid, SmemRowSink{FB_X(0), row});
         // ---- forward recompute: X_{l+1} = relu(X_l . W_l^T); W_{l+1} is loaded under the MMA of layer l
 #pragma unroll
         for (int l = 0; l < FN_HIDDEN; l++) {
@@ -641,11 +654,11 @@ freqnet_backward_kernel(const uint16_t* __restrict__ weights, const float* __res
             uint8_t* wn = (l & 1) ? wb0 : wb1;
             FB_RUN(fb_mma_fwd<FN_W>(tm + FB_COL_D, tc::smem_u32(xc), tc::smem_u32(wc)),
                    fb_load_weights(wn, weights, l + 1, tid));
-            fb_relu_row(t_row + FB_COL_D, xn, tid, mask[l]);
+            fb_relu_row(t_row + FB_COL_D, xn, row, half, mask[l]);
         }
         uint8_t* x8 = FB_X(FN_HIDDEN);
         FB_RUN(fb_mma_fwd<NET_OUT>(tm + FB_COL_D, tc::smem_u32(x8), tc::smem_u32(wb0)), (void)0);
-        {   // dOut = g * act'(out) on (r,g,b,sigma); the 12 padding outputs carry no gradient
+        if (half == 0) {   // dOut = g * act'(out) on (r,g,b,sigma); the 12 padding outputs carry no gradient
             uint32_t r[16];
             output_row_load(t_row + FB_COL_D, r);
             float d[4] = {0.f, 0.f, 0.f, 0.f};
@@ -665,9 +678,9 @@ freqnet_backward_kernel(const uint16_t* __restrict__ weights, const float* __res
                 }
             }
             const __half2 d01 = __floats2half2_rn(d[0], d[1]), d23 = __floats2half2_rn(d[2], d[3]);
-            *reinterpret_cast<uint4*>(dout + tile_chunk_off(tid, 0, NET_OUT)) =
+            *reinterpret_cast<uint4*>(dout + tile_chunk_off(row, 0, NET_OUT)) =
                 make_uint4(*reinterpret_cast<const uint32_t*>(&d01), *reinterpret_cast<const uint32_t*>(&d23), 0u, 0u);
-            *reinterpret_cast<uint4*>(dout + tile_chunk_off(tid, 1, NET_OUT)) = make_uint4(0u, 0u, 0u, 0u);
+            *reinterpret_cast<uint4*>(dout + tile_chunk_off(row, 1, NET_OUT)) = make_uint4(0u, 0u, 0u, 0u);
         }
         // ---- output layer: dW_8^T [in][out] += X_8^T . dOut ;  D = dOut . W_8   (W_7 is still in the other slot)
         FB_RUN({
@@ -675,7 +688,7 @@ freqnet_backward_kernel(const uint16_t* __restrict__ weights, const float* __res
                 fb_mma_wgrad<NET_OUT>(tm + FB_COL_G(FN_HIDDEN - l0), tc::smem_u32(x8), tc::smem_u32(dout), have);
             fb_mma_dgrad<NET_OUT>(tm + FB_COL_D, tc::smem_u32(dout), tc::smem_u32(wb0));
         }, (void)0);
-        fb_masked_row(t_row + FB_COL_D, work, tid, mask[FN_HIDDEN - 1]);        // dZ_7
+        fb_masked_row(t_row + FB_COL_D, work, row, half, mask[FN_HIDDEN - 1]);        // dZ_7
         // ---- hidden layers 7 .. 1: dW_l += dZ_l^T . X_l ;  D = dZ_l . W_l ;  dZ_{l-1} = D masked by (X_l > 0).
         // W_{l-1} is loaded under the MMAs into the slot of W_{l+1} (done with); for l = 1 that fetches W_0 for
         // the next tile's forward
@@ -688,7 +701,7 @@ freqnet_backward_kernel(const uint16_t* __restrict__ weights, const float* __res
                     fb_mma_wgrad<FN_W>(tm + FB_COL_G(l - l0), tc::smem_u32(work), tc::smem_u32(FB_X(l)), have);
                 fb_mma_dgrad<FN_W>(tm + FB_COL_D, tc::smem_u32(work), tc::smem_u32(wc));
             }, fb_load_weights(wn, weights, l - 1, tid));
-            fb_masked_row(t_row + FB_COL_D, work, tid, mask[l - 1]);             // dZ_{l-1}
+            fb_masked_row(t_row + FB_COL_D, work, row, half, mask[l - 1]);             // dZ_{l-1}
         }
         // ---- layer 0: dW_0 += dZ_0^T . X_0 (nothing flows into the parameter-free encoding)
         if (FB_KEEP(0))
@@ -705,22 +718,25 @@ freqnet_backward_kernel(const uint16_t* __restrict__ weights, const float* __res
             const int l = l0 + i;
             if (l > FN_HIDDEN) break;
             float* gw = grad_weights + fn_layer_src(l);
-            if (l == FN_HIDDEN) {        // transposed accumulator [in = tid][out j]
-                uint32_t r[16];
-                tc::tmem_ld_x16(t_row + FB_COL_G(i), r);
-                tc::tmem_ld_wait();
+            if (l == FN_HIDDEN) {        // transposed accumulator [in = row][out j]
+                if (half == 0) {
+                    uint32_t r[16];
+                    tc::tmem_ld_x16(t_row + FB_COL_G(i), r);
+                    tc::tmem_ld_wait();
 #pragma unroll
-                for (int j = 0; j < NET_OUT; j++) atomicAdd(gw + j * FN_W + tid, __uint_as_float(r[j]));
+                    for (int j = 0; j < NET_OUT; j++) atomicAdd(gw + j * FN_W + row, __uint_as_float(r[j]));
+                }
             } else {
                 const int K = fn_layer_k(l);
 #pragma unroll 1
-                for (int q = 0; q < FN_W / 16; q++) {
+                for (int qq = 0; qq < FN_W / 32; qq++) {
+                    const int q = 4 * half + qq;
                     uint32_t r[16];
                     tc::tmem_ld_x16(t_row + FB_COL_G(i) + q * 16, r);
                     tc::tmem_ld_wait();
 #pragma unroll
                     for (int j = 0; j < 16; j++)
-                        if (q * 16 + j < K) atomicAdd(gw + (size_t)tid * K + q * 16 + j, __uint_as_float(r[j]));
+                        if (q * 16 + j < K) atomicAdd(gw + (size_t)row * K + q * 16 + j, __uint_as_float(r[j]));
                 }
             }
         }
