@@ -159,6 +159,21 @@ int rtxnerf_ray_march_csr(const rtxnerf_grid* grid, const rtxnerf_camera* cam,
                           const rtxnerf_hits* hits, void* workspace, size_t workspace_bytes,
                           void* stream);
 
+/* The same march with NO device allocation and no caller-provided workspace.  No counterpart in the
+ * reference: added for callers that cannot call cudaMalloc (code under
+ * CUDA graph capture, tight serving loops, harnesses that forbid it).  The scratch of rtxnerf_ray_march_csr
+ * lives in a file-scope device array of the library (~321 KB that every GPU which loads the library holds until
+ * exit), sized for at most rtxnerf_ray_march_csr_static_max_rays() = 2^21 rays per call (a 1920x1080 view
+ * fits); more rays are refused with RTXNERF_ECAPACITY.  max_hits <= 32 runs the one-pass kernel, larger caps run
+ * count -> scan -> fill.  Outputs are identical to rtxnerf_ray_march_csr's.  Every call on a device shares the
+ * array and finds the previous call's contents in it: the march itself clears, on `stream`, the words that must
+ * start at zero, and calls that OVERLAP on the GPU (different streams without a dependency) race on it —
+ * serialise them.  Calls cudaMalloc / cudaFree nowhere. */
+long long rtxnerf_ray_march_csr_static_max_rays(void);
+int rtxnerf_ray_march_csr_static(const rtxnerf_grid* grid, const rtxnerf_camera* cam,
+                                 long long ray_begin, long long n_rays, int max_hits,
+                                 const rtxnerf_hits* hits, void* stream);
+
 /* ------------------------------------------------------------------------------------
  * Sampler — replaces launchSampler (sampler/sampler.h:19-30, sampler/sampler.cu:105-131).
  * samples_per_segment is the reference's NUM_SAMPLES_PER_SEGMENT (sampler.h:4, 32) made a

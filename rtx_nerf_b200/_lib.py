@@ -84,6 +84,9 @@ SIGNATURES = {
     "rtxnerf_ray_march_workspace_bytes_for": (c_size_t, [c_ll, c_int]),
     "rtxnerf_ray_march_csr": (c_int, [c_void_p, C.POINTER(Camera), c_ll, c_ll, c_int, C.POINTER(Hits),
                                       c_void_p, c_size_t, c_void_p]),
+    "rtxnerf_ray_march_csr_static_max_rays": (c_ll, []),
+    "rtxnerf_ray_march_csr_static": (c_int, [c_void_p, C.POINTER(Camera), c_ll, c_ll, c_int, C.POINTER(Hits),
+                                             c_void_p]),
     "rtxnerf_launch_sampler": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,
                                        c_void_p, c_void_p, c_int, c_int, c_void_p]),
     "rtxnerf_launch_sampler_seeded": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,

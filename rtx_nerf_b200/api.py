@@ -290,6 +290,24 @@ def ray_march_csr(grid, look_at_dev, focal_length, aspect_ratio, width, height, 
     _lib.count_launches(3 if n_rays > 0 else 0)
 
 
+def ray_march_csr_static(grid, look_at_dev, focal_length, aspect_ratio, width, height, hits, max_hits, ray_begin=0,
+                         n_rays=None, stream=None):
+    """ray_march_csr through rtxnerf_ray_march_csr_static: no device allocation, the scratch is a device array
+    inside the library (at most rtxnerf_ray_march_csr_static_max_rays() rays per call; calls that overlap on the
+    GPU race on it).  No counterpart in the reference (include/rtxnerf.h).  `hits.workspace` is not used."""
+    _chk_dev(look_at_dev, torch.float32, "look_at")
+    if n_rays is None:
+        n_rays = width * height - ray_begin
+    if n_rays > hits.n_rays:
+        raise ValueError("HitBuffers too small for %d rays" % n_rays)
+    cam = _lib.Camera(_p(look_at_dev), float(focal_length), float(aspect_ratio), int(width), int(height))
+    st = hits.c_struct()
+    _lib.check(_lib.load().rtxnerf_ray_march_csr_static(grid._h, C.byref(cam), int(ray_begin), int(n_rays),
+                                                        int(max_hits), C.byref(st), _stream_ptr(stream)),
+               "ray_march_csr_static")
+    _lib.count_launches(3 if n_rays > 0 else 0)
+
+
 def cell_radiance(hit_cells, total_hits, capacity_hits, samples_per_segment, cell_rgbs, radiance, stream=None):
     """BASELINE config 1: fixed per-cell (r,g,b,sigma) stands in for the network."""
     _lib.check(_lib.load().rtxnerf_cell_radiance(_p(hit_cells), _p(total_hits), int(capacity_hits),

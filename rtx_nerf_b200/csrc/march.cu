@@ -1018,3 +1018,44 @@ extern "C" int rtxnerf_ray_march_dense(const rtxnerf_params* p, void* stream)
         p->ray_origins, fo);
     return rtx_launch_status();
 }
+
+// ------------------------------------------------------------------------------------ no-allocation march
+// rtxnerf_ray_march_csr_static: the CSR march for callers that cannot allocate (CUDA graph capture, serving
+// loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The scratch rtxnerf_ray_march_csr takes from its caller (block offsets / block sums of the
+// two-pass path, the look-back status words and the tile ticket of the one-pass path) lives in this file-scope
+// device array instead: RTXNERF_MARCH_STATIC_MAX_RAYS rays at most (2^21: a 1920x1080 view fits), ~321 KB that
+// every GPU which loads the library holds until exit.  The array is shared by every call on a device and keeps
+// the last call's contents: the march clears the words that must start at zero (status + ticket) itself on
+// `stream`, and two calls that overlap on the GPU (different streams, no dependency) race on it.
+// In host code `g_march_static_scratch` is only a stand-in for the symbol: the device address comes from
+// cudaGetSymbolAddress, once per device, with that device current.
+#define RTXNERF_MARCH_STATIC_MAX_RAYS (1ll << 21)
+#define MARCH_STATIC_BLOCKS (RTXNERF_MARCH_STATIC_MAX_RAYS / MARCH_BLOCK)
+// the layout rtxnerf_ray_march_workspace_bytes() describes, for MARCH_STATIC_BLOCKS tiles
+#define MARCH_STATIC_BYTES                                                                          \
+    ((size_t)MARCH_STATIC_BLOCKS * sizeof(long long) + (((size_t)MARCH_STATIC_BLOCKS * sizeof(int) + 7) & ~(size_t)7) + \
+     (size_t)MARCH_STATIC_BLOCKS * sizeof(unsigned long long) + sizeof(unsigned long long) + 256)
+static __device__ __align__(256) unsigned char g_march_static_scratch[MARCH_STATIC_BYTES];
+
+extern "C" long long rtxnerf_ray_march_csr_static_max_rays(void) { return RTXNERF_MARCH_STATIC_MAX_RAYS; }
+
+extern "C" int rtxnerf_ray_march_csr_static(const rtxnerf_grid* grid, const rtxnerf_camera* cam, long long ray_begin,
+                                            long long n_rays, int max_hits, const rtxnerf_hits* hits, void* stream)
+{
+    if (n_rays > RTXNERF_MARCH_STATIC_MAX_RAYS) return RTXNERF_ECAPACITY;   // beyond the built-in scratch
+    static std::atomic<void*> scratch_of_device[256];
+    int dev = 0;
+    RTX_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 256) return RTXNERF_EINVAL;
+    void* ptr = scratch_of_device[dev].load(std::memory_order_acquire);
+    if (!ptr) {
+        RTX_CUDA_TRY(cudaGetSymbolAddress(&ptr, g_march_static_scratch));
+        if (!ptr) return RTXNERF_ENOMEM;
+        scratch_of_device[dev].store(ptr, std::memory_order_release);      // racing threads store the same address
+    }
+    // workspace_bytes = the base size: max_hits <= 32 is the one-pass kernel, larger caps take count -> scan ->
+    // fill (the staged one-pass path would need a slab of hit records that does not belong in a static array)
+    return rtxnerf_ray_march_csr(grid, cam, ray_begin, n_rays, max_hits, hits, ptr,
+                                 rtxnerf_ray_march_workspace_bytes(RTXNERF_MARCH_STATIC_MAX_RAYS), stream);
+}
