@@ -118,13 +118,15 @@ struct AxisState {
 
 __device__ __forceinline__ void axis_enter(AxisState& a, float o, float d, float r, int G, float L, float half_g)
 {
-    // cell containing o (planes compared exactly), clamped to the grid
+    // cell containing o (planes compared exactly), clamped to the grid.  The estimate e = floor(RN(o+1) * G/2)
+    // is never below the true index and at most one above it: o >= plane_i <=> o+1 >= i*L exactly, RN is monotone
+    // and i*L is representable, so RN(o+1) >= i*L; and o < plane_(i+1) gives RN(o+1) <= (i+1)*L, equality only by
+    // rounding up.  One conditional decrement therefore lands on the cell locate_cell's loops find (outside the
+    // grid the clamp decides; certified origins are finite).
     int i = (int)floorf(rn_mul(rn_add(o, 1.0f), half_g));
     i = max(0, min(G - 1, i));
-    float lo = plane_at(i, L);
-    while (i > 0 && o < lo) { i--; lo = plane_at(i, L); }
-    float hi = plane_at(i + 1, L);
-    while (i < G - 1 && o >= hi) { i++; lo = hi; hi = plane_at(i + 1, L); }
+    if (i > 0 && o < plane_at(i, L)) i--;
+    const float lo = plane_at(i, L), hi = plane_at(i + 1, L);
     const float tl = div_exact(rn_sub(lo, o), d, r), th = div_exact(rn_sub(hi, o), d, r);
     const bool neg = d < 0.0f;
     a.i = i;

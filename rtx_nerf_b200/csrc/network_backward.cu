@@ -51,30 +51,32 @@ template <int N, int K>
 __device__ __forceinline__ void mma_fwd(uint32_t d, uint32_t a, uint32_t w)
 {
     constexpr uint32_t id = tc::idesc_f16_f32_major(NET_TILE, N, 0, 0);
+    const uint64_t da = tc::smem_desc(a, 128, K * 16), dw = tc::smem_desc(w, 128, K * 16);
 #pragma unroll
     for (int ks = 0; ks < K / 16; ks++)
-        tc::mma_f16_ss(d, tc::smem_desc(a + ks * 256, 128, K * 16), tc::smem_desc(w + ks * 256, 128, K * 16), id,
-                       ks > 0 ? 1u : 0u);
+        tc::mma_f16_ss(d, tc::smem_desc_advance(da, ks * 256), tc::smem_desc_advance(dw, ks * 256), id, ks > 0 ? 1u : 0u);
 }
 // dgrad: D[128 x N_in] = dH[128 x K_out] (K-major, tile of K_out columns) . W[K_out][N_in] (MN-major B)
 template <int N_IN, int K_OUT>
 __device__ __forceinline__ void mma_dgrad(uint32_t d, uint32_t dh, uint32_t w)
 {
     constexpr uint32_t id = tc::idesc_f16_f32_major(NET_TILE, N_IN, 0, 1);
+    const uint64_t dd = tc::smem_desc(dh, 128, K_OUT * 16), dw = tc::smem_desc(w, N_IN * 16, 128);
 #pragma unroll
     for (int ks = 0; ks < K_OUT / 16; ks++)
-        tc::mma_f16_ss(d, tc::smem_desc(dh + ks * 256, 128, K_OUT * 16),
-                       tc::smem_desc(w + ks * 2 * (N_IN * 16), N_IN * 16, 128), id, ks > 0 ? 1u : 0u);
+        tc::mma_f16_ss(d, tc::smem_desc_advance(dd, ks * 256), tc::smem_desc_advance(dw, ks * 2 * (N_IN * 16)), id,
+                       ks > 0 ? 1u : 0u);
 }
 // wgrad: G[64 x N] (+)= X[128 samples][64]^T . Y[128 samples][N]   (both MN-major, K = samples)
 template <int N>
 __device__ __forceinline__ void mma_wgrad(uint32_t g, uint32_t x, uint32_t y, bool accumulate)
 {
     constexpr uint32_t id = tc::idesc_f16_f32_major(64, N, 1, 1);
+    const uint64_t dx = tc::smem_desc(x, NET_W * 16, 128), dy = tc::smem_desc(y, N * 16, 128);
 #pragma unroll
     for (int ks = 0; ks < NET_TILE / 16; ks++)
-        tc::mma_f16_ss(g, tc::smem_desc(x + ks * 2 * (NET_W * 16), NET_W * 16, 128),
-                       tc::smem_desc(y + ks * 2 * (N * 16), N * 16, 128), id, (accumulate || ks > 0) ? 1u : 0u);
+        tc::mma_f16_ss(g, tc::smem_desc_advance(dx, ks * 2 * (NET_W * 16)), tc::smem_desc_advance(dy, ks * 2 * (N * 16)), id,
+                       (accumulate || ks > 0) ? 1u : 0u);
 }
 
 // dgrad epilogue: TMEM row -> masked by ReLU'(h) (h = this row of the forward tile) -> fp16 tile
@@ -138,7 +140,7 @@ mlp_backward_kernel(const uint16_t* __restrict__ weights, const uint16_t* __rest
         tc::fence_proxy_async_smem();
         tc::fence_before_thread_sync();
         __syncthreads();
-        if (tid == 0) {
+        if (warp == 0 && tc::elect_one()) {     // one lane of the converged warp 0 (tcgen05.cuh: elect_one)
             tc::fence_after_thread_sync();
             issue();
             tc::mma_commit(bar);

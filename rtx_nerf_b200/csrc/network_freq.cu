@@ -319,8 +319,8 @@ freqnet_forward_kernel(const uint8_t* __restrict__ packed, const float* __restri
             first = false;
         }
     } else if (warp == FN_WARP_MMA) {
-        // ------------------------------------------------ MMA issue
-        if (lane == 0) {
+        // ------------------------------------------------ MMA issue (one elected lane: tcgen05.cuh elect_one)
+        if (tc::elect_one()) {
             uint32_t cnt = 0, a_par0 = 0, a_par1 = 0, e_par = 0, o_par = 0;
             bool first_pair = true;
             int tr = 0;
@@ -508,30 +508,32 @@ template <int N>
 __device__ __noinline__ void fb_mma_fwd(uint32_t d, uint32_t a, uint32_t w)
 {
     constexpr uint32_t id = tc::idesc_f16_f32_major(NET_TILE, N, 0, 0);
+    const uint64_t da = tc::smem_desc(a, 128, FN_W * 16), dw = tc::smem_desc(w, 128, FN_W * 16);
 #pragma unroll
     for (int ks = 0; ks < FN_W / 16; ks++)
-        tc::mma_f16_ss(d, tc::smem_desc(a + ks * 256, 128, FN_W * 16), tc::smem_desc(w + ks * 256, 128, FN_W * 16), id,
-                       ks > 0 ? 1u : 0u);
+        tc::mma_f16_ss(d, tc::smem_desc_advance(da, ks * 256), tc::smem_desc_advance(dw, ks * 256), id, ks > 0 ? 1u : 0u);
 }
 // D[128 x 128] = dZ[128 x K_OUT] (K-major, tile of K_OUT columns) . W[K_OUT out][128 in] (MN-major)
 template <int K_OUT>
 __device__ __noinline__ void fb_mma_dgrad(uint32_t d, uint32_t dz, uint32_t w)
 {
     constexpr uint32_t id = tc::idesc_f16_f32_major(NET_TILE, FN_W, 0, 1);
+    const uint64_t dd = tc::smem_desc(dz, 128, K_OUT * 16), dw = tc::smem_desc(w, FN_W * 16, 128);
 #pragma unroll
     for (int ks = 0; ks < K_OUT / 16; ks++)
-        tc::mma_f16_ss(d, tc::smem_desc(dz + ks * 256, 128, K_OUT * 16),
-                       tc::smem_desc(w + ks * 2 * (FN_W * 16), FN_W * 16, 128), id, ks > 0 ? 1u : 0u);
+        tc::mma_f16_ss(d, tc::smem_desc_advance(dd, ks * 256), tc::smem_desc_advance(dw, ks * 2 * (FN_W * 16)), id,
+                       ks > 0 ? 1u : 0u);
 }
 // G[128 x N] (+)= X[128 samples][128]^T . Y[128 samples][N]   (both MN-major, K = samples)
 template <int N>
 __device__ __noinline__ void fb_mma_wgrad(uint32_t g, uint32_t x, uint32_t y, bool accumulate)
 {
     constexpr uint32_t id = tc::idesc_f16_f32_major(NET_TILE, N, 1, 1);
+    const uint64_t dx = tc::smem_desc(x, FN_W * 16, 128), dy = tc::smem_desc(y, N * 16, 128);
 #pragma unroll
     for (int ks = 0; ks < NET_TILE / 16; ks++)
-        tc::mma_f16_ss(g, tc::smem_desc(x + ks * 2 * (FN_W * 16), FN_W * 16, 128),
-                       tc::smem_desc(y + ks * 2 * (N * 16), N * 16, 128), id, (accumulate || ks > 0) ? 1u : 0u);
+        tc::mma_f16_ss(g, tc::smem_desc_advance(dx, ks * 2 * (FN_W * 16)), tc::smem_desc_advance(dy, ks * 2 * (N * 16)), id,
+                       (accumulate || ks > 0) ? 1u : 0u);
 }
 
 // forward epilogue of one half row (columns 64 * half ..): fp32 -> ReLU -> fp16 -> dst; mask = (activation > 0)
@@ -612,7 +614,7 @@ freqnet_backward_kernel(const uint16_t* __restrict__ weights, const float* __res
         tc::fence_proxy_async_smem();               \
         tc::fence_before_thread_sync();             \
         __syncthreads();                            \
-        if (tid == 0) {                             \
+        if (warp == 0 && tc::elect_one()) {         \
             tc::fence_after_thread_sync();          \
             ISSUE;                                  \
             tc::mma_commit(bar);                    \

@@ -376,7 +376,7 @@ rays_roles_kernel(LeanLevels ll, Levels lv, const uint32_t* __restrict__ table32
                 // every row of the previous tile's output has been read: D is free
                 tc::fence_before_thread_sync();
                 rr_mlp_barrier();
-                if (mma_thread) {
+                if (rw == 0 && tc::elect_one()) {     // the converged issuing warp (tcgen05.cuh: elect_one)
                     rr_wait(enc_ready + b, (uint32_t)((m >> 1) & 1), a.wait_ticks);
                     tc::fence_after_thread_sync();
                     rr_issue_layer<NET_W, NET_IN>(tmem_base + RR_COL_D, tmem_base + RR_COL_AE + 16 * b, s_w0, mma_bar);
@@ -388,7 +388,7 @@ rays_roles_kernel(LeanLevels ll, Levels lv, const uint32_t* __restrict__ table32
                 rr_hidden_epilogue(t_d, t_ah);
                 tc::fence_before_thread_sync();
                 rr_mlp_barrier();
-                if (mma_thread) {
+                if (rw == 0 && tc::elect_one()) {     // the converged issuing warp (tcgen05.cuh: elect_one)
                     tc::fence_after_thread_sync();
                     rr_issue_layer<NET_W, NET_W>(tmem_base + RR_COL_D, tmem_base + RR_COL_AH, s_w1, mma_bar);
                 }
@@ -398,7 +398,7 @@ rays_roles_kernel(LeanLevels ll, Levels lv, const uint32_t* __restrict__ table32
                 rr_hidden_epilogue(t_d, t_ah);
                 tc::fence_before_thread_sync();
                 rr_mlp_barrier();
-                if (mma_thread) {
+                if (rw == 0 && tc::elect_one()) {     // the converged issuing warp (tcgen05.cuh: elect_one)
                     tc::fence_after_thread_sync();
                     rr_issue_layer<NET_OUT, NET_W>(tmem_base + RR_COL_D, tmem_base + RR_COL_AH, s_w2, mma_bar);
                 }

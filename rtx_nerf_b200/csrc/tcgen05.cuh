@@ -82,6 +82,27 @@ __device__ __forceinline__ uint64_t smem_desc(uint32_t saddr, uint32_t lbo_bytes
     d |= (uint64_t)1 << 46;
     return d;
 }
+// The descriptor of the same tile `bytes` further on (bytes a multiple of 16, the result still inside the
+// 256 KB shared window): one 64-bit add on the start-address field instead of rebuilding all fields per MMA.
+__device__ __forceinline__ uint64_t smem_desc_advance(uint64_t desc, uint32_t bytes) { return desc + (uint64_t)(bytes >> 4); }
+
+// One lane of a CONVERGED warp (all 32 lanes must execute this).  tcgen05.mma / commit take their operands
+// from uniform registers: under `if (tid == 0)` ptxas cannot prove a single active lane and wraps EVERY MMA
+// in an ELECT / R2UR / BRA.U.ANY loop (~14 instructions and their latencies per MMA, cuobjdump); under an
+// elect.sync predicate the descriptors are computed on the uniform datapath and the MMAs issue back to back.
+__device__ __forceinline__ bool elect_one()
+{
+    uint32_t pred;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred P;\n\t"
+        "elect.sync _|P, 0xffffffff;\n\t"
+        "selp.b32 %0, 1, 0, P;\n\t"
+        "}"
+        : "=r"(pred));
+    return pred != 0;
+}
+
 // K-major SWIZZLE_128B operand: rows of 128 bytes (64 fp16 of K), 8-row atoms of 1 KB whose
 // 16-byte chunks are XOR-ed with the row index; SBO = 1024 (next 8 rows), LBO unused, layout
 // type 2 at [61,64).  The tile base must be 1 KB-aligned; a K=16 slice inside the 128-byte row
