@@ -66,6 +66,7 @@ struct RrArgs {
     int groups_per_cta;   // consecutive 32-ray groups one CTA walks
     int wait_ticks;   // > 0: mbarrier waits carry this suspend-time hint (development knob)
     int mlp_last;     // 1: the MLP group is the LAST four warps of the CTA (development knob, see rr_launch)
+    int named_bars;   // 1: encoder -> MLP and MLP -> compositor hand-offs on named barriers, 0: on mbarriers (A/B knob)
 };
 
 __device__ __forceinline__ void rr_wait(uint64_t* bar, uint32_t parity, int ticks)
@@ -74,6 +75,22 @@ __device__ __forceinline__ void rr_wait(uint64_t* bar, uint32_t parity, int tick
     else tc::mbar_wait(bar, parity);
 }
 __device__ __forceinline__ void rr_mlp_barrier() { asm volatile("bar.sync 1, %0;" ::"n"(NET_TILE) : "memory"); }
+// Producer -> consumer hand-offs on HARDWARE named barriers: the producers bar.arrive (never block), the
+// consumers bar.sync and are descheduled until the count is reached.  The MLP group idles ~85 % of a tile period
+// waiting for an encoder group; on an mbarrier all of its 128 threads (and the compositor warp) polled try_wait
+// in a loop, ~11 % of the instructions this issue-bound kernel executed (ncu source page, profiles/r02_y).
+// ids: 0 __syncthreads, 1 the MLP group, 2 .. 2 + RR_BUFS - 1 operand buffer b (128 encoder + 128 MLP threads),
+// then two for the exchange buffers (128 MLP threads + the compositor warp); 14 of the 16 ids at EG = 5.
+#define RR_BAR_ENC 2
+#define RR_BAR_OUT(EG) (RR_BAR_ENC + RR_BUFS(EG))
+__device__ __forceinline__ void rr_named_sync(int id, int count)
+{
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory");
+}
+__device__ __forceinline__ void rr_named_arrive(int id, int count)
+{
+    asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(count) : "memory");
+}
 
 // segment-local sample parameter after i steps of 1/S (sampler.cu:54-66: t += 1.0f/S)
 __device__ __forceinline__ float rr_steps(float inv_s, int i, bool pow2)
@@ -298,7 +315,8 @@ rays_roles_kernel(LeanLevels ll, Levels lv, const uint32_t* __restrict__ table32
                 for (; l < NET_IN / 2; l++) emit1(l, 0u);     // fewer than 16 levels: the rest of the row is zero
                 tc::tmem_st_wait();
                 tc::fence_before_thread_sync();
-                tc::mbar_arrive(enc_ready + b);
+                if (a.named_bars) rr_named_arrive(RR_BAR_ENC + b, 2 * NET_TILE);
+                else tc::mbar_arrive(enc_ready + b);
             }
             t_mod = (t_mod + nt) % EG;
         }
@@ -321,7 +339,8 @@ rays_roles_kernel(LeanLevels ll, Levels lv, const uint32_t* __restrict__ table32
             float tau = 0.0f, t_prev = 0.0f, ax = 0.0f, ay = 0.0f, az = 0.0f;      // vol_render.cu:32-33
             for (int t = 0; t < nt; t++, T++) {
                 const int buf = T & 1;
-                rr_wait(out_ready + buf, (uint32_t)((T >> 1) & 1), a.wait_ticks);
+                if (a.named_bars) rr_named_sync(RR_BAR_OUT(EG) + buf, NET_TILE + 32);
+                else rr_wait(out_ready + buf, (uint32_t)((T >> 1) & 1), a.wait_ticks);
 #pragma unroll
                 for (int k = 0; k < 4; k++) {
                     const int q = 4 * t + k;
@@ -375,9 +394,10 @@ rays_roles_kernel(LeanLevels ll, Levels lv, const uint32_t* __restrict__ table32
                 const int b = 2 * e + (m & 1);
                 // every row of the previous tile's output has been read: D is free
                 tc::fence_before_thread_sync();
-                rr_mlp_barrier();
+                if (a.named_bars) rr_named_sync(RR_BAR_ENC + b, 2 * NET_TILE);   // D free AND the operand is there
+                else rr_mlp_barrier();
                 if (rw == 0 && tc::elect_one()) {     // the converged issuing warp (tcgen05.cuh: elect_one)
-                    rr_wait(enc_ready + b, (uint32_t)((m >> 1) & 1), a.wait_ticks);
+                    if (!a.named_bars) rr_wait(enc_ready + b, (uint32_t)((m >> 1) & 1), a.wait_ticks);
                     tc::fence_after_thread_sync();
                     rr_issue_layer<NET_W, NET_IN>(tmem_base + RR_COL_D, tmem_base + RR_COL_AE + 16 * b, s_w0, mma_bar);
                 }
@@ -411,7 +431,8 @@ rays_roles_kernel(LeanLevels ll, Levels lv, const uint32_t* __restrict__ table32
                     const int buf = T & 1;
                     if (T >= 2) rr_wait(out_free + buf, (uint32_t)(((T >> 1) - 1) & 1), a.wait_ticks);
                     exch[(buf * 4 + wk) * 32 + lane] = output_row_rgba(r, a.out_activation);
-                    tc::mbar_arrive(out_ready + buf);
+                    if (a.named_bars) rr_named_arrive(RR_BAR_OUT(EG) + buf, NET_TILE + 32);
+                    else tc::mbar_arrive(out_ready + buf);
                 } else {
                     const int q = 4 * t + wk;
                     if (q < ns) output_row_store(r, a.out_activation, first * S + q, a.out16, a.radiance4);

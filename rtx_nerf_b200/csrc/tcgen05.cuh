@@ -53,6 +53,21 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity)
 
 // the same wait with a suspend-time hint: the thread may sleep in hardware up to `ticks` before
 // try_wait returns false, so a long wait costs a handful of issue slots instead of a poll loop
+// non-blocking probe of a phase: true once the phase with this parity has completed
+__device__ __forceinline__ bool mbar_test(uint64_t* bar, uint32_t parity)
+{
+    uint32_t ok;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.b32 %0, 1, 0, p;\n\t"
+        "}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
 __device__ __forceinline__ void mbar_wait_sleep(uint64_t* bar, uint32_t parity, uint32_t ticks)
 {
     asm volatile(
