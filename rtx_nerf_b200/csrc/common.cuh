@@ -17,8 +17,13 @@ struct rtxnerf_grid {
     int G;
     size_t n_words;
     uint32_t* d_bits;   // G^3 bits, bit (p&31) of word (p>>5), p = (x*G+y)*G+z
+    unsigned long long* d_bricks;   // the same bits, one 64-bit word per 4x4x4 cells (march.cu: GridBits)
+    unsigned gb;                    // bricks per axis = ceil(G / 4)
     float* d_aabb;      // lazily built make_grid list (compat with Params.aabb)
 };
+
+// re-derive d_bricks from d_bits on `stream` (march.cu); every writer of d_bits calls it
+int rtx_grid_rebuild_bricks(const rtxnerf_grid* g, cudaStream_t stream);
 
 #define RTX_CUDA_TRY(expr)                      \
     do {                                        \

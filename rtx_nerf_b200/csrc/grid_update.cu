@@ -66,7 +66,9 @@ extern "C" int rtxnerf_grid_update_from_density(rtxnerf_grid* g, const float* d_
     const long long n = (long long)g->G * g->G * g->G;
     grid_update_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(n, d_sigma, sigma_stride, decay,
                                                                                     d_ema, threshold, g->d_bits);
-    return rtx_launch_status();
+    const int rc = rtx_launch_status();
+    if (rc) return rc;
+    return rtx_grid_rebuild_bricks(g, (cudaStream_t)stream);
 }
 
 extern "C" int rtxnerf_grid_read_bits(const rtxnerf_grid* g, uint32_t* bits_host)

@@ -65,6 +65,53 @@ __device__ __forceinline__ RayGen raygen(const float* __restrict__ l, float foca
     return r;
 }
 
+// ------------------------------------------------------------------------------------ occupancy bits
+// Two copies of the same G^3 bits live in a grid: the linear x-major array of the ABI (bit p & 31 of word p >> 5,
+// p = (x*G+y)*G+z) and a BRICK-ordered one, a 64-bit word per 4x4x4 cells (bit (x&3)<<4 | (y&3)<<2 | z&3 of
+// word ((x>>2)*GB + (y>>2))*GB + (z>>2), GB = ceil(G/4)), rebuilt on the device whenever the bits change.  The
+// sweep keeps the brick it is in in registers: one load serves every step the ray spends inside those 64 cells
+// (2.5-4 consecutive steps whatever the occupancy) and a 128-byte line covers a 3-D block of cells instead of
+// 1024 cells along z, where the linear order costs one L2-latency load per visited cell.  Which cells are
+// visited and how each is judged is unchanged — the hit lists are the same bits.
+struct GridBits {
+    const uint32_t* lin;
+    const unsigned long long* bricks;   // null: linear bits only (RTXNERF_MARCH_BRICKS=0)
+    unsigned gb;
+};
+struct BrickCache {
+    unsigned id;                        // brick whose word is cached; ~0u: none
+    unsigned long long word;
+};
+__device__ __forceinline__ bool cell_occupied(const GridBits& b, int G, unsigned x, unsigned y, unsigned z, BrickCache& c)
+{
+    if (b.bricks) {
+        const unsigned id = ((x >> 2) * b.gb + (y >> 2)) * b.gb + (z >> 2);
+        if (id != c.id) {
+            c.id = id;
+            c.word = __ldg(b.bricks + id);
+        }
+        return (c.word >> (((x & 3u) << 4) | ((y & 3u) << 2) | (z & 3u))) & 1ull;
+    }
+    const unsigned p = (x * (unsigned)G + y) * (unsigned)G + z;
+    return (__ldg(b.lin + (p >> 5)) >> (p & 31u)) & 1u;
+}
+
+__global__ void brick_build_kernel(const uint32_t* __restrict__ lin, int G, unsigned gb, unsigned long long* __restrict__ bricks)
+{
+    const long long id = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (id >= (long long)gb * gb * gb) return;
+    const unsigned bz = (unsigned)(id % gb), by = (unsigned)((id / gb) % gb), bx = (unsigned)(id / ((long long)gb * gb));
+    unsigned long long w = 0ull;
+    for (unsigned k = 0; k < 64u; k++) {
+        const unsigned x = 4u * bx + (k >> 4), y = 4u * by + ((k >> 2) & 3u), z = 4u * bz + (k & 3u);
+        if (x < (unsigned)G && y < (unsigned)G && z < (unsigned)G) {
+            const unsigned long long p = ((unsigned long long)x * G + y) * G + z;
+            w |= (unsigned long long)((__ldg(lin + (p >> 5)) >> (p & 31u)) & 1u) << k;
+        }
+    }
+    bricks[id] = w;
+}
+
 // ------------------------------------------------------------------------------------ sweep
 __device__ __forceinline__ float plane_at(int i, float L) { return rn_fma((float)i, L, -1.0f); }  // exact
 
@@ -140,7 +187,7 @@ __device__ __forceinline__ void axis_enter(AxisState& a, float o, float d, float
 // Certified operands only (every d normal and non-zero, every slab value finite): the sweep
 // direction and the exit candidate both follow the sign of d, so the state is (near, far).
 template <bool WANT_START, class Emit>
-__device__ __forceinline__ bool march_segment(const uint32_t* __restrict__ bits, int G, float L, float half_g,
+__device__ __forceinline__ bool march_segment(const GridBits& bits, int G, float L, float half_g,
                                               float& ox, float& oy, float& oz, float dx, float dy, float dz,
                                               float rx, float ry, float rz, int& nh, Emit& emit)
 {
@@ -151,12 +198,13 @@ __device__ __forceinline__ bool march_segment(const uint32_t* __restrict__ bits,
     // signed plane step per axis; the sign of d is fixed for the ray (d == 0 never advances)
     const float slx = dx < 0.0f ? -L : L, sly = dy < 0.0f ? -L : L, slz = dz < 0.0f ? -L : L;
     const int six = dx < 0.0f ? -1 : 1, siy = dy < 0.0f ? -1 : 1, siz = dz < 0.0f ? -1 : 1;
+    BrickCache brick{~0u, 0ull};
     for (;;) {
         // optixPrograms.cu:143-156 (fminf/fmaxf == PTX min/max: a NaN operand yields the other)
         const float txx = fmaxf(X.near_t, X.far_t), txy = fmaxf(Y.near_t, Y.far_t), txz = fmaxf(Z.near_t, Z.far_t);
-        const unsigned p = ((unsigned)X.i * (unsigned)G + (unsigned)Y.i) * (unsigned)G + (unsigned)Z.i;
-        const bool occ = (__ldg(bits + (p >> 5)) >> (p & 31u)) & 1u;
+        const bool occ = cell_occupied(bits, G, (unsigned)X.i, (unsigned)Y.i, (unsigned)Z.i, brick);
         if (occ) {
+            const unsigned p = ((unsigned)X.i * (unsigned)G + (unsigned)Y.i) * (unsigned)G + (unsigned)Z.i;
             const float tmin = fmaxf(fmaxf(fmaxf(-INFINITY, fminf(X.near_t, X.far_t)), fminf(Y.near_t, Y.far_t)),
                                      fminf(Z.near_t, Z.far_t));
             const float tmax = fminf(fminf(fminf(INFINITY, txx), txy), txz);
@@ -221,7 +269,7 @@ __device__ __forceinline__ int locate_cell(float ok, int G, float L, float half_
 }
 
 template <bool WANT_START, class Emit>
-__device__ __noinline__ bool march_segment_generic(const uint32_t* __restrict__ bits, int G, float L, float half_g,
+__device__ __noinline__ bool march_segment_generic(const GridBits& bits, int G, float L, float half_g,
                                                    float& ox, float& oy, float& oz, float dx, float dy, float dz,
                                                    int& nh, Emit& emit)
 {
@@ -231,13 +279,14 @@ __device__ __noinline__ bool march_segment_generic(const uint32_t* __restrict__ 
     float tlx = rn_div(rn_sub(plane_at(ix, L), ox), dx), thx = rn_div(rn_sub(plane_at(ix + 1, L), ox), dx);
     float tly = rn_div(rn_sub(plane_at(iy, L), oy), dy), thy = rn_div(rn_sub(plane_at(iy + 1, L), oy), dy);
     float tlz = rn_div(rn_sub(plane_at(iz, L), oz), dz), thz = rn_div(rn_sub(plane_at(iz + 1, L), oz), dz);
+    BrickCache brick{~0u, 0ull};
     for (;;) {
         if ((unsigned)ix >= (unsigned)G || (unsigned)iy >= (unsigned)G || (unsigned)iz >= (unsigned)G) return false;
         float txx = fmaxf(tlx, thx), txy = fmaxf(tly, thy), txz = fmaxf(tlz, thz);
         float tmin = fmaxf(fmaxf(fmaxf(-INFINITY, fminf(tlx, thx)), fminf(tly, thy)), fminf(tlz, thz));
         float tmax = fminf(fminf(fminf(INFINITY, txx), txy), txz);
         unsigned p = ((unsigned)ix * (unsigned)G + (unsigned)iy) * (unsigned)G + (unsigned)iz;
-        bool occ = (__ldg(bits + (p >> 5)) >> (p & 31u)) & 1u;
+        bool occ = cell_occupied(bits, G, (unsigned)ix, (unsigned)iy, (unsigned)iz, brick);
         if (occ && tmax > tmin) {
             float t = (tmin < 0.0f && tmax > CLAMP_EPS) ? 0.0f : tmin;
             if (t >= 0.0f && t <= RAY_TMAX) {
@@ -290,7 +339,7 @@ __device__ __noinline__ bool march_segment_generic(const uint32_t* __restrict__ 
 
 // Marches one ray; calls emit(j, HitRecord) for hit j.  Returns the number of hits (<= cap).
 template <bool WANT_START, class Emit>
-__device__ __forceinline__ int march_ray(const uint32_t* __restrict__ bits, int G, float ox, float oy,
+__device__ __forceinline__ int march_ray(const GridBits& bits, int G, float ox, float oy,
                                          float oz, float dx, float dy, float dz, int cap, Emit emit)
 {
     const float L = 2.0f / (float)G;
@@ -324,7 +373,7 @@ __device__ __forceinline__ int march_ray(const uint32_t* __restrict__ bits, int 
 __constant__ int c_enter_every = 4, c_enter_min = 12;
 
 template <bool WANT_START, class Emit>
-__device__ __forceinline__ int march_ray_flat(const uint32_t* __restrict__ bits, int G, float ox, float oy,
+__device__ __forceinline__ int march_ray_flat(const GridBits& bits, int G, float ox, float oy,
                                               float oz, float dx, float dy, float dz, int cap, bool valid,
                                               unsigned mask, Emit emit)
 {
@@ -339,6 +388,7 @@ __device__ __forceinline__ int march_ray_flat(const uint32_t* __restrict__ bits,
     X.near_t = X.far_t = X.far_plane = 0.f; X.i = 0;
     Y = X; Z = X;
     int nh = 0, since = 0;
+    BrickCache brick{~0u, 0ull};        // kept across the segments of the ray
     bool done = !valid || cap <= 0, need_enter = true;
     for (;;) {
         const unsigned live = __ballot_sync(mask, !done);
@@ -364,10 +414,10 @@ __device__ __forceinline__ int march_ray_flat(const uint32_t* __restrict__ bits,
         if (!need_enter && !done) {
             // one step of march_segment
             const float txx = fmaxf(X.near_t, X.far_t), txy = fmaxf(Y.near_t, Y.far_t), txz = fmaxf(Z.near_t, Z.far_t);
-            const unsigned p = ((unsigned)X.i * (unsigned)G + (unsigned)Y.i) * (unsigned)G + (unsigned)Z.i;
-            const bool occ = (__ldg(bits + (p >> 5)) >> (p & 31u)) & 1u;
+            const bool occ = cell_occupied(bits, G, (unsigned)X.i, (unsigned)Y.i, (unsigned)Z.i, brick);
             bool accepted = false;
             if (occ) {
+                const unsigned p = ((unsigned)X.i * (unsigned)G + (unsigned)Y.i) * (unsigned)G + (unsigned)Z.i;
                 const float tmin = fmaxf(fmaxf(fmaxf(-INFINITY, fminf(X.near_t, X.far_t)), fminf(Y.near_t, Y.far_t)),
                                          fminf(Z.near_t, Z.far_t));
                 const float tmax = fminf(fminf(fminf(INFINITY, txx), txy), txz);
@@ -434,7 +484,7 @@ struct CamArgs {
 
 // Pass 1: count hits per ray, write per-ray outputs and one partial sum per block.
 __global__ void __launch_bounds__(MARCH_BLOCK)
-march_count_kernel(const uint32_t* __restrict__ bits, int G, CamArgs cam, long long ray_begin, long long n_rays,
+march_count_kernel(GridBits bits, int G, CamArgs cam, long long ray_begin, long long n_rays,
                    int cap, int* __restrict__ num_hits, float* __restrict__ view_dirs,
                    float* __restrict__ ray_origins, int* __restrict__ block_sums)
 {
@@ -531,7 +581,7 @@ __device__ __forceinline__ void store_hit(const FillOut& o, long long slot, cons
 
 // Pass 3: block-local scan of the counts + block offset = CSR index; march again and store.
 __global__ void __launch_bounds__(MARCH_BLOCK)
-march_fill_kernel(const uint32_t* __restrict__ bits, int G, CamArgs cam, long long ray_begin, long long n_rays,
+march_fill_kernel(GridBits bits, int G, CamArgs cam, long long ray_begin, long long n_rays,
                   int cap, const int* __restrict__ num_hits, const long long* __restrict__ block_offsets,
                   int* __restrict__ indices, FillOut out)
 {
@@ -571,6 +621,9 @@ march_fill_kernel(const uint32_t* __restrict__ bits, int G, CamArgs cam, long lo
 //      profiles/r01_d_view_full.txt).  Entry points are rebuilt on the way out from the
 //      previous exit point (start = fma(t_start, d, o_prev), optixPrograms.cu:194-196).
 #define ONEPASS_MAX_CAP 32
+#ifndef MARCH_STAGED_MIN_CTAS
+#define MARCH_STAGED_MIN_CTAS 8      // the staged grid is sized for 8 CTAs per SM: hold the registers to 64
+#endif
 #define LOOKBACK_SPIN_LIMIT (1u << 24)
 
 __device__ __forceinline__ unsigned long long ld_status(const unsigned long long* p)
@@ -590,8 +643,8 @@ __device__ __forceinline__ void st_status(unsigned long long* p, unsigned long l
 // tiles, so the slabs stay a few hundred MB whatever the ray count; still ONE traversal per ray
 // (count -> scan -> fill walks every ray twice).
 template <bool STAGED, bool FLAT>
-__global__ void __launch_bounds__(MARCH_BLOCK)
-march_onepass_kernel(const uint32_t* __restrict__ bits, int G, CamArgs cam, long long ray_begin, long long n_rays,
+__global__ void __launch_bounds__(MARCH_BLOCK, STAGED ? MARCH_STAGED_MIN_CTAS : 1)
+march_onepass_kernel(GridBits bits, int G, CamArgs cam, long long ray_begin, long long n_rays,
                      int cap, int* __restrict__ num_hits, float* __restrict__ view_dirs,
                      float* __restrict__ ray_origins, int* __restrict__ indices, FillOut out,
                      unsigned long long* __restrict__ status, unsigned long long* __restrict__ ticket,
@@ -797,7 +850,7 @@ static size_t staged_slab_bytes(long long nb, int cap)
 
 // Dense layout of the reference (slot = ray*arr + j, optixPrograms.cu:184), one pass.
 __global__ void __launch_bounds__(MARCH_BLOCK)
-march_dense_kernel(const uint32_t* __restrict__ bits, int G, CamArgs cam, long long n_rays, int arr_size,
+march_dense_kernel(GridBits bits, int G, CamArgs cam, long long n_rays, int arr_size,
                    int* __restrict__ num_hits, float* __restrict__ view_dirs, float* __restrict__ ray_origins,
                    FillOut out)
 {
@@ -837,6 +890,19 @@ __global__ void make_grid_kernel(int G, float* __restrict__ aabb)
 // ------------------------------------------------------------------------------------ host ABI
 static bool valid_res(int G) { return G >= 2 && G <= 1024 && (G & (G - 1)) == 0; }
 
+int rtx_grid_rebuild_bricks(const rtxnerf_grid* g, cudaStream_t stream)
+{
+    const long long n = (long long)g->gb * g->gb * g->gb;
+    brick_build_kernel<<<(unsigned)((n + 127) / 128), 128, 0, stream>>>(g->d_bits, g->G, g->gb, g->d_bricks);
+    return rtx_launch_status();
+}
+// what the march kernels read: RTXNERF_MARCH_BRICKS=0 keeps them on the linear bits (development A/B)
+static GridBits grid_bits(const rtxnerf_grid* g)
+{
+    static const int use_bricks = rtx_env_int("RTXNERF_MARCH_BRICKS", 1);
+    return GridBits{g->d_bits, use_bricks ? g->d_bricks : nullptr, g->gb};
+}
+
 extern "C" int rtxnerf_grid_create(const uint32_t* occ_bits_host, int G, rtxnerf_grid** out)
 {
     if (!occ_bits_host || !out) return RTXNERF_EINVAL;
@@ -846,10 +912,16 @@ extern "C" int rtxnerf_grid_create(const uint32_t* occ_bits_host, int G, rtxnerf
     g->G = G;
     g->n_words = ((size_t)G * G * G + 31) / 32;
     g->d_aabb = nullptr;
+    g->d_bricks = nullptr;
+    g->gb = (unsigned)((G + 3) / 4);
     cudaError_t e = cudaMalloc(&g->d_bits, g->n_words * sizeof(uint32_t));
     if (e != cudaSuccess) { delete g; return (int)e; }
-    e = cudaMemcpy(g->d_bits, occ_bits_host, g->n_words * sizeof(uint32_t), cudaMemcpyHostToDevice);
+    e = cudaMalloc(&g->d_bricks, (size_t)g->gb * g->gb * g->gb * sizeof(unsigned long long));
     if (e != cudaSuccess) { cudaFree(g->d_bits); delete g; return (int)e; }
+    e = cudaMemcpy(g->d_bits, occ_bits_host, g->n_words * sizeof(uint32_t), cudaMemcpyHostToDevice);
+    int rc = e != cudaSuccess ? (int)e : rtx_grid_rebuild_bricks(g, (cudaStream_t)0);
+    if (!rc) rc = (int)cudaStreamSynchronize((cudaStream_t)0);
+    if (rc) { cudaFree(g->d_bits); cudaFree(g->d_bricks); delete g; return rc; }
     *out = g;
     return RTXNERF_OK;
 }
@@ -879,13 +951,14 @@ extern "C" int rtxnerf_grid_update(rtxnerf_grid* g, const uint32_t* occ_bits_hos
     if (!g || !occ_bits_host) return RTXNERF_EINVAL;
     RTX_CUDA_TRY(cudaMemcpyAsync(g->d_bits, occ_bits_host, g->n_words * sizeof(uint32_t), cudaMemcpyHostToDevice,
                                  (cudaStream_t)stream));
-    return RTXNERF_OK;
+    return rtx_grid_rebuild_bricks(g, (cudaStream_t)stream);
 }
 
 extern "C" int rtxnerf_grid_destroy(rtxnerf_grid* g)
 {
     if (!g) return RTXNERF_OK;
     cudaFree(g->d_bits);
+    cudaFree(g->d_bricks);
     if (g->d_aabb) cudaFree(g->d_aabb);
     delete g;
     return RTXNERF_OK;
@@ -974,7 +1047,7 @@ extern "C" int rtxnerf_ray_march_csr(const rtxnerf_grid* grid, const rtxnerf_cam
         RTX_CUDA_TRY(cudaMemsetAsync(status, 0, ((size_t)nb + 1) * sizeof(unsigned long long), s));
         auto kern = flat == 1 ? march_onepass_kernel<false, true> : march_onepass_kernel<false, false>;
         kern<<<(unsigned)nb, MARCH_BLOCK, smem, s>>>(
-            grid->d_bits, grid->G, c, ray_begin, n_rays, max_hits, hits->num_hits, hits->view_dirs,
+            grid_bits(grid), grid->G, c, ray_begin, n_rays, max_hits, hits->num_hits, hits->view_dirs,
             hits->ray_origins, hits->indices, fo, status, ticket, hits->total_hits, (int)nb, nullptr);
         return rtx_launch_status();
     }
@@ -994,15 +1067,15 @@ extern "C" int rtxnerf_ray_march_csr(const rtxnerf_grid* grid, const rtxnerf_cam
         RTX_CUDA_TRY(cudaMemsetAsync(status, 0, ((size_t)nb + 1) * sizeof(unsigned long long), s));
         auto kern = flat != 0 ? march_onepass_kernel<true, true> : march_onepass_kernel<true, false>;
         kern<<<(unsigned)staged_grid(nb), MARCH_BLOCK, smem, s>>>(
-            grid->d_bits, grid->G, c, ray_begin, n_rays, max_hits, hits->num_hits, hits->view_dirs,
+            grid_bits(grid), grid->G, c, ray_begin, n_rays, max_hits, hits->num_hits, hits->view_dirs,
             hits->ray_origins, hits->indices, fo, status, ticket, hits->total_hits, (int)nb, gstage);
         return rtx_launch_status();
     }
-    march_count_kernel<<<(unsigned)nb, MARCH_BLOCK, 0, s>>>(grid->d_bits, grid->G, c, ray_begin, n_rays, max_hits,
+    march_count_kernel<<<(unsigned)nb, MARCH_BLOCK, 0, s>>>(grid_bits(grid), grid->G, c, ray_begin, n_rays, max_hits,
                                                           hits->num_hits, hits->view_dirs, hits->ray_origins,
                                                           block_sums);
     block_scan_kernel<<<1, 1024, 0, s>>>(block_sums, (int)nb, block_offsets, hits->total_hits);
-    march_fill_kernel<<<(unsigned)nb, MARCH_BLOCK, 0, s>>>(grid->d_bits, grid->G, c, ray_begin, n_rays, max_hits,
+    march_fill_kernel<<<(unsigned)nb, MARCH_BLOCK, 0, s>>>(grid_bits(grid), grid->G, c, ray_begin, n_rays, max_hits,
                                                          hits->num_hits, block_offsets, hits->indices, fo);
     return rtx_launch_status(3);
 }
@@ -1016,7 +1089,7 @@ extern "C" int rtxnerf_ray_march_dense(const rtxnerf_params* p, void* stream)
     CamArgs c{p->look_at, p->focal_length, p->aspect_ratio, p->width, p->height};
     FillOut fo{p->t_start, p->t_end, p->start_points, p->end_points, nullptr, n_rays * p->intersection_arr_size};
     march_dense_kernel<<<(unsigned)((n_rays + MARCH_BLOCK - 1) / MARCH_BLOCK), MARCH_BLOCK, 0, (cudaStream_t)stream>>>(
-        grid->d_bits, grid->G, c, n_rays, p->intersection_arr_size, p->num_hits, p->viewing_direction,
+        grid_bits(grid), grid->G, c, n_rays, p->intersection_arr_size, p->num_hits, p->viewing_direction,
         p->ray_origins, fo);
     return rtx_launch_status();
 }
