@@ -288,6 +288,10 @@ mlp_backward_kernel(const uint16_t* __restrict__ weights, const uint16_t* __rest
 // run of consecutive lanes with equal cell (a segmented shuffle reduction whose run structure
 // comes from one ballot; it stops at the longest run) and only the head lane of a run issues
 // the reductions.
+// Tried and dropped (round 2): cutting long runs into pieces of at most 8 / 16 lanes to bound the shuffle rounds
+// (56 shuffles per level and warp on average, MIO the first stall reason).  It moves the load from the shuffles
+// to the L2 reductions, which are as close to their limit: 10.17 -> 9.99 ms on one training view, 15.3 -> 17.2 ms
+// on the store-fed batches of the bench (profiles/r02_bb_scatter_run_cap.txt).
 // ---------------------------------------------------------------------------------------
 #define HB_WARPS 8
 #ifndef HB_MIN_BLOCKS
@@ -296,8 +300,7 @@ mlp_backward_kernel(const uint16_t* __restrict__ weights, const uint16_t* __rest
 __global__ void __launch_bounds__(HB_WARPS * 32, HB_MIN_BLOCKS)
 hashgrid_backward_kernel(Levels lv, const float* __restrict__ samples, int stride,
                          const uint16_t* __restrict__ d_encoded, const int* __restrict__ num_hits,
-                         const int* __restrict__ indices, int n_rays, int S, float* __restrict__ grad_table,
-                         int max_run)
+                         const int* __restrict__ indices, int n_rays, int S, float* __restrict__ grad_table)
 {
     const unsigned FULL = 0xffffffffu;
     __shared__ uint32_t stage[HB_WARPS * 32][NET_IN / 2 + 1];   // +1: conflict-free per-thread rows
@@ -345,15 +348,15 @@ hashgrid_backward_kernel(Levels lv, const float* __restrict__ samples, int strid
                 const uint32_t k0 = live ? (pt.gx | (pt.gy << 16)) : 0xffffffffu;
                 const uint32_t k1 = live ? pt.gz : 0xffffffffu;
                 const uint32_t p0 = __shfl_up_sync(FULL, k0, 1), p1 = __shfl_up_sync(FULL, k1, 1);
-                const bool cell_head = lane == 0 || p0 != k0 || p1 != k1;
-                const unsigned cell_heads = __ballot_sync(FULL, cell_head);
+                const bool head = lane == 0 || p0 != k0 || p1 != k1;
+                const unsigned heads = __ballot_sync(FULL, head);
                 float v[16];
 #pragma unroll
                 for (int c = 0; c < 8; c++) {
                     v[2 * c] = pt.w[c] * gl.x;
                     v[2 * c + 1] = pt.w[c] * gl.y;
                 }
-                if (cell_heads == 1u) {
+                if (heads == 1u) {
                     // the whole warp sits in ONE cell (coarse levels): reduce-scatter instead of 5 x 16
                     // butterflies.  Two halving rounds leave each lane one x-pair quad (4 values), three
                     // plain rounds finish it: 24 shuffles instead of 80, and ONE 16-byte reduction per quad.
@@ -391,17 +394,10 @@ hashgrid_backward_kernel(Levels lv, const float* __restrict__ samples, int strid
                     }
                     continue;
                 }
-                // A run of equal cells longer than max_run lanes is cut into pieces of max_run (a power of two): the
-                // shuffle rounds stop at log2(max_run) — they were 56 shuffles per level and warp on average, the
-                // first stall reason of the kernel (MIO) — and each piece sends its own reductions; L2 had the room.
-                const int run_head = 31 - __clz(cell_heads & (0xffffffffu >> (31 - lane)));   // head lane of my run
-                const bool head = ((lane - run_head) & (max_run - 1)) == 0;
-                const unsigned heads = __ballot_sync(FULL, head);
-                // lanes i and i+d are in the same piece iff no head in (i, i+d]
+                // lanes i and i+d are in the same run iff no head in (i, i+d]
                 const unsigned after = lane < 31 ? (heads >> (lane + 1)) : 1u;
 #pragma unroll
                 for (int d = 1; d < 32; d <<= 1) {
-                    if (d >= max_run) break;
                     const bool same = (lane + d < 32) && (after & ((1u << d) - 1u)) == 0u;
                     if (!__any_sync(FULL, same)) break;     // longest run reached
 #pragma unroll
@@ -558,9 +554,9 @@ extern "C" int rtxnerf_mlp_backward(const rtxnerf_mlp* mlp, const uint16_t* d_en
     if (mlp->in_dim != NET_IN || mlp->width != NET_W || mlp->n_hidden != 2) return RTXNERF_ECONFIG;
     if (mlp->out_activation != 0 && mlp->out_activation != 1) return RTXNERF_ECONFIG;
     if (n_max == 0) return RTXNERF_OK;
-    const long long tiles = (n_max + NET_TILE - 1) / NET_TILE;
     static RtxPerDeviceOnce attr_set;
     RTX_CUDA_TRY((cudaError_t)rtx_set_max_smem(attr_set, mlp_backward_kernel, NbSmem::BYTES));
+    const long long tiles = (n_max + NET_TILE - 1) / NET_TILE;
     const long long resident = (long long)RTX_NUM_SMS * 2;   // 2 CTAs per SM: 2 x 256 TMEM columns, 2 x 75 KB
     mlp_backward_kernel<<<(unsigned)(tiles < resident ? tiles : resident), NET_TILE, NbSmem::BYTES, (cudaStream_t)stream>>>(
         mlp->weights, d_encoded, d_dl_dradiance, mlp->out_activation, d_count, count_scale, n_max, d_dencoded,
@@ -586,13 +582,9 @@ extern "C" int rtxnerf_hashgrid_backward_rays(const rtxnerf_hashgrid* enc, const
 #define HB_BLOCKS_PER_SM 64
 #endif
     const long long max_blocks = (long long)RTX_NUM_SMS * HB_BLOCKS_PER_SM;
-    // longest piece of a run of equal cells that is summed in registers before it goes to L2 (power of two)
-    static const int max_run_env = rtx_env_int("RTXNERF_HB_MAX_RUN", 8);
-    int max_run = 32;
-    while (max_run > 1 && max_run > max_run_env) max_run >>= 1;
     hashgrid_backward_kernel<<<(unsigned)(groups < max_blocks ? groups : max_blocks), HB_WARPS * 32, 0,
                                (cudaStream_t)stream>>>(lv, d_samples, sample_stride, d_dencoded, d_num_hits, d_indices,
-                                                       n_rays, samples_per_segment, d_grad_table, max_run);
+                                                       n_rays, samples_per_segment, d_grad_table);
     return rtx_launch_status();
 }
 

@@ -75,6 +75,30 @@ def test_grid_update_feeds_the_march(cuda_api, orc):
     assert np.array_equal(hb.hit_cells[:ora.total_hits].cpu().numpy(), ora.hit_prims)
 
 
+@pytest.mark.parametrize("G,max_hits", [(2, 6), (4, 12), (32, 12), (64, 40)])
+def test_host_bit_update_reaches_the_brick_copy(cuda_api, orc, G, max_hits):
+    """rtxnerf_grid_update replaces the linear bits; the march reads its brick-ordered copy (a 64-bit word per
+    4x4x4 cells, march.cu: GridBits), which every writer of the bits must rebuild — including grids smaller than
+    one brick (G = 2) and the staged path (max_hits > 32)."""
+    import torch
+    api = cuda_api
+    W, H = 40, 30
+    occ_a = synth.occupancy_bernoulli(G, 0.5, seed=11)
+    occ_b = synth.occupancy_bernoulli(G, 0.3, seed=12)
+    grid = api.OccupancyGrid.from_occupancy(occ_a, G)
+    pose, focal = synth.poses(1, seed=5)[0], synth.focal_length()
+    for occ in (occ_a, occ_b, occ_a):
+        grid.update(synth.pack_bits(occ))
+        hb = api.HitBuffers(W * H, W * H * max_hits)
+        api.ray_march_csr(grid, _t(pose.reshape(-1)), focal, W / H, W, H, hb, max_hits)
+        torch.cuda.synchronize()
+        ora = orc.ray_march_dda(pose, focal, W / H, W, H, occ, G, max_hits=max_hits, csr=True)
+        assert np.array_equal(hb.num_hits.cpu().numpy(), ora.num_hits)
+        assert np.array_equal(hb.hit_cells[:ora.total_hits].cpu().numpy(), ora.hit_prims)
+        assert np.array_equal(hb.end_points[:ora.total_hits].cpu().numpy(), ora.end_points)
+    grid.destroy()
+
+
 @pytest.mark.parametrize("sample_type,S", [(1, 32), (2, 32), (1, 5), (2, 4)])
 def test_seeded_sampling_modes(cuda_api, orc, sample_type, S):
     """STRATIFIED / UNIFORM with counter-based draws: bit-exact against the oracle, different seeds
