@@ -291,7 +291,11 @@ mlp_backward_kernel(const uint16_t* __restrict__ weights, const uint16_t* __rest
 // Tried and dropped (round 2): cutting long runs into pieces of at most 8 / 16 lanes to bound the shuffle rounds
 // (56 shuffles per level and warp on average, MIO the first stall reason).  It moves the load from the shuffles
 // to the L2 reductions, which are as close to their limit: 10.17 -> 9.99 ms on one training view, 15.3 -> 17.2 ms
-// on the store-fed batches of the bench (profiles/r02_bb_scatter_run_cap.txt).
+// on the store-fed batches of the bench (profiles/r02_bb_scatter_run_cap.txt).  Timed alone (a level mask), the
+// two coarsest levels cost 1.5 and 1.6 ms of the 5.8 ms and a fine level 0.4 ms: reductions on the same few
+// entries serialise in L2 (profiles/r02_bc_scatter_per_level.txt).  Collecting the coarse levels in a
+// shared-memory accumulator of the CTA (open addressing, shared-memory atomics, one flush per ray group) moved
+// that serialisation into shared memory and lost 2.5 ms (profiles/r02_bd_scatter_cta_accumulator.txt).
 // ---------------------------------------------------------------------------------------
 #define HB_WARPS 8
 #ifndef HB_MIN_BLOCKS
