@@ -1,13 +1,13 @@
 #!/bin/bash
-# One gpurun --gpus 2 call: the contract bench under torchrun at N = 2 (both arms).
+# One gpurun --gpus 8 call: two-device-thread test, the overlap check at N = 2, the contract bench at N = 8 and N = 2.
 TAG=${1:-x}
 O=gpurun_out/$TAG
 mkdir -p $O
-timeout 400 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29502 \
-  bench.py --gpus 2 --steps 20 --warmup 3 > $O/bench_n2.json 2> $O/bench_n2.err; echo "N=2 rc=$?" | tee -a $O/rc.txt
-tail -1 $O/bench_n2.json | cut -c1-250
-python -c "import json;d=json.loads(open('$O/bench_n2.json').read().strip().splitlines()[-1]);print(json.dumps(d['train_step'],indent=1))"
-tail -5 $O/bench_n2.err
-timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29512 \
-  bench.py --impl reference --gpus 2 --steps 2 --warmup 1 > $O/bench_ref_n2.json 2> $O/bench_ref_n2.err; echo "ref N=2 rc=$?" | tee -a $O/rc.txt
-tail -1 $O/bench_ref_n2.json | cut -c1-200
+timeout 600 python -m pytest tests/test_gpu_multidevice.py -x -q -m gpu > $O/pytest.log 2>&1; echo "pytest rc=$?" | tee -a $O/rc.txt
+timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 scripts/check_overlap.py > $O/overlap.log 2>&1; echo "overlap rc=$?" | tee -a $O/rc.txt
+grep "^rank" $O/overlap.log | head -4
+for N in 8 2; do
+  timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 2950$N \
+    bench.py --gpus $N --steps 20 --warmup 3 > $O/bench_n$N.json 2> $O/bench_n$N.err; echo "N=$N rc=$?" | tee -a $O/rc.txt
+  tail -1 $O/bench_n$N.json | cut -c1-200
+done
