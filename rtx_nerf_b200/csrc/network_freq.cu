@@ -471,21 +471,28 @@ struct FbSmem {
 #define FB_COL_D 0
 #define FB_COL_G(i) (128 + 128 * (i))
 
-// row-major [rows][K] fp16 layer -> core-matrix tile with 128 columns (columns >= K are zero)
+// row-major [rows][K] fp16 layer -> core-matrix tile with 128 columns (columns >= K are zero).  16-byte
+// cp.async copies: a chunk of eight K values of one row IS one row of a core matrix, so the layout change is
+// only the destination address; no registers, nothing for a thread to wait on until fb_weights_landed().
+// (Through registers the loads were 24 % of the kernel's stall samples and, with the compiler hoisting them
+// above barriers, the reason it ran at 255 registers + spills; ncu, profiles/r02_cc_freqnet_backward_lines.txt.)
 __device__ __forceinline__ void fb_load_weights(uint8_t* tile, const uint16_t* __restrict__ w, int l, int tid)
 {
     const int rows = fn_layer_n(l), K = fn_layer_k(l);
     const uint16_t* src = w + fn_layer_src(l);
-#pragma unroll 8
+    const uint32_t dst = tc::smem_u32(tile);
+#pragma unroll 4
     for (int i = tid; i < rows * 16; i += FB_THREADS) {
         const int r = i >> 4, c = i & 15;
-        uint4 v = make_uint4(0u, 0u, 0u, 0u);
-        // a volatile load: as plain read-only loads the compiler moved the copies of several phases above their
-        // barriers to hide latency and ran out of registers (255 + 2 KB of spill)
-        if (c * 8 < K) v = ld_stream_u4(reinterpret_cast<const uint4*>(src + (size_t)r * K + c * 8));
-        *reinterpret_cast<uint4*>(tile + tile_chunk_off(r, c, FN_W)) = v;
+        const bool real = c * 8 < K;             // padding columns: zero fill (source size 0)
+        const uint16_t* g = real ? src + (size_t)r * K + c * 8 : src;
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst + tile_chunk_off(r, c, FN_W)), "l"(g),
+                     "r"(real ? 16u : 0u)
+                     : "memory");
     }
+    asm volatile("cp.async.commit_group;" ::: "memory");
 }
+__device__ __forceinline__ void fb_weights_landed() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
 struct SmemRowSink {       // frequency_row -> this thread's row of a [128][128] core-matrix tile
     uint8_t* tile;
@@ -540,44 +547,49 @@ __device__ __noinline__ void fb_mma_wgrad(uint32_t g, uint32_t x, uint32_t y, bo
 __device__ __forceinline__ void fb_relu_row(uint32_t t_row, uint8_t* dst, int row, int half, uint32_t (&mask)[2])
 {
 #pragma unroll
-    for (int qq = 0; qq < FN_W / 32; qq++) {
-        const int q = 4 * half + qq;
-        uint32_t r[16];
-        tc::tmem_ld_x16(t_row + q * 16, r);
+    for (int hh = 0; hh < FN_W / 64; hh++) {        // 32 columns per step: both loads are issued before the wait
+        const int q = 4 * half + 2 * hh;
+        uint32_t r[32];
+        tc::tmem_ld_x16(t_row + q * 16, *reinterpret_cast<uint32_t(*)[16]>(r));
+        tc::tmem_ld_x16(t_row + q * 16 + 16, *reinterpret_cast<uint32_t(*)[16]>(r + 16));
         tc::tmem_ld_wait();
-        uint32_t pk[8], m = 0u;
+        uint32_t pk[16], m = 0u;
 #pragma unroll
-        for (int j = 0; j < 8; j++) {
+        for (int j = 0; j < 16; j++) {
             pk[j] = relu_pack_f16x2(__uint_as_float(r[2 * j]), __uint_as_float(r[2 * j + 1]));
             m |= ((pk[j] & 0xffffu) ? 1u : 0u) << (2 * j);
             m |= ((pk[j] >> 16) ? 1u : 0u) << (2 * j + 1);
         }
-        if (qq & 1) mask[qq >> 1] |= m << 16;
-        else mask[qq >> 1] = m;
-        *reinterpret_cast<uint4*>(dst + tile_chunk_off(row, 2 * q, FN_W)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-        *reinterpret_cast<uint4*>(dst + tile_chunk_off(row, 2 * q + 1, FN_W)) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+        mask[hh] = m;
+#pragma unroll
+        for (int c = 0; c < 4; c++)
+            *reinterpret_cast<uint4*>(dst + tile_chunk_off(row, 2 * q + c, FN_W)) =
+                make_uint4(pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
     }
 }
 // dgrad epilogue of one half row: fp32 -> masked -> fp16 -> dst
 __device__ __forceinline__ void fb_masked_row(uint32_t t_row, uint8_t* dst, int row, int half, const uint32_t (&mask)[2])
 {
 #pragma unroll
-    for (int qq = 0; qq < FN_W / 32; qq++) {
-        const int q = 4 * half + qq;
-        uint32_t r[16];
-        tc::tmem_ld_x16(t_row + q * 16, r);
+    for (int hh = 0; hh < FN_W / 64; hh++) {
+        const int q = 4 * half + 2 * hh;
+        uint32_t r[32];
+        tc::tmem_ld_x16(t_row + q * 16, *reinterpret_cast<uint32_t(*)[16]>(r));
+        tc::tmem_ld_x16(t_row + q * 16 + 16, *reinterpret_cast<uint32_t(*)[16]>(r + 16));
         tc::tmem_ld_wait();
-        const uint32_t m = (qq & 1) ? (mask[qq >> 1] >> 16) : (mask[qq >> 1] & 0xffffu);
-        uint32_t pk[8];
+        const uint32_t m = mask[hh];
+        uint32_t pk[16];
 #pragma unroll
-        for (int j = 0; j < 8; j++) {
+        for (int j = 0; j < 16; j++) {
             const float a = ((m >> (2 * j)) & 1u) ? __uint_as_float(r[2 * j]) : 0.0f;
             const float b = ((m >> (2 * j + 1)) & 1u) ? __uint_as_float(r[2 * j + 1]) : 0.0f;
             const __half2 v = __floats2half2_rn(a, b);
             pk[j] = *reinterpret_cast<const uint32_t*>(&v);
         }
-        *reinterpret_cast<uint4*>(dst + tile_chunk_off(row, 2 * q, FN_W)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-        *reinterpret_cast<uint4*>(dst + tile_chunk_off(row, 2 * q + 1, FN_W)) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+#pragma unroll
+        for (int c = 0; c < 4; c++)
+            *reinterpret_cast<uint4*>(dst + tile_chunk_off(row, 2 * q + c, FN_W)) =
+                make_uint4(pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
     }
 }
 
@@ -598,6 +610,7 @@ freqnet_backward_kernel(const uint16_t* __restrict__ weights, const float* __res
     }
     if (warp == 0) tc::tmem_alloc<512>(tmem_slot);
     fb_load_weights(smem + FbSmem::WB, weights, 0, tid);
+    fb_weights_landed();
     tc::fence_proxy_async_smem();
     tc::fence_before_thread_sync();
     __syncthreads();
@@ -611,6 +624,7 @@ freqnet_backward_kernel(const uint16_t* __restrict__ weights, const float* __res
     // (a macro, not a lambda: by-reference captures pushed the mask registers into local memory)
 #define FB_RUN(ISSUE, UNDER)                        \
     do {                                            \
+        fb_weights_landed();                        \
         tc::fence_proxy_async_smem();               \
         tc::fence_before_thread_sync();             \
         __syncthreads();                            \
@@ -694,16 +708,24 @@ freqnet_backward_kernel(const uint16_t* __restrict__ weights, const float* __res
         // ---- hidden layers 7 .. 1: dW_l += dZ_l^T . X_l ;  D = dZ_l . W_l ;  dZ_{l-1} = D masked by (X_l > 0).
         // W_{l-1} is loaded under the MMAs into the slot of W_{l+1} (done with); for l = 1 that fetches W_0 for
         // the next tile's forward
+        // A launch that keeps layers l0 .. l0 + 2 needs the chain only down to dZ_{l0}: below its lowest layer
+        // nothing is computed (launches 3 / 6 stop after 6 / 3 of the 9 backward phases).  Its last phase is the
+        // weight gradient of layer l0 alone, under which W_0 is fetched for the next tile's forward.
 #pragma unroll
         for (int l = FN_HIDDEN - 1; l >= 1; l--) {
+            if (l < l0) break;
             uint8_t* wc = (l & 1) ? wb1 : wb0;
             uint8_t* wn = (l & 1) ? wb0 : wb1;
+            const bool last = l == l0;
             FB_RUN({
                 if (FB_KEEP(l))
                     fb_mma_wgrad<FN_W>(tm + FB_COL_G(l - l0), tc::smem_u32(work), tc::smem_u32(FB_X(l)), have);
-                fb_mma_dgrad<FN_W>(tm + FB_COL_D, tc::smem_u32(work), tc::smem_u32(wc));
-            }, fb_load_weights(wn, weights, l - 1, tid));
-            fb_masked_row(t_row + FB_COL_D, work, row, half, mask[l - 1]);             // dZ_{l-1}
+                if (!last) fb_mma_dgrad<FN_W>(tm + FB_COL_D, tc::smem_u32(work), tc::smem_u32(wc));
+            }, {
+                if (last) fb_load_weights(wb0, weights, 0, tid);
+                else if (l - 1 != l0 || l0 == 0) fb_load_weights(wn, weights, l - 1, tid);
+            });
+            if (!last) fb_masked_row(t_row + FB_COL_D, work, row, half, mask[l - 1]);  // dZ_{l-1}
         }
         // ---- layer 0: dW_0 += dZ_0^T . X_0 (nothing flows into the parameter-free encoding)
         if (FB_KEEP(0))
