@@ -450,13 +450,14 @@ extern "C" int rtxnerf_freqnet_forward(const rtxnerf_freqnet* net, const float* 
 // The nine weight-gradient accumulators are 9 x 128 fp32 TMEM columns — more than the 512 an SM has next
 // to the 128 of the working accumulator — so the kernel is launched THREE times, each launch recomputing
 // the forward and the dgrad chain and accumulating the gradients of three layers in TMEM over all of its
-// tiles (one flush of fp32 atomics per CTA at the end): 63 layer products per tile instead of 27.
+// tiles (one flush of fp32 atomics per CTA at the end).  A launch stops its dgrad chain at its lowest kept layer:
+// 27 forward + 15 dgrad + 9 wgrad = 51 layer products per tile instead of the minimal 27.
 // Operand tiles live in shared memory in the no-swizzle core-matrix layout, which the tensor cores read in
 // both majors (tcgen05.cuh): X_l [sample][feature] is the K-major A of the forward layer and the MN-major
 // B of dW_l; dZ_l is the K-major A of the dgrad and the MN-major A of dW_l; W_l [out][in] is the K-major B
 // of the forward and the MN-major B of the dgrad.  Weights stream from L2 into a two-slot ring by plain
-// loads issued under the running MMA.  First version: one tile per CTA, serial phases — correctness first;
-// the measured rate is in DESIGN.md.
+// cp.async copies issued under the running MMA.  One tile per CTA, serial phases; the measured rate is in
+// DESIGN.md.
 // =========================================================================================
 #define FB_THREADS (2 * NET_TILE)          // two threads per sample row: each owns 64 of the 128 columns
 #define FB_TILE_BYTES (NET_TILE * FN_W * 2)                 // 32 KB: [128][128] fp16

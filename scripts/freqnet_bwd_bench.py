@@ -34,7 +34,7 @@ def main():
         e1.synchronize()
         ts.append(e0.elapsed_time(e1))
     ms = float(np.median(ts))
-    tf = 63 * 2.0 * 128 ** 3 * (a.rows / 128) / (ms * 1e-3) / 1e12
+    tf = 51 * 2.0 * 128 ** 3 * (a.rows / 128) / (ms * 1e-3) / 1e12
     print("freqnet backward: %d rows, %.2f ms (%.1f ms at 33.5 M rows), %.0f TFLOP/s executed; |grad| sum %.6e, max %.4e"
           % (a.rows, ms, ms * 33.5e6 / a.rows, tf, float(grads.abs().sum()), float(grads.abs().max())))
 
