@@ -17,8 +17,9 @@
 //               same depth).  Tiles of the CTA's ray groups are dealt round-robin to the encoder
 //               groups; a group writes the 32 features of its 128 rows straight into TMEM as the
 //               layer-0 A operand (16 columns, two buffers per group) and never waits for the MLP.
-// The MLP group consumes tiles in order; hand-offs are mbarriers (enc_ready: 128 encoder threads
-// -> MMA thread, enc_free: MMA thread -> encoder group once layer 0 has read the operand).
+// The MLP group consumes tiles in order.  Producer -> consumer hand-offs are hardware named barriers (encoder
+// group -> MLP group per operand buffer, MLP group -> compositor per exchange buffer: rr_named_*), the "buffer is
+// free again" signals are mbarriers (enc_free: the MLP warps once layer 0 has read the operand, out_free).
 // TMEM per CTA (256 columns, two CTAs per SM): D 64 | A_hidden 32 | 6 x A_encoded 16.
 // Shared memory is only the weights (14 KB) and the 4 KB radiance exchange, so ~190 KB of the SM
 // stays L1 for the hash-table gathers.
@@ -44,7 +45,7 @@ struct RrSmem {
     static constexpr int W1 = W0 + NET_W * NET_IN * 2;
     static constexpr int W2 = W1 + NET_W * NET_W * 2;
     static constexpr int EXCH = W2 + NET_OUT * NET_W * 2;            // [2][4][32] float4
-    static constexpr int BAR = EXCH + 2 * 4 * 32 * 16;     // enc_ready[], enc_free[], mma, out_ready[2], out_free[2], tmem slot
+    static constexpr int BAR = EXCH + 2 * 4 * 32 * 16;     // enc_free[] (+ unused words), mma, out_free[2], tmem slot
     static constexpr int BYTES = BAR + 8 * (2 * RR_BUFS(RR_MAX_ENC_GROUPS) + 5) + 16;
 };
 
@@ -66,7 +67,6 @@ struct RrArgs {
     int groups_per_cta;   // consecutive 32-ray groups one CTA walks
     int wait_ticks;   // > 0: mbarrier waits carry this suspend-time hint (development knob)
     int mlp_last;     // 1: the MLP group is the LAST four warps of the CTA (development knob, see rr_launch)
-    int named_bars;   // 1: encoder -> MLP and MLP -> compositor hand-offs on named barriers, 0: on mbarriers (A/B knob)
 };
 
 __device__ __forceinline__ void rr_wait(uint64_t* bar, uint32_t parity, int ticks)
@@ -150,30 +150,23 @@ rays_roles_kernel(LeanLevels ll, Levels lv, const uint32_t* __restrict__ table32
                   RrArgs a)
 {
     extern __shared__ __align__(128) uint8_t smem[];
-    uint64_t* enc_ready = reinterpret_cast<uint64_t*>(smem + RrSmem::BAR);
-    uint64_t* enc_free = enc_ready + RR_BUFS(EG);
-    uint64_t* mma_bar = enc_free + RR_BUFS(EG);
-    uint64_t* out_ready = mma_bar + 1;     // MLP group -> compositor: a tile's radiance is parked in exch[buf]
-    uint64_t* out_free = out_ready + 2;    // compositor -> MLP group: exch[buf] has been read
+    uint64_t* enc_free = reinterpret_cast<uint64_t*>(smem + RrSmem::BAR);
+    uint64_t* mma_bar = enc_free + 2 * RR_BUFS(EG);
+    uint64_t* out_free = mma_bar + 3;      // compositor -> MLP group: exch[buf] has been read
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(out_free + 2);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, wk = warp & 3;
     // role index: 0-3 the MLP group, 4 .. 4 * EG + 3 the encoder groups, 4 * EG + 4 the compositor (render mode)
     const int rw = warp >= 4 * (EG + 1) ? warp : (a.mlp_last ? (warp >= 4 * EG ? warp - 4 * EG : warp + 4) : warp);
-    const bool mma_thread = rw == 0 && lane == 0;
 
     load_weight_tile(smem + RrSmem::W0, weights, NET_W, NET_IN, tid, RR_CTA_THREADS(EG, RENDER));
     load_weight_tile(smem + RrSmem::W1, weights + NET_W * NET_IN, NET_W, NET_W, tid, RR_CTA_THREADS(EG, RENDER));
     load_weight_tile(smem + RrSmem::W2, weights + NET_W * NET_IN + NET_W * NET_W, NET_OUT, NET_W, tid, RR_CTA_THREADS(EG, RENDER));
     if (tid == 0) {
         for (int i = 0; i < RR_BUFS(EG); i++) {
-            tc::mbar_init(enc_ready + i, NET_TILE);
-            tc::mbar_init(enc_free + i, 1);
+            tc::mbar_init(enc_free + i, NET_TILE / 32);   // one arrival per MLP warp (its rows of the operand are read)
         }
         tc::mbar_init(mma_bar, 1);
-        for (int i = 0; i < 2; i++) {
-            tc::mbar_init(out_ready + i, NET_TILE);
-            tc::mbar_init(out_free + i, 1);
-        }
+        for (int i = 0; i < 2; i++) tc::mbar_init(out_free + i, 1);
         tc::fence_mbar_init();
     }
     if (warp == 0) tc::tmem_alloc<RR_TMEM_COLS>(tmem_slot);
@@ -243,15 +236,11 @@ rays_roles_kernel(LeanLevels ll, Levels lv, const uint32_t* __restrict__ table32
                 }
                 const uint32_t t_e = tmem_base + lane_sel + (uint32_t)(RR_COL_AE + 16 * b);
                 // feature pair(s) of level(s) l.. -> columns l.. of this row of the operand (and the training copy)
-                auto emit1 = [&](int l, uint32_t f) {
-                    if (!RENDER && a.encoded_out && valid) reinterpret_cast<uint32_t*>(a.encoded_out + s * NET_IN)[l] = f;
-                    tc::tmem_st_x1(t_e + l, f);
-                };
-                auto emit2 = [&](int l, uint32_t f0, uint32_t f1) {
-                    if (!RENDER && a.encoded_out && valid)
-                        *reinterpret_cast<uint2*>(a.encoded_out + s * NET_IN + 2 * l) = make_uint2(f0, f1);
-                    tc::tmem_st_x2(t_e + l, f0, f1);
-                };
+                // (the training copy of the features, encoded_out, is written by the MLP group from this operand:
+                // eight 8-byte stores per sample at a 64-byte lane stride were 256 LSU wavefronts per 32 samples on
+                // the warps that already keep the LSU pipe 61 % busy with the gathers)
+                auto emit1 = [&](int l, uint32_t f) { tc::tmem_st_x1(t_e + l, f); };
+                auto emit2 = [&](int l, uint32_t f0, uint32_t f1) { tc::tmem_st_x2(t_e + l, f0, f1); };
                 int l = 0;
                 if (LEAN) {
                     const int nd = ll.n_dense, nl = ll.n_levels;
@@ -315,8 +304,7 @@ rays_roles_kernel(LeanLevels ll, Levels lv, const uint32_t* __restrict__ table32
                 for (; l < NET_IN / 2; l++) emit1(l, 0u);     // fewer than 16 levels: the rest of the row is zero
                 tc::tmem_st_wait();
                 tc::fence_before_thread_sync();
-                if (a.named_bars) rr_named_arrive(RR_BAR_ENC + b, 2 * NET_TILE);
-                else tc::mbar_arrive(enc_ready + b);
+                rr_named_arrive(RR_BAR_ENC + b, 2 * NET_TILE);
             }
             t_mod = (t_mod + nt) % EG;
         }
@@ -339,8 +327,7 @@ rays_roles_kernel(LeanLevels ll, Levels lv, const uint32_t* __restrict__ table32
             float tau = 0.0f, t_prev = 0.0f, ax = 0.0f, ay = 0.0f, az = 0.0f;      // vol_render.cu:32-33
             for (int t = 0; t < nt; t++, T++) {
                 const int buf = T & 1;
-                if (a.named_bars) rr_named_sync(RR_BAR_OUT(EG) + buf, NET_TILE + 32);
-                else rr_wait(out_ready + buf, (uint32_t)((T >> 1) & 1), a.wait_ticks);
+                rr_named_sync(RR_BAR_OUT(EG) + buf, NET_TILE + 32);
 #pragma unroll
                 for (int k = 0; k < 4; k++) {
                     const int q = 4 * t + k;
@@ -394,17 +381,30 @@ rays_roles_kernel(LeanLevels ll, Levels lv, const uint32_t* __restrict__ table32
                 const int b = 2 * e + (m & 1);
                 // every row of the previous tile's output has been read: D is free
                 tc::fence_before_thread_sync();
-                if (a.named_bars) rr_named_sync(RR_BAR_ENC + b, 2 * NET_TILE);   // D free AND the operand is there
-                else rr_mlp_barrier();
+                rr_named_sync(RR_BAR_ENC + b, 2 * NET_TILE);   // D free AND the operand is there
                 if (rw == 0 && tc::elect_one()) {     // the converged issuing warp (tcgen05.cuh: elect_one)
-                    if (!a.named_bars) rr_wait(enc_ready + b, (uint32_t)((m >> 1) & 1), a.wait_ticks);
                     tc::fence_after_thread_sync();
                     rr_issue_layer<NET_W, NET_IN>(tmem_base + RR_COL_D, tmem_base + RR_COL_AE + 16 * b, s_w0, mma_bar);
+                }
+                if (!RENDER && a.encoded_out) {
+                    // training copy of this row's 32 features, straight from the layer-0 operand in TMEM (read-only
+                    // beside the running MMA): 64 contiguous bytes per sample, four 16-byte stores
+                    tc::fence_after_thread_sync();
+                    uint32_t f[16];
+                    tc::tmem_ld_x16(tmem_base + lane_sel + (uint32_t)(RR_COL_AE + 16 * b), f);
+                    tc::tmem_ld_wait();
+                    const int q = 4 * t + wk;
+                    if (q < ns) {
+                        uint4* o = reinterpret_cast<uint4*>(a.encoded_out + (first * S + q) * NET_IN);
+#pragma unroll
+                        for (int c = 0; c < 4; c++) o[c] = make_uint4(f[4 * c], f[4 * c + 1], f[4 * c + 2], f[4 * c + 3]);
+                    }
                 }
                 rr_wait(mma_bar, phase, a.wait_ticks);
                 phase ^= 1;
                 tc::fence_after_thread_sync();
-                if (mma_thread) tc::mbar_arrive(enc_free + b);
+                __syncwarp();
+                if (lane == 0) tc::mbar_arrive(enc_free + b);
                 rr_hidden_epilogue(t_d, t_ah);
                 tc::fence_before_thread_sync();
                 rr_mlp_barrier();
@@ -431,8 +431,7 @@ rays_roles_kernel(LeanLevels ll, Levels lv, const uint32_t* __restrict__ table32
                     const int buf = T & 1;
                     if (T >= 2) rr_wait(out_free + buf, (uint32_t)(((T >> 1) - 1) & 1), a.wait_ticks);
                     exch[(buf * 4 + wk) * 32 + lane] = output_row_rgba(r, a.out_activation);
-                    if (a.named_bars) rr_named_arrive(RR_BAR_OUT(EG) + buf, NET_TILE + 32);
-                    else tc::mbar_arrive(out_ready + buf);
+                    rr_named_arrive(RR_BAR_OUT(EG) + buf, NET_TILE + 32);
                 } else {
                     const int q = 4 * t + wk;
                     if (q < ns) output_row_store(r, a.out_activation, first * S + q, a.out16, a.radiance4);

@@ -54,8 +54,6 @@ int rr_launch(bool render, const rtxnerf_hashgrid* enc, const rtxnerf_mlp* mlp, 
     RrArgs a = a_in;
     static const int mlp_last = rtx_env_int("RTXNERF_RR_MLP_LAST", 1);
     a.mlp_last = mlp_last;
-    static const int named_bars = rtx_env_int("RTXNERF_RR_NAMED_BARS", 1);
-    a.named_bars = named_bars;
     static const int gpc = rtx_env_int("RTXNERF_RR_GROUPS_PER_CTA", RR_GROUPS_PER_CTA);
     a.groups_per_cta = gpc > 0 ? gpc : RR_GROUPS_PER_CTA;
     static const int wait_ticks = rtx_env_int("RTXNERF_RR_WAIT_TICKS", 0);

@@ -216,3 +216,44 @@ def test_adam_vectorised_body_equals_scalar_kernel(cuda_api, n, offset):
         out.append([x.cpu().numpy().copy() for x in (dm, dp, d1, d2)])
     for a, b in zip(*out):
         assert np.array_equal(a.view(np.uint8), b.view(np.uint8))
+
+
+def test_positions_outside_the_cube_are_clamped_forward_and_backward(cuda_api, orc):
+    """the ABI takes caller-supplied positions; a coordinate below -1 used to wrap the dense
+    level index to 0xFFFFFFFF (gather, and in the backward an fp32 atomicAdd, far outside the table).  Positions are
+    clamped to the cube in every kernel and in the oracle: rows at +-1.5 and +-40 encode like the faces, and the
+    scatter stays inside the table (guard words around it untouched)."""
+    import torch
+    net, lv, table, w = _net(cuda_api, seed=9, out_activation=1)
+    n_rays, S = 64, 4
+    nh, idx, n, s = _rays(n_rays, S, seed=21)
+    bad = np.array([[-1.5, 0.2, 0.3], [1.5, -0.4, 0.1], [0.0, -1.5, 1.5], [-40.0, 40.0, -1.5], [1.0, 1.0, 1.0],
+                    [-1.0, -1.0, -1.0], [1.0000001, -1.0000001, 0.0], [-1.5, -1.5, -1.5]], np.float32)
+    s[:len(bad), :3] = bad
+    s[n - len(bad):, :3] = bad[::-1]
+    ds, dnh, didx = _t(s), _t(nh), _t(idx)
+    enc = torch.zeros((n, 32), dtype=torch.float16, device="cuda")
+    rad = torch.zeros((n, 4), dtype=torch.float32, device="cuda")
+    net.forward_rays(None, ds, dnh, didx, n_rays, S, radiance=rad, encoded_out=enc)
+    flat = net.encode(ds)
+    torch.cuda.synchronize()
+    eo = orc.hashgrid_encode(lv, table, s)
+    assert np.array_equal(enc.cpu().numpy().view(np.uint16), eo.view(np.uint16))
+    assert np.array_equal(flat.cpu().numpy().view(np.uint16), eo.view(np.uint16))
+    clamped = s.copy()
+    clamped[:, :3] = np.clip(clamped[:, :3], -1.0, 1.0)
+    assert np.array_equal(orc.hashgrid_encode(lv, table, clamped).view(np.uint16), eo.view(np.uint16))
+    # backward: the table gradient lives in the middle of a guarded buffer
+    guard = 4096
+    buf = torch.zeros((lv["n_entries"] + 2 * guard, 2), dtype=torch.float32, device="cuda")
+    gt = buf[guard:guard + lv["n_entries"]]
+    gw = torch.zeros(w.size, dtype=torch.float32, device="cuda")
+    g = (np.random.default_rng(3).uniform(-1, 1, (n, 4)) * 0.05).astype(np.float16)
+    dencoded = torch.zeros((n, 32), dtype=torch.float16, device="cuda")
+    cnt = torch.tensor([int(nh.sum())], dtype=torch.int64, device="cuda")
+    net.backward_rays(None, ds, enc, _t(g), dnh, didx, n_rays, S, cnt, n, dencoded, gt, gw)
+    torch.cuda.synchronize()
+    assert float(buf[:guard].abs().sum()) == 0.0 and float(buf[guard + lv["n_entries"]:].abs().sum()) == 0.0
+    gt_o = orc.hashgrid_backward(lv, s, dencoded.cpu().numpy())
+    np.testing.assert_allclose(gt.cpu().numpy(), gt_o, rtol=0, atol=1e-4 * np.abs(gt_o).max())
+    assert np.isfinite(rad.cpu().numpy()).all()
