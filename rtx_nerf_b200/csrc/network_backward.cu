@@ -32,6 +32,15 @@
 #define NB_G1 64      // dW1   [64 out x 64 in]
 #define NB_G0 128     // dW0   [64 out x 32 in]
 #define NB_G2 160     // dW2^T [64 in  x 16 out]
+// A operands of the forward / dgrad products (TS form, tcgen05.cuh mma_f16_ts): the tile that is the A of the next
+// product is ALSO written to TMEM by the epilogue that produces it.  An MMA with both operands in shared memory
+// costs (A + B bytes) / 128 cycles of the SM's shared-memory port (scripts/probes/mma_issue_probe.cu) and this
+// kernel's epilogues need the same port; with A in TMEM the six products read only their weight tile there:
+// 1 488 -> 880 cycles of operand reads per 128-sample tile.  The shared-memory copies stay: they are the
+// MN-major operands of the weight-gradient products.
+#define NB_AH 176     // [128 x 64] fp16: H1, H2, dH2, dH1 in turn (32 columns)
+#define NB_A0 208     // [128 x 32] fp16 encoded features (16 columns)
+#define NB_ADO 224    // [128 x 16] fp16 dOut (8 columns)
 
 struct NbSmem {
     static constexpr int W0 = 0;                             // [64][32]
@@ -79,8 +88,52 @@ __device__ __forceinline__ void mma_wgrad(uint32_t g, uint32_t x, uint32_t y, bo
                        (accumulate || ks > 0) ? 1u : 0u);
 }
 
+// TS forms: A [128 x K] from TMEM (K / 2 columns), B from shared memory
+template <int N, int K>
+__device__ __forceinline__ void mma_fwd_ts(uint32_t d, uint32_t a_tmem, uint32_t w)
+{
+    constexpr uint32_t id = tc::idesc_f16_f32_major(NET_TILE, N, 0, 0);
+    const uint64_t dw = tc::smem_desc(w, 128, K * 16);
+#pragma unroll
+    for (int ks = 0; ks < K / 16; ks++)
+        tc::mma_f16_ts(d, a_tmem + ks * 8, tc::smem_desc_advance(dw, ks * 256), id, ks > 0 ? 1u : 0u);
+}
+template <int N_IN, int K_OUT>
+__device__ __forceinline__ void mma_dgrad_ts(uint32_t d, uint32_t a_tmem, uint32_t w)
+{
+    constexpr uint32_t id = tc::idesc_f16_f32_major(NET_TILE, N_IN, 0, 1);
+    const uint64_t dw = tc::smem_desc(w, N_IN * 16, 128);
+#pragma unroll
+    for (int ks = 0; ks < K_OUT / 16; ks++)
+        tc::mma_f16_ts(d, a_tmem + ks * 8, tc::smem_desc_advance(dw, ks * 2 * (N_IN * 16)), id, ks > 0 ? 1u : 0u);
+}
+
+// forward epilogue of this kernel: relu_row_to_smem (mlp_tile.cuh) plus the TMEM copy of the row (the next A)
+__device__ __forceinline__ void relu_row_to_smem_tmem(uint32_t taddr, uint8_t* a_next, int row, uint32_t t_a)
+{
+#pragma unroll
+    for (int h = 0; h < NET_W / 32; h++) {
+        uint32_t r0[16], r1[16];
+        tc::tmem_ld_x16(taddr + h * 32, r0);
+        tc::tmem_ld_x16(taddr + h * 32 + 16, r1);
+        tc::tmem_ld_wait();
+        uint32_t pk[16];
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            pk[j] = relu_pack_f16x2(__uint_as_float(r0[2 * j]), __uint_as_float(r0[2 * j + 1]));
+            pk[8 + j] = relu_pack_f16x2(__uint_as_float(r1[2 * j]), __uint_as_float(r1[2 * j + 1]));
+        }
+        tc::tmem_st_x16(t_a + h * 16, pk);
+#pragma unroll
+        for (int c = 0; c < 4; c++)
+            *reinterpret_cast<uint4*>(a_next + tile_chunk_off(row, 4 * h + c, NET_W)) =
+                make_uint4(pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
+    }
+}
+
 // dgrad epilogue: TMEM row -> masked by ReLU'(h) (h = this row of the forward tile) -> fp16 tile
-__device__ __forceinline__ void masked_row_to_smem(uint32_t taddr, const uint8_t* h_tile, uint8_t* dst, int row)
+__device__ __forceinline__ void masked_row_to_smem(uint32_t taddr, const uint8_t* h_tile, uint8_t* dst, int row,
+                                                   uint32_t t_a)
 {
 #pragma unroll
     for (int q = 0; q < NET_W / 16; q++) {
@@ -99,6 +152,7 @@ __device__ __forceinline__ void masked_row_to_smem(uint32_t taddr, const uint8_t
             const __half2 v = __floats2half2_rn(a, b);
             pk[j] = *reinterpret_cast<const uint32_t*>(&v);
         }
+        tc::tmem_st_x8(t_a + q * 8, pk);
         *reinterpret_cast<uint4*>(dst + tile_chunk_off(row, 2 * q, NET_W)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
         *reinterpret_cast<uint4*>(dst + tile_chunk_off(row, 2 * q + 1, NET_W)) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
     }
@@ -136,7 +190,8 @@ mlp_backward_kernel(const uint16_t* __restrict__ weights, const uint16_t* __rest
     uint32_t phase = 0;
     bool have_grads = false;   // the TMEM weight-gradient accumulators hold at least one tile
 
-    auto sync_then = [&](auto issue) {   // publish this phase's smem tile, run the MMAs, wait for them
+    auto sync_then = [&](auto issue) {   // publish this phase's smem tile + TMEM operand, run the MMAs, wait for them
+        tc::tmem_st_wait();
         tc::fence_proxy_async_smem();
         tc::fence_before_thread_sync();
         __syncthreads();
@@ -170,15 +225,18 @@ mlp_backward_kernel(const uint16_t* __restrict__ weights, const uint16_t* __rest
 #pragma unroll
             for (int c = 0; c < NET_IN / 8; c++)
                 *reinterpret_cast<uint4*>(smem + NbSmem::A0 + tile_chunk_off(tid, c, NET_IN)) = pre[c];
+            const uint32_t a0w[16] = {pre[0].x, pre[0].y, pre[0].z, pre[0].w, pre[1].x, pre[1].y, pre[1].z, pre[1].w,
+                                      pre[2].x, pre[2].y, pre[2].z, pre[2].w, pre[3].x, pre[3].y, pre[3].z, pre[3].w};
+            tc::tmem_st_x16(t_row + NB_A0, a0w);
         }
         const uint2 gb = pre_g;
         fetch_row(tile + gridDim.x);
         // ---- forward recompute
-        sync_then([&] { mma_fwd<NET_W, NET_IN>(tm + NB_D, s_a0, s_w0); });
-        relu_row_to_smem(t_row + NB_D, smem + NbSmem::H1, tid);
-        sync_then([&] { mma_fwd<NET_W, NET_W>(tm + NB_D, s_h1, s_w1); });
-        relu_row_to_smem(t_row + NB_D, smem + NbSmem::H2, tid);
-        sync_then([&] { mma_fwd<NET_OUT, NET_W>(tm + NB_D, s_h2, s_w2); });
+        sync_then([&] { mma_fwd_ts<NET_W, NET_IN>(tm + NB_D, tm + NB_A0, s_w0); });
+        relu_row_to_smem_tmem(t_row + NB_D, smem + NbSmem::H1, tid, t_row + NB_AH);
+        sync_then([&] { mma_fwd_ts<NET_W, NET_W>(tm + NB_D, tm + NB_AH, s_w1); });
+        relu_row_to_smem_tmem(t_row + NB_D, smem + NbSmem::H2, tid, t_row + NB_AH);
+        sync_then([&] { mma_fwd_ts<NET_OUT, NET_W>(tm + NB_D, tm + NB_AH, s_w2); });
         {   // dOut = g * act'(out) on (r,g,b,sigma); the 12 padding outputs carry no gradient
             uint32_t r[16];
             output_row_load(t_row + NB_D, r);
@@ -200,23 +258,26 @@ mlp_backward_kernel(const uint16_t* __restrict__ weights, const uint16_t* __rest
             *reinterpret_cast<uint4*>(smem + NbSmem::DO + tile_chunk_off(tid, 0, NET_OUT)) =
                 make_uint4(*reinterpret_cast<const uint32_t*>(&d01), *reinterpret_cast<const uint32_t*>(&d23), 0u, 0u);
             *reinterpret_cast<uint4*>(smem + NbSmem::DO + tile_chunk_off(tid, 1, NET_OUT)) = make_uint4(0u, 0u, 0u, 0u);
+            const uint32_t dow[8] = {*reinterpret_cast<const uint32_t*>(&d01), *reinterpret_cast<const uint32_t*>(&d23),
+                                     0u, 0u, 0u, 0u, 0u, 0u};
+            tc::tmem_st_x8(t_row + NB_ADO, dow);
         }
         // ---- layer 2: dW2^T += H2^T . dOut ;  dH2 = (dOut . W2) * ReLU'(H2)
         sync_then([&] {
             mma_wgrad<NET_OUT>(tm + NB_G2, s_h2, s_do, have_grads);
-            mma_dgrad<NET_W, NET_OUT>(tm + NB_D, s_do, s_w2);
+            mma_dgrad_ts<NET_W, NET_OUT>(tm + NB_D, tm + NB_ADO, s_w2);
         });
-        masked_row_to_smem(t_row + NB_D, smem + NbSmem::H2, smem + NbSmem::DH, tid);
+        masked_row_to_smem(t_row + NB_D, smem + NbSmem::H2, smem + NbSmem::DH, tid, t_row + NB_AH);
         // ---- layer 1: dW1 += dH2^T . H1 ;  dH1 = (dH2 . W1) * ReLU'(H1)   (dH1 overwrites H2)
         sync_then([&] {
             mma_wgrad<NET_W>(tm + NB_G1, s_dh, s_h1, have_grads);
-            mma_dgrad<NET_W, NET_W>(tm + NB_D, s_dh, s_w1);
+            mma_dgrad_ts<NET_W, NET_W>(tm + NB_D, tm + NB_AH, s_w1);
         });
-        masked_row_to_smem(t_row + NB_D, smem + NbSmem::H1, smem + NbSmem::H2, tid);
+        masked_row_to_smem(t_row + NB_D, smem + NbSmem::H1, smem + NbSmem::H2, tid, t_row + NB_AH);
         // ---- layer 0: dW0 += dH1^T . A0 ;  dEnc = dH1 . W0
         sync_then([&] {
             mma_wgrad<NET_IN>(tm + NB_G0, s_h2, s_a0, have_grads);
-            mma_dgrad<NET_IN, NET_W>(tm + NB_D, s_h2, s_w0);
+            mma_dgrad_ts<NET_IN, NET_W>(tm + NB_D, tm + NB_AH, s_w0);
         });
         have_grads = true;
 #pragma unroll
