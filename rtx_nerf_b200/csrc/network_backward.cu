@@ -339,6 +339,254 @@ mlp_backward_kernel(const uint16_t* __restrict__ weights, const uint16_t* __rest
 }
 
 // ---------------------------------------------------------------------------------------
+// (1b) mlp_backward with TWO tiles per CTA (two CTAs per SM: four tiles and four issuing threads per SM).  The
+// kernel above is bound by the latency of its serial phase chain (barrier -> issue -> MMA -> commit -> wait ->
+// epilogue, ~1 000 cycles x 6 per tile) with the MMA pipe ~40 % busy; what limits the tiles in flight is TMEM: the
+// weight-gradient accumulators take 112 of a CTA's 256 columns.  Here two warp-groups of a CTA walk their own
+// tiles through the same six phases, each with its own accumulator D, its own issuing thread and its own named
+// barrier, and SHARE the three weight-gradient accumulators: MMAs issued by different threads into one TMEM
+// accumulator are serialised by the tensor pipe without losing updates (scripts/probes/mma_shared_acc_probe.cu:
+// 1 / 2 / 4 issuers, 16 384 accumulating MMAs, exact sums).  The accumulators are zeroed once with tcgen05.st, so
+// every weight-gradient MMA accumulates.  Shared memory per tile drops to 44 KB (dH2 overwrites H2 and dH1
+// overwrites H1 in place: a thread rewrites the chunks of its own row after the MMAs that read them have completed),
+// 102 KB per CTA.  Both operands of every product come from shared memory (the TS form of the kernel above would
+// need 2 x 56 more TMEM columns).
+// ---------------------------------------------------------------------------------------
+#define N2_GROUPS 2
+#define N2_THREADS (N2_GROUPS * NET_TILE)
+#define N2_TMEM_COLS 256
+#define N2_D(g) (64 * (g))
+#define N2_G1 128
+#define N2_G0 192
+#define N2_G2 224
+struct N2Smem {
+    static constexpr int W0 = 0;
+    static constexpr int W1 = W0 + NET_W * NET_IN * 2;
+    static constexpr int W2 = W1 + NET_W * NET_W * 2;
+    static constexpr int SLOT = W2 + NET_OUT * NET_W * 2;
+    static constexpr int A0 = 0;                               // inside a slot: [128][32] encoded features
+    static constexpr int H1 = A0 + NET_TILE * NET_IN * 2;      // [128][64], later dH1
+    static constexpr int H2 = H1 + NET_TILE * NET_W * 2;       // [128][64], later dH2
+    static constexpr int DO = H2 + NET_TILE * NET_W * 2;       // [128][16] dOut
+    static constexpr int SLOT_BYTES = DO + NET_TILE * NET_OUT * 2;
+    static constexpr int BAR = SLOT + N2_GROUPS * SLOT_BYTES;
+    static constexpr int BYTES = BAR + N2_GROUPS * 8 + 16;
+};
+
+// dgrad epilogue in place: TMEM row -> masked by ReLU'(h), h = this row of `tile` -> fp16 over the same chunks
+__device__ __forceinline__ void masked_row_in_place(uint32_t taddr, uint8_t* tile, int row)
+{
+#pragma unroll
+    for (int q = 0; q < NET_W / 16; q++) {
+        uint32_t r[16];
+        tc::tmem_ld_x16(taddr + q * 16, r);
+        uint4* c0 = reinterpret_cast<uint4*>(tile + tile_chunk_off(row, 2 * q, NET_W));
+        uint4* c1 = reinterpret_cast<uint4*>(tile + tile_chunk_off(row, 2 * q + 1, NET_W));
+        const uint4 h0 = *c0, h1 = *c1;
+        tc::tmem_ld_wait();
+        const uint32_t hw[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
+        uint32_t pk[8];
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            const float a = (hw[j] & 0xffffu) ? __uint_as_float(r[2 * j]) : 0.0f;
+            const float b = (hw[j] >> 16) ? __uint_as_float(r[2 * j + 1]) : 0.0f;
+            const __half2 v = __floats2half2_rn(a, b);
+            pk[j] = *reinterpret_cast<const uint32_t*>(&v);
+        }
+        *c0 = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+        *c1 = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+    }
+}
+
+__global__ void __launch_bounds__(N2_THREADS, 2)
+mlp_backward2_kernel(const uint16_t* __restrict__ weights, const uint16_t* __restrict__ encoded,
+                     const uint16_t* __restrict__ dl_dradiance, int out_activation,
+                     const long long* __restrict__ d_count, long long count_scale, long long n_max,
+                     uint16_t* __restrict__ d_encoded, float* __restrict__ grad_weights)
+{
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + N2Smem::BAR);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + N2_GROUPS);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int grp = warp >> 2, row = tid & (NET_TILE - 1);
+
+    load_weight_tile(smem + N2Smem::W0, weights, NET_W, NET_IN, tid, N2_THREADS);
+    load_weight_tile(smem + N2Smem::W1, weights + NET_W * NET_IN, NET_W, NET_W, tid, N2_THREADS);
+    load_weight_tile(smem + N2Smem::W2, weights + NET_W * NET_IN + NET_W * NET_W, NET_OUT, NET_W, tid, N2_THREADS);
+    if (tid == 0) {
+        for (int g = 0; g < N2_GROUPS; g++) tc::mbar_init(bars + g, 1);
+        tc::fence_mbar_init();
+    }
+    if (warp == 0) tc::tmem_alloc<N2_TMEM_COLS>(tmem_slot);
+    tc::fence_proxy_async_smem();
+    tc::fence_before_thread_sync();
+    __syncthreads();
+    tc::fence_after_thread_sync();
+    const uint32_t tm = *tmem_slot;
+    const uint32_t t_q = tm + ((uint32_t)((warp & 3) * 32) << 16);      // this warp's TMEM lane quarter
+    if (grp == 0) {      // the shared weight-gradient accumulators start at zero: every wgrad MMA accumulates
+        uint32_t z[16];
+#pragma unroll
+        for (int i = 0; i < 16; i++) z[i] = 0u;
+#pragma unroll
+        for (int c = N2_G1; c < N2_G2 + NET_OUT; c += 16) tc::tmem_st_x16(t_q + c, z);
+        tc::tmem_st_wait();
+    }
+    tc::fence_before_thread_sync();
+    __syncthreads();
+    tc::fence_after_thread_sync();
+
+    uint8_t* sl = smem + N2Smem::SLOT + grp * N2Smem::SLOT_BYTES;
+    const uint32_t t_d = t_q + N2_D(grp);
+    const uint32_t d_col = tm + N2_D(grp);
+    const uint32_t s_w0 = tc::smem_u32(smem + N2Smem::W0), s_w1 = tc::smem_u32(smem + N2Smem::W1),
+                   s_w2 = tc::smem_u32(smem + N2Smem::W2), s_a0 = tc::smem_u32(sl + N2Smem::A0),
+                   s_h1 = tc::smem_u32(sl + N2Smem::H1), s_h2 = tc::smem_u32(sl + N2Smem::H2),
+                   s_do = tc::smem_u32(sl + N2Smem::DO);
+    uint64_t* bar = bars + grp;
+    uint32_t phase = 0;
+    const bool issuer_warp = (warp & 3) == 0;
+
+    auto sync_then = [&](auto issue) {   // publish the group's tiles, run its MMAs, wait for them
+        tc::fence_proxy_async_smem();
+        tc::fence_before_thread_sync();
+        asm volatile("bar.sync %0, %1;" ::"r"(1 + grp), "n"(NET_TILE) : "memory");
+        if (issuer_warp && tc::elect_one()) {
+            tc::fence_after_thread_sync();
+            issue();
+            tc::mma_commit(bar);
+        }
+        tc::mbar_wait(bar, phase);
+        phase ^= 1;
+        tc::fence_after_thread_sync();
+    };
+
+    const long long n = row_count(d_count, count_scale, n_max);
+    const long long n_tiles = (n + NET_TILE - 1) / NET_TILE;
+    const long long stride = (long long)gridDim.x * N2_GROUPS;
+    const long long first = (long long)blockIdx.x * N2_GROUPS + grp;
+    uint4 pre[NET_IN / 8];
+    uint2 pre_g;
+    auto fetch_row = [&](long long t) {
+        const long long sn = t * NET_TILE + row;
+        const bool ok = sn < n;
+        const uint4* src = reinterpret_cast<const uint4*>(encoded + sn * NET_IN);
+#pragma unroll
+        for (int c = 0; c < NET_IN / 8; c++) pre[c] = ok ? __ldg(src + c) : make_uint4(0, 0, 0, 0);
+        pre_g = ok ? __ldg(reinterpret_cast<const uint2*>(dl_dradiance + sn * 4)) : make_uint2(0, 0);
+    };
+    fetch_row(first);
+    for (long long tile = first; tile < n_tiles; tile += stride) {
+        const long long s = tile * NET_TILE + row;
+        const bool valid = s < n;
+#pragma unroll
+        for (int c = 0; c < NET_IN / 8; c++)
+            *reinterpret_cast<uint4*>(sl + N2Smem::A0 + tile_chunk_off(row, c, NET_IN)) = pre[c];
+        const uint2 gb = pre_g;
+        fetch_row(tile + stride);
+        // ---- forward recompute
+        sync_then([&] { mma_fwd<NET_W, NET_IN>(d_col, s_a0, s_w0); });
+        relu_row_to_smem(t_d, sl + N2Smem::H1, row);
+        sync_then([&] { mma_fwd<NET_W, NET_W>(d_col, s_h1, s_w1); });
+        relu_row_to_smem(t_d, sl + N2Smem::H2, row);
+        sync_then([&] { mma_fwd<NET_OUT, NET_W>(d_col, s_h2, s_w2); });
+        {   // dOut = g * act'(out) on (r,g,b,sigma); the 12 padding outputs carry no gradient
+            uint32_t r[16];
+            output_row_load(t_d, r);
+            float d[4] = {0.f, 0.f, 0.f, 0.f};
+            if (valid) {
+                const float2 g01 = h2_bits_to_f2(gb.x), g23 = h2_bits_to_f2(gb.y);
+                const float g[4] = {g01.x, g01.y, g23.x, g23.y};
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    float da = 1.0f;
+                    if (out_activation == 1) {
+                        const float sg = __fdividef(1.0f, 1.0f + __expf(-__uint_as_float(r[j])));
+                        da = sg * (1.0f - sg);
+                    }
+                    d[j] = g[j] * da;
+                }
+            }
+            const __half2 d01 = __floats2half2_rn(d[0], d[1]), d23 = __floats2half2_rn(d[2], d[3]);
+            *reinterpret_cast<uint4*>(sl + N2Smem::DO + tile_chunk_off(row, 0, NET_OUT)) =
+                make_uint4(*reinterpret_cast<const uint32_t*>(&d01), *reinterpret_cast<const uint32_t*>(&d23), 0u, 0u);
+            *reinterpret_cast<uint4*>(sl + N2Smem::DO + tile_chunk_off(row, 1, NET_OUT)) = make_uint4(0u, 0u, 0u, 0u);
+        }
+        // ---- layer 2: dW2^T += H2^T . dOut ;  dH2 = (dOut . W2) * ReLU'(H2), over H2
+        sync_then([&] {
+            mma_wgrad<NET_OUT>(tm + N2_G2, s_h2, s_do, true);
+            mma_dgrad<NET_W, NET_OUT>(d_col, s_do, s_w2);
+        });
+        masked_row_in_place(t_d, sl + N2Smem::H2, row);
+        // ---- layer 1: dW1 += dH2^T . H1 ;  dH1 = (dH2 . W1) * ReLU'(H1), over H1
+        sync_then([&] {
+            mma_wgrad<NET_W>(tm + N2_G1, s_h2, s_h1, true);
+            mma_dgrad<NET_W, NET_W>(d_col, s_h2, s_w1);
+        });
+        masked_row_in_place(t_d, sl + N2Smem::H1, row);
+        // ---- layer 0: dW0 += dH1^T . A0 ;  dEnc = dH1 . W0
+        sync_then([&] {
+            mma_wgrad<NET_IN>(tm + N2_G0, s_h1, s_a0, true);
+            mma_dgrad<NET_IN, NET_W>(d_col, s_h1, s_w0);
+        });
+#pragma unroll
+        for (int q = 0; q < NET_IN / 16; q++) {
+            uint32_t r[16];
+            tc::tmem_ld_x16(t_d + q * 16, r);
+            tc::tmem_ld_wait();
+            if (valid) {
+                uint32_t pk[8];
+#pragma unroll
+                for (int j = 0; j < 8; j++) {
+                    const __half2 v = __floats2half2_rn(__uint_as_float(r[2 * j]), __uint_as_float(r[2 * j + 1]));
+                    pk[j] = *reinterpret_cast<const uint32_t*>(&v);
+                }
+                uint4* o = reinterpret_cast<uint4*>(d_encoded + s * NET_IN + q * 16);
+                o[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                o[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+            }
+        }
+    }
+    // ---- weight gradients leave TMEM once (M = 64 accumulator: row r in TMEM lane (r / 16) * 32 + r % 16)
+    tc::fence_before_thread_sync();
+    __syncthreads();
+    tc::fence_after_thread_sync();
+    if (grp == 0 && (long long)blockIdx.x * N2_GROUPS < n_tiles) {
+        const int grow = warp * 16 + lane;   // meaningful for lane < 16
+        float* g0 = grad_weights;
+        float* g1 = g0 + NET_W * NET_IN;
+        float* g2 = g1 + NET_W * NET_W;
+#pragma unroll
+        for (int q = 0; q < NET_W / 16; q++) {
+            uint32_t r[16];
+            tc::tmem_ld_x16(t_q + N2_G1 + q * 16, r);
+            tc::tmem_ld_wait();
+            if (lane < 16)
+                for (int j = 0; j < 16; j++) atomicAdd(g1 + grow * NET_W + q * 16 + j, __uint_as_float(r[j]));
+        }
+#pragma unroll
+        for (int q = 0; q < NET_IN / 16; q++) {
+            uint32_t r[16];
+            tc::tmem_ld_x16(t_q + N2_G0 + q * 16, r);
+            tc::tmem_ld_wait();
+            if (lane < 16)
+                for (int j = 0; j < 16; j++) atomicAdd(g0 + grow * NET_IN + q * 16 + j, __uint_as_float(r[j]));
+        }
+        {
+            uint32_t r[16];
+            tc::tmem_ld_x16(t_q + N2_G2, r);
+            tc::tmem_ld_wait();
+            if (lane < 16)
+                for (int j = 0; j < 16; j++) atomicAdd(g2 + j * NET_W + grow, __uint_as_float(r[j]));   // [out j][in row]
+        }
+    }
+    tc::fence_before_thread_sync();
+    __syncthreads();
+    tc::fence_after_thread_sync();
+    if (warp == 0) tc::tmem_dealloc<N2_TMEM_COLS>(tm);
+}
+
+// ---------------------------------------------------------------------------------------
 // (2) dEnc -> table gradient.  grad_table is fp32 [n_entries][2]; a corner update is one 8-byte
 // vector reduction, an x-pair of corners that shares an aligned entry pair one 16-byte one.
 // lane = ray, warp = sample slot (as in network_rays.cu): the 32 lanes of a warp are
@@ -619,9 +867,21 @@ extern "C" int rtxnerf_mlp_backward(const rtxnerf_mlp* mlp, const uint16_t* d_en
     if (mlp->in_dim != NET_IN || mlp->width != NET_W || mlp->n_hidden != 2) return RTXNERF_ECONFIG;
     if (mlp->out_activation != 0 && mlp->out_activation != 1) return RTXNERF_ECONFIG;
     if (n_max == 0) return RTXNERF_OK;
+    const long long tiles = (n_max + NET_TILE - 1) / NET_TILE;
+    // RTXNERF_MLPB_VERSION=1 keeps the one-tile-per-CTA kernel (development A/B)
+    static const int version = rtx_env_int("RTXNERF_MLPB_VERSION", 2);
+    if (version == 2) {
+        static RtxPerDeviceOnce attr2;
+        RTX_CUDA_TRY((cudaError_t)rtx_set_max_smem(attr2, mlp_backward2_kernel, N2Smem::BYTES));
+        const long long ctas = (tiles + N2_GROUPS - 1) / N2_GROUPS;
+        const long long res2 = (long long)RTX_NUM_SMS * 2;          // 2 CTAs per SM: 2 x 256 TMEM columns, 2 x 102 KB
+        mlp_backward2_kernel<<<(unsigned)(ctas < res2 ? ctas : res2), N2_THREADS, N2Smem::BYTES, (cudaStream_t)stream>>>(
+            mlp->weights, d_encoded, d_dl_dradiance, mlp->out_activation, d_count, count_scale, n_max, d_dencoded,
+            d_grad_weights);
+        return rtx_launch_status();
+    }
     static RtxPerDeviceOnce attr_set;
     RTX_CUDA_TRY((cudaError_t)rtx_set_max_smem(attr_set, mlp_backward_kernel, NbSmem::BYTES));
-    const long long tiles = (n_max + NET_TILE - 1) / NET_TILE;
     const long long resident = (long long)RTX_NUM_SMS * 2;   // 2 CTAs per SM: 2 x 256 TMEM columns, 2 x 75 KB
     mlp_backward_kernel<<<(unsigned)(tiles < resident ? tiles : resident), NET_TILE, NbSmem::BYTES, (cudaStream_t)stream>>>(
         mlp->weights, d_encoded, d_dl_dradiance, mlp->out_activation, d_count, count_scale, n_max, d_dencoded,
