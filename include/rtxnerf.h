@@ -158,6 +158,17 @@ int rtxnerf_ray_march_csr(const rtxnerf_grid* grid, const rtxnerf_camera* cam,
                           long long ray_begin, long long n_rays, int max_hits,
                           const rtxnerf_hits* hits, void* workspace, size_t workspace_bytes,
                           void* stream);
+/* The same march that ALSO writes every hit's entry and exit point as one 32-byte record,
+ * d_segments8[slot] = (sx, sy, sz, ex, ey, ez, 0, 0), [capacity][8] floats, 32-byte aligned.  The lanes of a warp
+ * read the hits of 32 different rays, whose lists are ~200 bytes apart: from the two [capacity][3] arrays that is
+ * six 4-byte loads of 32 different sectors each per sample, from the record two 16-byte loads of one sector per
+ * lane.  Consumer: rtxnerf_render_rays_fused_seg.  hits->start_points and hits->end_points may both be NULL here
+ * (the records alone are written).  (Repo-native layout; the reference keeps the two arrays,
+ * optixPrograms.cu:194-211.) */
+int rtxnerf_ray_march_csr_seg(const rtxnerf_grid* grid, const rtxnerf_camera* cam,
+                              long long ray_begin, long long n_rays, int max_hits,
+                              const rtxnerf_hits* hits, float* d_segments8, void* workspace,
+                              size_t workspace_bytes, void* stream);
 
 /* The same march with NO device allocation and no caller-provided workspace.  No counterpart in the
  * reference: added for callers that cannot call cudaMalloc (code under
@@ -348,6 +359,11 @@ int rtxnerf_render_rays_fused(const rtxnerf_hashgrid* enc, const rtxnerf_mlp* ml
                               const float* d_start_points, const float* d_end_points,
                               const int* d_num_hits, const int* d_indices, int n_rays,
                               int samples_per_segment, int sample_type, float* d_pixels, void* stream);
+/* rtxnerf_render_rays_fused over the packed hit records of rtxnerf_ray_march_csr_seg: same samples, same pixels. */
+int rtxnerf_render_rays_fused_seg(const rtxnerf_hashgrid* enc, const rtxnerf_mlp* mlp,
+                                  const float* d_segments8, const int* d_num_hits, const int* d_indices,
+                                  int n_rays, int samples_per_segment, int sample_type, float* d_pixels,
+                                  void* stream);
 
 /* ------------------------------------------------------------------------------------
  * Training step — replaces network->backward (main.cu:781), loss->evaluate + reduce_sum

@@ -84,6 +84,8 @@ SIGNATURES = {
     "rtxnerf_ray_march_workspace_bytes_for": (c_size_t, [c_ll, c_int]),
     "rtxnerf_ray_march_csr": (c_int, [c_void_p, C.POINTER(Camera), c_ll, c_ll, c_int, C.POINTER(Hits),
                                       c_void_p, c_size_t, c_void_p]),
+    "rtxnerf_ray_march_csr_seg": (c_int, [c_void_p, C.POINTER(Camera), c_ll, c_ll, c_int, C.POINTER(Hits), c_void_p,
+                                          c_void_p, c_size_t, c_void_p]),
     "rtxnerf_ray_march_csr_static_max_rays": (c_ll, []),
     "rtxnerf_ray_march_csr_static": (c_int, [c_void_p, C.POINTER(Camera), c_ll, c_ll, c_int, C.POINTER(Hits),
                                              c_void_p]),
@@ -106,6 +108,8 @@ SIGNATURES = {
                                              c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
     "rtxnerf_render_rays_fused": (c_int, [C.POINTER(HashGrid), C.POINTER(Mlp), c_void_p, c_void_p, c_void_p, c_void_p,
                                           c_int, c_int, c_int, c_void_p, c_void_p]),
+    "rtxnerf_render_rays_fused_seg": (c_int, [C.POINTER(HashGrid), C.POINTER(Mlp), c_void_p, c_void_p, c_void_p,
+                                              c_int, c_int, c_int, c_void_p, c_void_p]),
     "rtxnerf_freqnet_param_count": (c_size_t, []),
     "rtxnerf_freqnet_packed_count": (c_size_t, []),
     "rtxnerf_freqnet_pack": (c_int, [c_void_p, c_void_p, c_void_p]),

@@ -248,7 +248,8 @@ def optixLaunch(pipeline, stream, params, params_size=None, sbt=None, width=None
 class HitBuffers:
     """Caller-owned CSR hit records for up to n_rays rays and `capacity` hits."""
 
-    def __init__(self, n_rays, capacity, device="cuda", want_t=True, want_cells=True, want_origins=True):
+    def __init__(self, n_rays, capacity, device="cuda", want_t=True, want_cells=True, want_origins=True,
+                 want_segments=False):
         dev = torch.device(device)
         self.n_rays, self.capacity = n_rays, capacity
         self.num_hits = torch.empty(n_rays, dtype=torch.int32, device=dev)
@@ -261,32 +262,43 @@ class HitBuffers:
         self.end_points = torch.empty((capacity, 3), dtype=torch.float32, device=dev)
         self.hit_cells = torch.empty(capacity, dtype=torch.int32, device=dev) if want_cells else None
         self.total_hits = torch.zeros(1, dtype=torch.int64, device=dev)
+        # packed (sx, sy, sz, ex, ey, ez, 0, 0) per hit for the fused render kernel (rtxnerf_ray_march_csr_seg)
+        self.segments8 = torch.empty((capacity, 8), dtype=torch.float32, device=dev) if want_segments else None
         ws = _lib.load().rtxnerf_ray_march_workspace_bytes(n_rays)
         self.workspace = torch.empty(ws, dtype=torch.uint8, device=dev)
 
-    def c_struct(self):
+    def c_struct(self, points=True):
         return _lib.Hits(_p(self.num_hits), _p(self.indices), _p(self.view_dirs), _p(self.ray_origins),
-                         _p(self.t_start), _p(self.t_end), _p(self.start_points), _p(self.end_points),
-                         _p(self.hit_cells), _p(self.total_hits), self.capacity)
+                         _p(self.t_start), _p(self.t_end), _p(self.start_points) if points else None,
+                         _p(self.end_points) if points else None, _p(self.hit_cells), _p(self.total_hits),
+                         self.capacity)
 
 
 def ray_march_csr(grid, look_at_dev, focal_length, aspect_ratio, width, height, hits, max_hits, ray_begin=0,
-                  n_rays=None, stream=None):
+                  n_rays=None, stream=None, points=True):
     """Ray-grid intersection straight to CSR: replaces optixLaunch + D2H + thrust reduce/scan +
-    host gather (main.cu:506-543,631-676).  Asynchronous."""
+    host gather (main.cu:506-543,631-676).  Asynchronous.  With HitBuffers(want_segments=True) the packed 32-byte
+    hit records are written too (ray_march_csr_seg); points=False then leaves start_points / end_points out."""
     _chk_dev(look_at_dev, torch.float32, "look_at")
     if n_rays is None:
         n_rays = width * height - ray_begin
     if n_rays > hits.n_rays:
         raise ValueError("HitBuffers too small for %d rays" % n_rays)
     cam = _lib.Camera(_p(look_at_dev), float(focal_length), float(aspect_ratio), int(width), int(height))
-    st = hits.c_struct()
+    has_seg = getattr(hits, "segments8", None) is not None
+    st = hits.c_struct(points=points or not has_seg)
     need = _lib.load().rtxnerf_ray_march_workspace_bytes_for(int(n_rays), int(max_hits))
     if hits.workspace.numel() < need:      # first march with a cap above 32: room for the staged single pass
         hits.workspace = torch.empty(need, dtype=torch.uint8, device=hits.workspace.device)
-    _lib.check(_lib.load().rtxnerf_ray_march_csr(grid._h, C.byref(cam), int(ray_begin), int(n_rays), int(max_hits),
-                                                 C.byref(st), _p(hits.workspace), hits.workspace.numel(),
-                                                 _stream_ptr(stream)), "ray_march_csr")
+    if has_seg:
+        _lib.check(_lib.load().rtxnerf_ray_march_csr_seg(grid._h, C.byref(cam), int(ray_begin), int(n_rays),
+                                                         int(max_hits), C.byref(st), _p(hits.segments8),
+                                                         _p(hits.workspace), hits.workspace.numel(),
+                                                         _stream_ptr(stream)), "ray_march_csr_seg")
+    else:
+        _lib.check(_lib.load().rtxnerf_ray_march_csr(grid._h, C.byref(cam), int(ray_begin), int(n_rays), int(max_hits),
+                                                     C.byref(st), _p(hits.workspace), hits.workspace.numel(),
+                                                     _stream_ptr(stream)), "ray_march_csr")
     _lib.count_launches(3 if n_rays > 0 else 0)
 
 
@@ -587,6 +599,15 @@ class Network:
                                                          _p(end_points), _p(num_hits), _p(indices), int(n_rays),
                                                          int(samples_per_segment), int(sample_type), _p(pixels),
                                                          _stream_ptr(stream)), "render_rays_fused")
+        return pixels
+
+    def render_rays_fused_seg(self, stream, segments8, num_hits, indices, n_rays, samples_per_segment, pixels,
+                              sample_type=0):
+        """render_rays_fused over the packed hit records of ray_march_csr_seg ([capacity][8] floats)."""
+        _lib.check(_lib.load().rtxnerf_render_rays_fused_seg(C.byref(self._hg), C.byref(self._mlp), _p(segments8),
+                                                             _p(num_hits), _p(indices), int(n_rays),
+                                                             int(samples_per_segment), int(sample_type), _p(pixels),
+                                                             _stream_ptr(stream)), "render_rays_fused_seg")
         return pixels
 
     def backward_rays(self, stream, samples, encoded, dl_dradiance, num_hits, indices, n_rays,

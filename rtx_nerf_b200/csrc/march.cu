@@ -565,18 +565,30 @@ struct FillOut {
     float* end_points;
     int* hit_cells;
     long long capacity;
+    float* seg8;      // optional [capacity][8]: (sx, sy, sz, ex | ey, ez, 0, 0), one 32-byte sector per hit
 };
+
+__device__ __forceinline__ void store_seg8(float* seg8, long long slot, float sx, float sy, float sz, float ex, float ey,
+                                           float ez)
+{
+    float4* p = reinterpret_cast<float4*>(seg8) + 2 * slot;
+    p[0] = make_float4(sx, sy, sz, ex);
+    p[1] = make_float4(ey, ez, 0.0f, 0.0f);
+}
 
 __device__ __forceinline__ void store_hit(const FillOut& o, long long slot, const HitRecord& h)
 {
     if (slot >= o.capacity) return;
     if (o.t_start) o.t_start[slot] = h.t_start;
     if (o.t_end) o.t_end[slot] = h.t_end;
-    float* s = o.start_points + 3 * slot;
-    s[0] = h.sx; s[1] = h.sy; s[2] = h.sz;
-    float* e = o.end_points + 3 * slot;
-    e[0] = h.ex; e[1] = h.ey; e[2] = h.ez;
+    if (o.start_points) {      // (null with the packed records alone: rtxnerf_ray_march_csr_seg)
+        float* s = o.start_points + 3 * slot;
+        s[0] = h.sx; s[1] = h.sy; s[2] = h.sz;
+        float* e = o.end_points + 3 * slot;
+        e[0] = h.ex; e[1] = h.ey; e[2] = h.ez;
+    }
     if (o.hit_cells) o.hit_cells[slot] = h.cell;
+    if (o.seg8) store_seg8(o.seg8, slot, h.sx, h.sy, h.sz, h.ex, h.ey, h.ez);
 }
 
 // Pass 3: block-local scan of the counts + block offset = CSR index; march again and store.
@@ -797,19 +809,24 @@ march_onepass_kernel(GridBits bits, int G, CamArgs cam, long long ray_begin, lon
             float px = o0x, py = o0y, pz = o0z;                  // the origin this hit was launched from
             if (j > 0) { px = __uint_as_float(w[-4]); py = __uint_as_float(w[-3]); pz = __uint_as_float(w[-2]); }
             const float* d = dirs + 3 * lo;
-            pts[3 * tid] = rn_fma(ts, d[0], px);                 // optixPrograms.cu:194-196
-            pts[3 * tid + 1] = rn_fma(ts, d[1], py);
-            pts[3 * tid + 2] = rn_fma(ts, d[2], pz);
-            pts[3 * MARCH_BLOCK + 3 * tid] = ex;
-            pts[3 * MARCH_BLOCK + 3 * tid + 1] = ey;
-            pts[3 * MARCH_BLOCK + 3 * tid + 2] = ez;
+            const float sx = rn_fma(ts, d[0], px), sy = rn_fma(ts, d[1], py), sz = rn_fma(ts, d[2], pz);   // optixPrograms.cu:194-196
+            if (out.start_points) {
+                pts[3 * tid] = sx;
+                pts[3 * tid + 1] = sy;
+                pts[3 * tid + 2] = sz;
+                pts[3 * MARCH_BLOCK + 3 * tid] = ex;
+                pts[3 * MARCH_BLOCK + 3 * tid + 1] = ey;
+                pts[3 * MARCH_BLOCK + 3 * tid + 2] = ez;
+            }
             const long long slot = base + k;
             if (slot < out.capacity) {
                 if (out.t_start) out.t_start[slot] = ts;
                 if (out.t_end) out.t_end[slot] = te;
                 if (out.hit_cells) out.hit_cells[slot] = (int)w[5];
+                if (out.seg8) store_seg8(out.seg8, slot, sx, sy, sz, ex, ey, ez);
             }
         }
+        if (!out.start_points) continue;                        // packed records only: nothing to transpose
         __syncthreads();
         const int words = 3 * min(MARCH_BLOCK, block_total - k0);
         const long long w0 = 3 * (base + k0);
@@ -999,14 +1016,37 @@ extern "C" size_t rtxnerf_ray_march_workspace_bytes_for(long long n_rays, int ma
     return march_base_workspace(n_rays) + staged_slab_bytes(nb, max_hits);
 }
 
+static int march_csr_impl(const rtxnerf_grid* grid, const rtxnerf_camera* cam, long long ray_begin, long long n_rays,
+                          int max_hits, const rtxnerf_hits* hits, float* seg8, void* workspace, size_t workspace_bytes,
+                          void* stream);
+
 extern "C" int rtxnerf_ray_march_csr(const rtxnerf_grid* grid, const rtxnerf_camera* cam, long long ray_begin,
                                      long long n_rays, int max_hits, const rtxnerf_hits* hits, void* workspace,
                                      size_t workspace_bytes, void* stream)
 {
+    return march_csr_impl(grid, cam, ray_begin, n_rays, max_hits, hits, nullptr, workspace, workspace_bytes, stream);
+}
+
+// The same march that ALSO writes every hit's entry and exit point as one 32-byte record
+// d_segments8[slot] = (sx, sy, sz, ex, ey, ez, 0, 0) (32-byte aligned): what rtxnerf_render_rays_fused_seg reads with
+// two 16-byte loads per sample instead of six 4-byte loads at a hit-list stride between lanes.
+extern "C" int rtxnerf_ray_march_csr_seg(const rtxnerf_grid* grid, const rtxnerf_camera* cam, long long ray_begin,
+                                         long long n_rays, int max_hits, const rtxnerf_hits* hits, float* d_segments8,
+                                         void* workspace, size_t workspace_bytes, void* stream)
+{
+    if (!d_segments8 || ((uintptr_t)d_segments8 & 31u)) return RTXNERF_EINVAL;
+    return march_csr_impl(grid, cam, ray_begin, n_rays, max_hits, hits, d_segments8, workspace, workspace_bytes, stream);
+}
+
+static int march_csr_impl(const rtxnerf_grid* grid, const rtxnerf_camera* cam, long long ray_begin, long long n_rays,
+                          int max_hits, const rtxnerf_hits* hits, float* seg8, void* workspace, size_t workspace_bytes,
+                          void* stream)
+{
     if (!grid || !cam || !hits || !workspace || !cam->look_at) return RTXNERF_EINVAL;
-    if (!hits->num_hits || !hits->indices || !hits->view_dirs || !hits->start_points || !hits->end_points ||
-        !hits->total_hits)
-        return RTXNERF_EINVAL;
+    if (!hits->num_hits || !hits->indices || !hits->view_dirs || !hits->total_hits) return RTXNERF_EINVAL;
+    // the two point arrays go together; they may be left out when the packed records are written
+    if ((hits->start_points == nullptr) != (hits->end_points == nullptr)) return RTXNERF_EINVAL;
+    if (!hits->start_points && !seg8) return RTXNERF_EINVAL;
     if (n_rays < 0 || ray_begin < 0 || max_hits < 1 || cam->width == 0 || cam->height == 0) return RTXNERF_EINVAL;
     if (ray_begin + n_rays > (long long)cam->width * cam->height) return RTXNERF_EINVAL;
     if (workspace_bytes < rtxnerf_ray_march_workspace_bytes(n_rays)) return RTXNERF_ECAPACITY;
@@ -1020,7 +1060,7 @@ extern "C" int rtxnerf_ray_march_csr(const rtxnerf_grid* grid, const rtxnerf_cam
     long long* block_offsets = reinterpret_cast<long long*>(workspace);
     int* block_sums = reinterpret_cast<int*>(block_offsets + nb);
     CamArgs c{cam->look_at, cam->focal_length, cam->aspect_ratio, cam->width, cam->height};
-    FillOut fo{hits->t_start, hits->t_end, hits->start_points, hits->end_points, hits->hit_cells, hits->capacity};
+    FillOut fo{hits->t_start, hits->t_end, hits->start_points, hits->end_points, hits->hit_cells, hits->capacity, seg8};
     // development knobs, read once per process: RTXNERF_MARCH_TWO_PASS=1 forces count -> scan -> fill,
     // RTXNERF_MARCH_FLAT=0/1 picks the loop shape (default 2: flat loop for the staged path only);
     // _ENTER_EVERY / _ENTER_MIN tune the flat loop's relaunch batching (a __constant__ per device)

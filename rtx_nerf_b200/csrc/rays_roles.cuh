@@ -67,6 +67,7 @@ struct RrArgs {
     int groups_per_cta;   // consecutive 32-ray groups one CTA walks
     int wait_ticks;   // > 0: mbarrier waits carry this suspend-time hint (development knob)
     int mlp_last;     // 1: the MLP group is the LAST four warps of the CTA (development knob, see rr_launch)
+    const float4* seg8;   // render mode, optional: packed (sx,sy,sz,ex | ey,ez,0,0) per hit instead of the two arrays
 };
 
 __device__ __forceinline__ void rr_wait(uint64_t* bar, uint32_t parity, int ticks)
@@ -215,13 +216,23 @@ rays_roles_kernel(LeanLevels ll, Levels lv, const uint32_t* __restrict__ table32
                         // sample position, sampler.cu:45-59
                         const int j = pow2 ? (q >> log2s) : (q / S);
                         const int i = q - j * S;
-                        const float* sp = a.start_points + 3 * (first + j);
-                        const float* ep = a.end_points + 3 * (first + j);
-                        const float sx = __ldg(sp), sy = __ldg(sp + 1), sz = __ldg(sp + 2);
+                        float sx, sy, sz, ex, ey, ez;
+                        if (a.seg8) {
+                            // one 32-byte sector per lane, two requests: the lanes' hit lists are ~200 bytes apart, so
+                            // each of the six scalar loads below costs the L1 a lookup of 32 different sectors
+                            const float4 s0 = __ldg(a.seg8 + 2 * (first + j));
+                            const float4 s1 = __ldg(a.seg8 + 2 * (first + j) + 1);
+                            sx = s0.x; sy = s0.y; sz = s0.z; ex = s0.w; ey = s1.x; ez = s1.y;
+                        } else {
+                            const float* sp = a.start_points + 3 * (first + j);
+                            const float* ep = a.end_points + 3 * (first + j);
+                            sx = __ldg(sp); sy = __ldg(sp + 1); sz = __ldg(sp + 2);
+                            ex = __ldg(ep); ey = __ldg(ep + 1); ez = __ldg(ep + 2);
+                        }
                         const float tt = rr_steps(inv_s, i, pow2);
-                        x01 = unit_coord(rn_fma(tt, rn_sub(__ldg(ep), sx), sx));
-                        y01 = unit_coord(rn_fma(tt, rn_sub(__ldg(ep + 1), sy), sy));
-                        z01 = unit_coord(rn_fma(tt, rn_sub(__ldg(ep + 2), sz), sz));
+                        x01 = unit_coord(rn_fma(tt, rn_sub(ex, sx), sx));
+                        y01 = unit_coord(rn_fma(tt, rn_sub(ey, sy), sy));
+                        z01 = unit_coord(rn_fma(tt, rn_sub(ez, sz), sz));
                     } else {
                         s = first * S + q;
                         const float* p = a.samples + s * a.stride;

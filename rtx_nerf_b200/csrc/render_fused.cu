@@ -92,3 +92,31 @@ extern "C" int rtxnerf_render_rays_fused(const rtxnerf_hashgrid* enc, const rtxn
     a.out_activation = mlp->out_activation;
     return rr_launch(true, enc, mlp, lv, a, (cudaStream_t)stream);
 }
+
+// rtxnerf_render_rays_fused reading the hits as the packed 32-byte records rtxnerf_ray_march_csr_seg writes
+// (d_segments8[slot] = sx, sy, sz, ex, ey, ez, 0, 0): same samples, same pixels.
+extern "C" int rtxnerf_render_rays_fused_seg(const rtxnerf_hashgrid* enc, const rtxnerf_mlp* mlp,
+                                             const float* d_segments8, const int* d_num_hits, const int* d_indices,
+                                             int n_rays, int samples_per_segment, int sample_type, float* d_pixels,
+                                             void* stream)
+{
+    if (!enc || !mlp || !mlp->weights || !d_segments8 || !d_num_hits || !d_indices || !d_pixels) return RTXNERF_EINVAL;
+    if (((uintptr_t)d_segments8 & 31u) || n_rays < 0 || samples_per_segment < 1) return RTXNERF_EINVAL;
+    if (sample_type != 0) return RTXNERF_ECONFIG;
+    if (mlp->in_dim != NET_IN || mlp->width != NET_W || mlp->n_hidden != 2) return RTXNERF_ECONFIG;
+    if (mlp->out_activation != 0 && mlp->out_activation != 1) return RTXNERF_ECONFIG;
+    Levels lv;
+    int rc = levels_from(enc, &lv);
+    if (rc) return rc;
+    if (enc->n_levels * 2 > NET_IN) return RTXNERF_ECONFIG;
+    if (n_rays == 0) return RTXNERF_OK;
+    RrArgs a = {};
+    a.seg8 = reinterpret_cast<const float4*>(d_segments8);
+    a.pixels = d_pixels;
+    a.num_hits = d_num_hits;
+    a.indices = d_indices;
+    a.n_rays = n_rays;
+    a.S = samples_per_segment;
+    a.out_activation = mlp->out_activation;
+    return rr_launch(true, enc, mlp, lv, a, (cudaStream_t)stream);
+}

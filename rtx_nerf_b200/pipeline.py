@@ -26,8 +26,9 @@ class ViewRenderer:
         self.cap = int(capacity_hits if capacity_hits is not None else self.R * self.max_hits)
         self.radiance_stage = radiance
         dev = torch.device(device)
+        fusable = isinstance(radiance, NetworkRadiance) and radiance.fusable
         self.hits = api.HitBuffers(self.R, self.cap, device=dev, want_t=keep_t, want_cells=radiance.needs_cells,
-                                   want_origins=False)
+                                   want_origins=False, want_segments=fusable)
         N = self.cap * self.S
         self.N_cap = N
         self._dev = dev
@@ -64,6 +65,12 @@ class ViewRenderer:
         api.ray_march_csr(self.grid, self.pose_dev, self.focal, self.aspect, self.W, self.H, self.hits,
                           self.max_hits, ray_begin=self.ray_begin, n_rays=self.R)
 
+    def stage_march_fused(self):
+        """The march of the fused render path: packed hit records only (no start / end point arrays)."""
+        api.ray_march_csr(self.grid, self.pose_dev, self.focal, self.aspect, self.W, self.H, self.hits,
+                          self.max_hits, ray_begin=self.ray_begin, n_rays=self.R,
+                          points=self.hits.segments8 is None)
+
     def stage_sampler(self):
         h = self.hits
         api.launchSampler(h.start_points, h.end_points, h.view_dirs, self.t_vals, self.samples, self.R,
@@ -80,6 +87,10 @@ class ViewRenderer:
     def stage_fused(self):
         """Sampler + network + compositing in one kernel (render path with a NetworkRadiance)."""
         h = self.hits
+        if h.segments8 is not None:
+            self.radiance_stage.net.render_rays_fused_seg(None, h.segments8, h.num_hits, h.indices, self.R, self.S,
+                                                          self.pixels)
+            return
         self.radiance_stage.net.render_rays_fused(None, h.start_points, h.end_points, h.num_hits, h.indices,
                                                   self.R, self.S, self.pixels)
 
@@ -91,7 +102,7 @@ class ViewRenderer:
         """[(name, callable)] of one view: the fused render path when available (or asked for)."""
         fused = self.can_fuse if fused is None else fused
         if fused:
-            return [("march", self.stage_march), ("sample+network+composite", self.stage_fused)]
+            return [("march", self.stage_march_fused), ("sample+network+composite", self.stage_fused)]
         return [("march", self.stage_march), ("sampler", self.stage_sampler), ("network", self.stage_radiance),
                 ("composite", self.stage_composite)]
 

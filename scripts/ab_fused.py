@@ -51,7 +51,8 @@ def main():
         r.render_host(pose)
     N = r.total_hits() * a.S
     print("%s R=%d samples=%d" % (a.tag, r.R, N))
-    for name, fn in (("march", r.stage_march), ("fused", r.stage_fused), ("sampler", r.stage_sampler),
+    for name, fn in (("march(records)", r.stage_march_fused), ("march", r.stage_march), ("fused", r.stage_fused),
+                     ("sampler", r.stage_sampler),
                      ("network(staged)", r.stage_radiance), ("composite", r.stage_composite)):
         med, best = timeit(fn)
         print("%-18s median %.3f ms  best %.3f ms   %.2f Gsamples/s" % (name, med, best, N / med / 1e6))

@@ -431,3 +431,37 @@ def test_reference_cuda_kernels_agree(cuda_api, orc):
     gr = _volrender_bwd_gpu(cuda_api, lg, rad, t, nh, idx, S)
     assert np.array_equal(gr.view(np.uint16), g_ref.cpu().numpy().view(np.uint16)), \
         "new backward != reference backward kernel (bit-exact expected: same op sequence)"
+
+
+@pytest.mark.parametrize("max_hits", [16, 48])
+def test_packed_hit_records_equal_the_point_arrays(cuda_api, max_hits):
+    """rtxnerf_ray_march_csr_seg writes (sx, sy, sz, ex, ey, ez, 0, 0) per hit beside — or instead of — the two
+    [capacity][3] arrays: same bits, one-pass (<= 32 hits) and staged paths, and nothing else changes."""
+    import torch
+    api = cuda_api
+    G, W, H = 64, 96, 64
+    grid = api.OccupancyGrid.from_occupancy(synth.occupancy_lego(G, seed=2), G)
+    pose = _t(synth.poses(1, seed=12)[0].reshape(-1))
+    focal = synth.focal_length()
+    R = W * H
+    ref = api.HitBuffers(R, R * max_hits)
+    api.ray_march_csr(grid, pose, focal, W / H, W, H, ref, max_hits)
+    both = api.HitBuffers(R, R * max_hits, want_segments=True)
+    api.ray_march_csr(grid, pose, focal, W / H, W, H, both, max_hits)
+    only = api.HitBuffers(R, R * max_hits, want_segments=True)
+    only.start_points.fill_(-5.0)
+    only.end_points.fill_(-5.0)
+    api.ray_march_csr(grid, pose, focal, W / H, W, H, only, max_hits, points=False)
+    torch.cuda.synchronize()
+    n = int(ref.total_hits.item())
+    assert n > 1000 and int(both.total_hits.item()) == n and int(only.total_hits.item()) == n
+    sp, ep = ref.start_points[:n].cpu().numpy(), ref.end_points[:n].cpu().numpy()
+    for hb in (both, only):
+        seg = hb.segments8[:n].cpu().numpy()
+        assert np.array_equal(seg[:, 0:3], sp) and np.array_equal(seg[:, 3:6], ep) and not seg[:, 6:].any()
+        for k in ("num_hits", "indices", "t_start", "t_end", "hit_cells"):
+            assert torch.equal(getattr(hb, k)[:n] if k in ("t_start", "t_end", "hit_cells") else getattr(hb, k),
+                               getattr(ref, k)[:n] if k in ("t_start", "t_end", "hit_cells") else getattr(ref, k)), k
+    assert torch.equal(both.start_points[:n], ref.start_points[:n]) and torch.equal(both.end_points[:n], ref.end_points[:n])
+    assert float(only.start_points.max()) == -5.0 and float(only.end_points.max()) == -5.0     # left alone
+    grid.destroy()
