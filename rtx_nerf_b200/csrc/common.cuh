@@ -88,6 +88,22 @@ __device__ __forceinline__ float rn_mul(float a, float b) { return __fmul_rn(a, 
 __device__ __forceinline__ float rn_div(float a, float b) { return __fdiv_rn(a, b); }
 __device__ __forceinline__ float rn_fma(float a, float b, float c) { return __fmaf_rn(a, b, c); }
 
+// 256-bit global accesses (sm_100: LDG.E.256 / STG.E.256), 32-byte aligned addresses.  When the lanes of a warp
+// read records that lie far apart, what a load costs the L1 is one tag lookup per lane and per instruction,
+// whatever its width: a 32-byte record is one instruction instead of two (or of eight scalar ones).
+__device__ __forceinline__ void ldg_v8(const void* p, uint32_t (&r)[8])
+{
+    asm volatile("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+                 : "l"(p));
+}
+__device__ __forceinline__ void stg_v8(void* p, const uint32_t (&r)[8])
+{
+    asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(r[0]), "r"(r[1]), "r"(r[2]),
+                 "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])
+                 : "memory");
+}
+
 // streaming (read-once / write-once) global accesses: keep them out of L1
 __device__ __forceinline__ float4 ld_stream_f4(const float4* p)
 {

@@ -642,11 +642,15 @@ hashgrid_backward_kernel(Levels lv, const float* __restrict__ samples, int strid
                 x01 = unit_coord(ld_stream_f1(p));
                 y01 = unit_coord(ld_stream_f1(p + 1));
                 z01 = unit_coord(ld_stream_f1(p + 2));
-                const uint4* ge = reinterpret_cast<const uint4*>(d_encoded + s * NET_IN);
+                // the 64-byte row in two 256-bit loads (the lanes' rows lie a ray apart: one tag lookup per lane and
+                // instruction, whatever the width)
+                const uint16_t* ge = d_encoded + s * NET_IN;
 #pragma unroll
-                for (int c = 0; c < NET_IN / 8; c++) {
-                    const uint4 e = ld_stream_u4(ge + c);
-                    my[4 * c] = e.x; my[4 * c + 1] = e.y; my[4 * c + 2] = e.z; my[4 * c + 3] = e.w;
+                for (int c = 0; c < 2; c++) {
+                    uint32_t e[8];
+                    ldg_v8(ge + 16 * c, e);
+#pragma unroll
+                    for (int i = 0; i < 8; i++) my[8 * c + i] = e[i];
                 }
             }
 #pragma unroll 1
@@ -895,6 +899,7 @@ extern "C" int rtxnerf_hashgrid_backward_rays(const rtxnerf_hashgrid* enc, const
 {
     if (!enc || !d_samples || !d_dencoded || !d_num_hits || !d_indices || !d_grad_table) return RTXNERF_EINVAL;
     if (n_rays < 0 || samples_per_segment < 1 || sample_stride < 3) return RTXNERF_EINVAL;
+    if ((uintptr_t)d_dencoded & 31u) return RTXNERF_EINVAL;         // 64-byte rows read with 256-bit loads
     Levels lv;
     int rc = levels_from(enc, &lv);
     if (rc) return rc;

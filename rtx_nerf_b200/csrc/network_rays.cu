@@ -343,6 +343,7 @@ extern "C" int rtxnerf_network_forward_rays(const rtxnerf_hashgrid* enc, const r
     if (!enc || !mlp || !mlp->weights || !d_samples || !d_num_hits || !d_indices || (!d_out16 && !d_radiance4))
         return RTXNERF_EINVAL;
     if (n_rays < 0 || samples_per_segment < 1 || sample_stride < 3) return RTXNERF_EINVAL;
+    if ((uintptr_t)d_encoded_out & 31u) return RTXNERF_EINVAL;      // 64-byte rows written with 256-bit stores
     if (mlp->in_dim != NET_IN || mlp->width != NET_W || mlp->n_hidden != 2) return RTXNERF_ECONFIG;
     if (mlp->out_activation != 0 && mlp->out_activation != 1) return RTXNERF_ECONFIG;
     Levels lv;

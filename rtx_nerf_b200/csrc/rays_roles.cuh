@@ -218,11 +218,12 @@ rays_roles_kernel(LeanLevels ll, Levels lv, const uint32_t* __restrict__ table32
                         const int i = q - j * S;
                         float sx, sy, sz, ex, ey, ez;
                         if (a.seg8) {
-                            // one 32-byte sector per lane, two requests: the lanes' hit lists are ~200 bytes apart, so
+                            // one 32-byte sector per lane in ONE request: the lanes' hit lists are ~200 bytes apart, so
                             // each of the six scalar loads below costs the L1 a lookup of 32 different sectors
-                            const float4 s0 = __ldg(a.seg8 + 2 * (first + j));
-                            const float4 s1 = __ldg(a.seg8 + 2 * (first + j) + 1);
-                            sx = s0.x; sy = s0.y; sz = s0.z; ex = s0.w; ey = s1.x; ez = s1.y;
+                            uint32_t rec[8];
+                            ldg_v8(a.seg8 + 2 * (first + j), rec);
+                            sx = __uint_as_float(rec[0]); sy = __uint_as_float(rec[1]); sz = __uint_as_float(rec[2]);
+                            ex = __uint_as_float(rec[3]); ey = __uint_as_float(rec[4]); ez = __uint_as_float(rec[5]);
                         } else {
                             const float* sp = a.start_points + 3 * (first + j);
                             const float* ep = a.end_points + 3 * (first + j);
@@ -406,9 +407,11 @@ rays_roles_kernel(LeanLevels ll, Levels lv, const uint32_t* __restrict__ table32
                     tc::tmem_ld_wait();
                     const int q = 4 * t + wk;
                     if (q < ns) {
-                        uint4* o = reinterpret_cast<uint4*>(a.encoded_out + (first * S + q) * NET_IN);
-#pragma unroll
-                        for (int c = 0; c < 4; c++) o[c] = make_uint4(f[4 * c], f[4 * c + 1], f[4 * c + 2], f[4 * c + 3]);
+                        uint16_t* o = a.encoded_out + (first * S + q) * NET_IN;        // 64-byte rows
+                        const uint32_t lo[8] = {f[0], f[1], f[2], f[3], f[4], f[5], f[6], f[7]};
+                        const uint32_t hi[8] = {f[8], f[9], f[10], f[11], f[12], f[13], f[14], f[15]};
+                        stg_v8(o, lo);
+                        stg_v8(o + 16, hi);
                     }
                 }
                 rr_wait(mma_bar, phase, a.wait_ticks);
