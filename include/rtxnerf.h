@@ -309,6 +309,16 @@ int rtxnerf_network_forward_rays(const rtxnerf_hashgrid* enc, const rtxnerf_mlp*
                                  uint16_t* d_out16, float* d_radiance4, uint16_t* d_encoded_out,
                                  void* stream);
 
+/* The same forward without a sample buffer: sample (j,i) of ray x is rebuilt from the packed hit records of
+ * rtxnerf_ray_march_csr_seg / rtxnerf_batch_assemble_seg with the sampler's own arithmetic
+ * (sampler/sampler.cu:45-59, REGULAR sampling); row order and results as rtxnerf_launch_sampler followed by
+ * rtxnerf_network_forward_rays.  A training step that uses this and rtxnerf_hashgrid_backward_seg launches no
+ * sampler and keeps no [N][5] sample buffer (main.cu:704-721). */
+int rtxnerf_network_forward_seg(const rtxnerf_hashgrid* enc, const rtxnerf_mlp* mlp,
+                                const float* d_segments8, const int* d_num_hits, const int* d_indices,
+                                int n_rays, int samples_per_segment, uint16_t* d_out16,
+                                float* d_radiance4, uint16_t* d_encoded_out, void* stream);
+
 /* ------------------------------------------------------------------------------------
  * The reference's literal network (main.cu:47-68): Composite[Frequency(xyz, 10 frequencies) +
  * Frequency(theta/phi, tiny-cuda-nn's default 12)] padded with ones to 112 inputs ->
@@ -394,6 +404,11 @@ int rtxnerf_mlp_backward(const rtxnerf_mlp* mlp, const uint16_t* d_encoded, cons
 int rtxnerf_hashgrid_backward_rays(const rtxnerf_hashgrid* enc, const float* d_samples, int sample_stride,
                                    const uint16_t* d_dencoded, const int* d_num_hits, const int* d_indices,
                                    int n_rays, int samples_per_segment, float* d_grad_table, void* stream);
+/* rtxnerf_hashgrid_backward_rays with the positions rebuilt from the packed hit records (REGULAR sampling)
+ * instead of read from the sample buffer: the backward half of rtxnerf_network_forward_seg (main.cu:781). */
+int rtxnerf_hashgrid_backward_seg(const rtxnerf_hashgrid* enc, const float* d_segments8,
+                                  const uint16_t* d_dencoded, const int* d_num_hits, const int* d_indices,
+                                  int n_rays, int samples_per_segment, float* d_grad_table, void* stream);
 
 /* values[i] = (pred-target)^2 / n (optional), gradients[i] = fp16(loss_scale * 2 (pred-target) / n),
  * *d_loss_sum += sum(values) (optional, caller-zeroed).  n = batch_size * 3. */
@@ -454,6 +469,13 @@ int rtxnerf_batch_assemble(const rtxnerf_ray_store* store, unsigned long long se
                            long long first, long long batch_rays, const rtxnerf_hits* batch,
                            float* d_gt_pixels, long long* d_ray_ids, void* workspace,
                            size_t workspace_bytes, void* stream);
+/* rtxnerf_batch_assemble that also writes the batch's hits as the packed 32-byte records of
+ * rtxnerf_ray_march_csr_seg (d_segments8 [batch->capacity][8], 32-byte aligned); batch->start_points and
+ * batch->end_points may both be NULL (records only). */
+int rtxnerf_batch_assemble_seg(const rtxnerf_ray_store* store, unsigned long long seed, int group,
+                               long long first, long long batch_rays, const rtxnerf_hits* batch,
+                               float* d_segments8, float* d_gt_pixels, long long* d_ray_ids,
+                               void* workspace, size_t workspace_bytes, void* stream);
 
 #ifdef __cplusplus
 }

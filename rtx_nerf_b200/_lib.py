@@ -134,6 +134,12 @@ SIGNATURES = {
     "rtxnerf_batch_workspace_bytes": (c_size_t, [c_ll]),
     "rtxnerf_batch_assemble": (c_int, [C.POINTER(RayStore), C.c_ulonglong, c_int, c_ll, c_ll, C.POINTER(Hits),
                                        c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "rtxnerf_batch_assemble_seg": (c_int, [C.POINTER(RayStore), C.c_ulonglong, c_int, c_ll, c_ll, C.POINTER(Hits),
+                                           c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "rtxnerf_network_forward_seg": (c_int, [C.POINTER(HashGrid), C.POINTER(Mlp), c_void_p, c_void_p, c_void_p,
+                                            c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "rtxnerf_hashgrid_backward_seg": (c_int, [C.POINTER(HashGrid), c_void_p, c_void_p, c_void_p, c_void_p,
+                                              c_int, c_int, c_void_p, c_void_p]),
 }
 
 _lib = None

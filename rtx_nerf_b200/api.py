@@ -410,7 +410,7 @@ def ray_permutation(n, seed, group=1, first=0, count=None, out=None, stream=None
 
 
 def batch_assemble(store, seed, group, first, batch_rays, hits, gt_pixels=None, ray_ids=None, workspace=None,
-                   stream=None):
+                   stream=None, points=True):
     """One training batch from the ray store: replaces main.cu:621-676 (host slice + collect +
     H2D + thrust reduce/scan + host gather + H2D).  `hits` is a HitBuffers that receives the batch
     CSR (num_hits, indices, view_dirs, start/end points, t's, total_hits).  Asynchronous."""
@@ -424,10 +424,18 @@ def batch_assemble(store, seed, group, first, batch_rays, hits, gt_pixels=None, 
         workspace = hits.workspace
         if workspace.numel() < need:
             workspace = hits.workspace = torch.empty(need, dtype=torch.uint8, device=hits.num_hits.device)
-    st, hs = store.c_struct(), hits.c_struct()
-    _lib.check(lib.rtxnerf_batch_assemble(C.byref(st), int(seed), int(group), int(first), int(batch_rays),
-                                          C.byref(hs), _p(gt_pixels), _p(ray_ids), _p(workspace), workspace.numel(),
-                                          _stream_ptr(stream)), "batch_assemble")
+    st = store.c_struct()
+    if getattr(hits, "segments8", None) is not None:      # packed records too (or alone: points=False)
+        hs = hits.c_struct(points=points)
+        _lib.check(lib.rtxnerf_batch_assemble_seg(C.byref(st), int(seed), int(group), int(first), int(batch_rays),
+                                                  C.byref(hs), _p(hits.segments8), _p(gt_pixels), _p(ray_ids),
+                                                  _p(workspace), workspace.numel(), _stream_ptr(stream)),
+                   "batch_assemble_seg")
+    else:
+        hs = hits.c_struct()
+        _lib.check(lib.rtxnerf_batch_assemble(C.byref(st), int(seed), int(group), int(first), int(batch_rays),
+                                              C.byref(hs), _p(gt_pixels), _p(ray_ids), _p(workspace), workspace.numel(),
+                                              _stream_ptr(stream)), "batch_assemble")
     _lib.count_launches(3 if batch_rays > 0 else 0)
 
 
@@ -635,8 +643,30 @@ def _network_stage_methods():
             C.byref(self._hg), _p(samples), samples.shape[1], _p(dencoded), _p(num_hits), _p(indices), int(n_rays),
             int(samples_per_segment), _p(grad_table), _stream_ptr(stream)), "hashgrid_backward_rays")
 
+    def forward_seg(self, stream, segments8, num_hits, indices, n_rays, samples_per_segment, output=None,
+                    radiance=None, encoded_out=None):
+        """forward_rays without a sample buffer: positions rebuilt from the packed hit records ([capacity][8]) by the
+        sampler's arithmetic (REGULAR sampling); same rows, same results."""
+        if output is None and radiance is None:
+            raise ValueError("forward_seg needs an output and/or radiance buffer")
+        _lib.check(_lib.load().rtxnerf_network_forward_seg(
+            C.byref(self._hg), C.byref(self._mlp), _p(segments8), _p(num_hits), _p(indices), int(n_rays),
+            int(samples_per_segment), _p(output), _p(radiance), _p(encoded_out), _stream_ptr(stream)),
+            "network_forward_seg")
+        _lib.count_launches(1 if n_rays > 0 else 0)
+        return output if output is not None else radiance
+
+    def hashgrid_backward_seg(self, stream, segments8, dencoded, num_hits, indices, n_rays, samples_per_segment,
+                              grad_table):
+        """hashgrid_backward_rays with the positions rebuilt from the packed hit records."""
+        _lib.check(_lib.load().rtxnerf_hashgrid_backward_seg(
+            C.byref(self._hg), _p(segments8), _p(dencoded), _p(num_hits), _p(indices), int(n_rays),
+            int(samples_per_segment), _p(grad_table), _stream_ptr(stream)), "hashgrid_backward_seg")
+
     Network.mlp_backward = mlp_backward
     Network.hashgrid_backward_rays = hashgrid_backward_rays
+    Network.forward_seg = forward_seg
+    Network.hashgrid_backward_seg = hashgrid_backward_seg
 
 
 _network_stage_methods()

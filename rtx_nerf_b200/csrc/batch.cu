@@ -177,7 +177,8 @@ __global__ void __launch_bounds__(BATCH_BLOCK)
 batch_gather_kernel(rtxnerf_ray_store st, long long n_batch, const int* __restrict__ num_hits,
                     const long long* __restrict__ src_base, const long long* __restrict__ block_offsets,
                     int* __restrict__ indices, float* __restrict__ t_start, float* __restrict__ t_end,
-                    float* __restrict__ start_points, float* __restrict__ end_points, long long capacity)
+                    float* __restrict__ start_points, float* __restrict__ end_points, float* __restrict__ seg8,
+                    long long capacity)
 {
     __shared__ int excl[BATCH_BLOCK + 1];      // block-local exclusive scan of the hit counts
     __shared__ long long sbase[BATCH_BLOCK];
@@ -212,10 +213,17 @@ batch_gather_kernel(rtxnerf_ray_store st, long long n_batch, const int* __restri
         const float* sp = st.start_points + 3 * src;
         const float* ep = st.end_points + 3 * src;
         float a0 = sp[0], a1 = sp[1], a2 = sp[2], b0 = ep[0], b1 = ep[1], b2 = ep[2];
-        float* dp = start_points + 3 * dst;
-        float* dq = end_points + 3 * dst;
-        dp[0] = a0; dp[1] = a1; dp[2] = a2;
-        dq[0] = b0; dq[1] = b1; dq[2] = b2;
+        if (start_points) {
+            float* dp = start_points + 3 * dst;
+            float* dq = end_points + 3 * dst;
+            dp[0] = a0; dp[1] = a1; dp[2] = a2;
+            dq[0] = b0; dq[1] = b1; dq[2] = b2;
+        }
+        if (seg8) {      // packed 32-byte record (march.cu: store_seg8)
+            float4* r = reinterpret_cast<float4*>(seg8) + 2 * dst;
+            r[0] = make_float4(a0, a1, a2, b0);
+            r[1] = make_float4(b1, b2, 0.0f, 0.0f);
+        }
         if (t_start && st.t_start) t_start[dst] = st.t_start[src];
         if (t_end && st.t_end) t_end[dst] = st.t_end[src];
     }
@@ -244,15 +252,41 @@ extern "C" int rtxnerf_ray_permutation(long long n, unsigned long long seed, int
     return rtx_launch_status();
 }
 
+static int batch_assemble_impl(const rtxnerf_ray_store* store, unsigned long long seed, int group, long long first,
+                               long long batch_rays, const rtxnerf_hits* batch, float* seg8, float* d_gt_pixels,
+                               long long* d_ray_ids, void* workspace, size_t workspace_bytes, void* stream);
+
 extern "C" int rtxnerf_batch_assemble(const rtxnerf_ray_store* store, unsigned long long seed, int group,
                                       long long first, long long batch_rays, const rtxnerf_hits* batch,
                                       float* d_gt_pixels, long long* d_ray_ids, void* workspace,
                                       size_t workspace_bytes, void* stream)
 {
+    return batch_assemble_impl(store, seed, group, first, batch_rays, batch, nullptr, d_gt_pixels, d_ray_ids, workspace,
+                               workspace_bytes, stream);
+}
+
+// rtxnerf_batch_assemble that also (or, with batch->start_points == batch->end_points == NULL, only) writes the
+// batch's hits as the packed 32-byte records of rtxnerf_ray_march_csr_seg.
+extern "C" int rtxnerf_batch_assemble_seg(const rtxnerf_ray_store* store, unsigned long long seed, int group,
+                                          long long first, long long batch_rays, const rtxnerf_hits* batch,
+                                          float* d_segments8, float* d_gt_pixels, long long* d_ray_ids,
+                                          void* workspace, size_t workspace_bytes, void* stream)
+{
+    if (!d_segments8 || ((uintptr_t)d_segments8 & 31u)) return RTXNERF_EINVAL;
+    return batch_assemble_impl(store, seed, group, first, batch_rays, batch, d_segments8, d_gt_pixels, d_ray_ids,
+                               workspace, workspace_bytes, stream);
+}
+
+static int batch_assemble_impl(const rtxnerf_ray_store* store, unsigned long long seed, int group, long long first,
+                               long long batch_rays, const rtxnerf_hits* batch, float* seg8, float* d_gt_pixels,
+                               long long* d_ray_ids, void* workspace, size_t workspace_bytes, void* stream)
+{
     if (!store || !batch || !store->num_hits || !store->indices || !store->view_base || !store->view_dirs ||
         !store->start_points || !store->end_points || !batch->num_hits || !batch->indices || !batch->view_dirs ||
-        !batch->start_points || !batch->end_points || !batch->total_hits)
+        !batch->total_hits)
         return RTXNERF_EINVAL;
+    if ((batch->start_points == nullptr) != (batch->end_points == nullptr)) return RTXNERF_EINVAL;
+    if (!batch->start_points && !seg8) return RTXNERF_EINVAL;
     if (store->n_rays <= 0 || store->rays_per_view <= 0 || store->n_rays % store->rays_per_view != 0 ||
         group <= 0 || store->n_rays % group != 0 || first < 0 || batch_rays < 0 ||
         first + batch_rays > store->n_rays || batch_rays > 0x7fffffffLL * (long long)BATCH_BLOCK)
@@ -278,7 +312,7 @@ extern "C" int rtxnerf_batch_assemble(const rtxnerf_ray_store* store, unsigned l
     batch_scan_kernel<<<1, 1024, 0, s>>>(block_sums, (int)nb, block_offsets, batch->total_hits);
     batch_gather_kernel<<<(unsigned)nb, BATCH_BLOCK, 0, s>>>(*store, batch_rays, batch->num_hits, src_base,
                                                              block_offsets, batch->indices, batch->t_start,
-                                                             batch->t_end, batch->start_points, batch->end_points,
+                                                             batch->t_end, batch->start_points, batch->end_points, seg8,
                                                              batch->capacity);
     return rtx_launch_status(3);
 }

@@ -611,10 +611,14 @@ mlp_backward2_kernel(const uint16_t* __restrict__ weights, const uint16_t* __res
 #define HB_MIN_BLOCKS 4
 #endif
 __global__ void __launch_bounds__(HB_WARPS * 32, HB_MIN_BLOCKS)
-hashgrid_backward_kernel(Levels lv, const float* __restrict__ samples, int stride,
+hashgrid_backward_kernel(Levels lv, const float* __restrict__ samples, int stride, const float* __restrict__ seg8,
                          const uint16_t* __restrict__ d_encoded, const int* __restrict__ num_hits,
                          const int* __restrict__ indices, int n_rays, int S, float* __restrict__ grad_table)
 {
+    // samples == null: positions are rebuilt from the packed hit records with the sampler's arithmetic
+    const float inv_s = 1.0f / (float)S;
+    const bool pow2 = (S & (S - 1)) == 0;
+    const int log2s = 31 - __clz(S);
     const unsigned FULL = 0xffffffffu;
     __shared__ uint32_t stage[HB_WARPS * 32][NET_IN / 2 + 1];   // +1: conflict-free per-thread rows
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -638,10 +642,25 @@ hashgrid_backward_kernel(Levels lv, const float* __restrict__ samples, int strid
             // level loop is rolled; a 4-byte load per level would cost 32 L1TEX wavefronts each)
             uint32_t* my = stage[threadIdx.x];
             if (valid) {
-                const float* p = samples + s * stride;
-                x01 = unit_coord(ld_stream_f1(p));
-                y01 = unit_coord(ld_stream_f1(p + 1));
-                z01 = unit_coord(ld_stream_f1(p + 2));
+                if (samples) {
+                    const float* p = samples + s * stride;
+                    x01 = unit_coord(ld_stream_f1(p));
+                    y01 = unit_coord(ld_stream_f1(p + 1));
+                    z01 = unit_coord(ld_stream_f1(p + 2));
+                } else {                                     // sampler.cu:45-59, REGULAR
+                    const int j = pow2 ? (q >> log2s) : (q / S);
+                    const int i = q - j * S;
+                    uint32_t rec[8];
+                    ldg_v8(seg8 + 8 * (base / S + j), rec);  // base = indices[ray] * S
+                    const float sx = __uint_as_float(rec[0]), sy = __uint_as_float(rec[1]), sz = __uint_as_float(rec[2]);
+                    float tt = 0.0f;
+                    if (pow2) tt = rn_mul((float)i, inv_s);
+                    else
+                        for (int k = 0; k < i; k++) tt = rn_add(tt, inv_s);
+                    x01 = unit_coord(rn_fma(tt, rn_sub(__uint_as_float(rec[3]), sx), sx));
+                    y01 = unit_coord(rn_fma(tt, rn_sub(__uint_as_float(rec[4]), sy), sy));
+                    z01 = unit_coord(rn_fma(tt, rn_sub(__uint_as_float(rec[5]), sz), sz));
+                }
                 // the 64-byte row in two 256-bit loads (the lanes' rows lie a ray apart: one tag lookup per lane and
                 // instruction, whatever the width)
                 const uint16_t* ge = d_encoded + s * NET_IN;
@@ -913,7 +932,29 @@ extern "C" int rtxnerf_hashgrid_backward_rays(const rtxnerf_hashgrid* enc, const
 #endif
     const long long max_blocks = (long long)RTX_NUM_SMS * HB_BLOCKS_PER_SM;
     hashgrid_backward_kernel<<<(unsigned)(groups < max_blocks ? groups : max_blocks), HB_WARPS * 32, 0,
-                               (cudaStream_t)stream>>>(lv, d_samples, sample_stride, d_dencoded, d_num_hits, d_indices,
+                               (cudaStream_t)stream>>>(lv, d_samples, sample_stride, nullptr, d_dencoded, d_num_hits,
+                                                       d_indices, n_rays, samples_per_segment, d_grad_table);
+    return rtx_launch_status();
+}
+
+// The scatter with the sample positions rebuilt from the packed hit records (REGULAR sampling) instead of read
+// from a sample buffer: the backward half of rtxnerf_network_forward_seg.
+extern "C" int rtxnerf_hashgrid_backward_seg(const rtxnerf_hashgrid* enc, const float* d_segments8,
+                                             const uint16_t* d_dencoded, const int* d_num_hits, const int* d_indices,
+                                             int n_rays, int samples_per_segment, float* d_grad_table, void* stream)
+{
+    if (!enc || !d_segments8 || !d_dencoded || !d_num_hits || !d_indices || !d_grad_table) return RTXNERF_EINVAL;
+    if (n_rays < 0 || samples_per_segment < 1) return RTXNERF_EINVAL;
+    if (((uintptr_t)d_segments8 & 31u) || ((uintptr_t)d_dencoded & 31u)) return RTXNERF_EINVAL;
+    Levels lv;
+    int rc = levels_from(enc, &lv);
+    if (rc) return rc;
+    if (enc->n_levels * 2 > NET_IN) return RTXNERF_ECONFIG;
+    if (n_rays == 0) return RTXNERF_OK;
+    const long long groups = ((long long)n_rays + 31) / 32;
+    const long long max_blocks = (long long)RTX_NUM_SMS * HB_BLOCKS_PER_SM;
+    hashgrid_backward_kernel<<<(unsigned)(groups < max_blocks ? groups : max_blocks), HB_WARPS * 32, 0,
+                               (cudaStream_t)stream>>>(lv, nullptr, 0, d_segments8, d_dencoded, d_num_hits, d_indices,
                                                        n_rays, samples_per_segment, d_grad_table);
     return rtx_launch_status();
 }

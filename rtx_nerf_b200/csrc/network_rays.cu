@@ -410,3 +410,37 @@ extern "C" int rtxnerf_network_forward_rays(const rtxnerf_hashgrid* enc, const r
         mlp->out_activation, d_num_hits, d_indices, n_rays, samples_per_segment, d_out16, d_radiance4, d_encoded_out);
     return rtx_launch_status();
 }
+
+// The same forward without a sample buffer: sample (j,i) of ray x is rebuilt from the packed hit records of
+// rtxnerf_ray_march_csr_seg / rtxnerf_batch_assemble_seg with the sampler's own arithmetic (sampler.cu:45-59,
+// REGULAR sampling) — one 256-bit load per sample instead of three scalar loads from rows that lie a ray apart,
+// and a training step needs no sampler launch.  Row order and results are those of rtxnerf_launch_sampler +
+// rtxnerf_network_forward_rays.
+extern "C" int rtxnerf_network_forward_seg(const rtxnerf_hashgrid* enc, const rtxnerf_mlp* mlp,
+                                           const float* d_segments8, const int* d_num_hits, const int* d_indices,
+                                           int n_rays, int samples_per_segment, uint16_t* d_out16,
+                                           float* d_radiance4, uint16_t* d_encoded_out, void* stream)
+{
+    if (!enc || !mlp || !mlp->weights || !d_segments8 || !d_num_hits || !d_indices || (!d_out16 && !d_radiance4))
+        return RTXNERF_EINVAL;
+    if (n_rays < 0 || samples_per_segment < 1) return RTXNERF_EINVAL;
+    if (((uintptr_t)d_segments8 & 31u) || ((uintptr_t)d_encoded_out & 31u)) return RTXNERF_EINVAL;
+    if (mlp->in_dim != NET_IN || mlp->width != NET_W || mlp->n_hidden != 2) return RTXNERF_ECONFIG;
+    if (mlp->out_activation != 0 && mlp->out_activation != 1) return RTXNERF_ECONFIG;
+    Levels lv;
+    int rc = levels_from(enc, &lv);
+    if (rc) return rc;
+    if (enc->n_levels * 2 > NET_IN) return RTXNERF_ECONFIG;
+    if (n_rays == 0) return RTXNERF_OK;
+    RrArgs a = {};
+    a.seg8 = reinterpret_cast<const float4*>(d_segments8);
+    a.out16 = d_out16;
+    a.radiance4 = d_radiance4;
+    a.encoded_out = d_encoded_out;
+    a.num_hits = d_num_hits;
+    a.indices = d_indices;
+    a.n_rays = n_rays;
+    a.S = samples_per_segment;
+    a.out_activation = mlp->out_activation;
+    return rr_launch(false, enc, mlp, lv, a, (cudaStream_t)stream);
+}

@@ -67,7 +67,7 @@ struct RrArgs {
     int groups_per_cta;   // consecutive 32-ray groups one CTA walks
     int wait_ticks;   // > 0: mbarrier waits carry this suspend-time hint (development knob)
     int mlp_last;     // 1: the MLP group is the LAST four warps of the CTA (development knob, see rr_launch)
-    const float4* seg8;   // render mode, optional: packed (sx,sy,sz,ex | ey,ez,0,0) per hit instead of the two arrays
+    const float4* seg8;   // optional: packed (sx,sy,sz,ex | ey,ez,0,0) per hit instead of the two arrays / the samples
 };
 
 __device__ __forceinline__ void rr_wait(uint64_t* bar, uint32_t parity, int ticks)
@@ -212,7 +212,7 @@ rays_roles_kernel(LeanLevels ll, Levels lv, const uint32_t* __restrict__ table32
                 float x01 = 0.f, y01 = 0.f, z01 = 0.f;
                 long long s = 0;
                 if (valid) {
-                    if (RENDER) {
+                    if (RENDER || !a.samples) {     // (staged mode without a sample buffer: the training forward)
                         // sample position, sampler.cu:45-59
                         const int j = pow2 ? (q >> log2s) : (q / S);
                         const int i = q - j * S;

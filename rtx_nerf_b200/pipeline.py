@@ -17,7 +17,8 @@ class ViewRenderer:
     """Renders views of W x H rays (or a contiguous ray range of them: the multi-GPU shard)."""
 
     def __init__(self, grid, width, height, focal_length, aspect_ratio, samples_per_segment, max_hits,
-                 radiance, n_rays=None, ray_begin=0, capacity_hits=None, device="cuda", keep_t=False):
+                 radiance, n_rays=None, ray_begin=0, capacity_hits=None, device="cuda", keep_t=False,
+                 want_segments=None):
         self.grid, self.W, self.H = grid, width, height
         self.focal, self.aspect = float(focal_length), float(aspect_ratio)
         self.S, self.max_hits = int(samples_per_segment), int(max_hits)
@@ -28,7 +29,8 @@ class ViewRenderer:
         dev = torch.device(device)
         fusable = isinstance(radiance, NetworkRadiance) and radiance.fusable
         self.hits = api.HitBuffers(self.R, self.cap, device=dev, want_t=keep_t, want_cells=radiance.needs_cells,
-                                   want_origins=False, want_segments=fusable)
+                                   want_origins=False,
+                                   want_segments=fusable if want_segments is None else bool(want_segments))
         N = self.cap * self.S
         self.N_cap = N
         self._dev = dev
@@ -81,7 +83,8 @@ class ViewRenderer:
 
     def stage_composite(self):
         h = self.hits
-        api.launch_volrender_cuda(self.samples, self.radiance, h.num_hits, h.indices, self.t_vals, self.R, self.S,
+        # (network_inputs is unused, as in the reference: pass the sample buffer only if one exists)
+        api.launch_volrender_cuda(self._samples, self.radiance, h.num_hits, h.indices, self.t_vals, self.R, self.S,
                                   self.pixels)
 
     def stage_fused(self):
@@ -237,9 +240,14 @@ class Trainer:
         # the reference's literal network (Frequency + 8 x 128, main.cu:47-68) trains through the same step: its
         # backward recomputes the forward per tile, so no features are kept, and it has no encoding parameters
         self.literal = isinstance(network, api.FrequencyNetwork)
+        # hash-grid network, REGULAR sampling: forward and scatter rebuild the sample positions from the packed hit
+        # records (one 256-bit load per sample), so the step launches no sampler and touches no [N][5] sample
+        # buffer; the t-values the compositing reads depend only on a sample's index inside its segment and are
+        # written once.  from_hits = False puts the sampler back into the step.
+        self.from_hits = not self.literal
         stage = FrequencyNetworkRadiance(network) if self.literal else _EncodedNetworkRadiance(self)
         self.view = ViewRenderer(grid, width, height, focal_length, aspect_ratio, samples_per_segment, max_hits,
-                                 stage, n_rays=n_rays, ray_begin=0, device=device)
+                                 stage, n_rays=n_rays, ray_begin=0, device=device, want_segments=self.from_hits)
         v = self.view
         dev = torch.device(device)
         N = v.N_cap
@@ -258,11 +266,26 @@ class Trainer:
         self.m1 = torch.zeros(n_params, dtype=torch.float32, device=dev)
         self.m2 = torch.zeros(n_params, dtype=torch.float32, device=dev)
         self.step_count = 0
+        if self.from_hits:
+            # sampler.cu:54-66 (REGULAR): t_vals of sample i of a segment = (i steps of 1/S) + 1/S in fp32
+            inv_s = np.float32(1.0) / np.float32(self.S)
+            tv, t = np.empty(self.S, np.float32), np.float32(0.0)
+            for i in range(self.S):
+                t = np.float32(t + inv_s)
+                tv[i] = t
+            v.t_vals.copy_(torch.from_numpy(np.tile(tv, v.cap)).to(dev))
+
+    def _sample(self):
+        if not self.from_hits:
+            self.view.stage_sampler()
 
     def forward(self):
         v = self.view
-        v.stage_march()
-        v.stage_sampler()
+        if self.from_hits:
+            v.stage_march_fused()      # packed hit records only
+        else:
+            v.stage_march()
+        self._sample()
         v.stage_radiance()
         v.stage_composite()
 
@@ -280,9 +303,9 @@ class Trainer:
             self._reduced = False
             return
         if self.world == 1 or not self.overlap:
-            self.net.backward_rays(None, v.samples, self.encoded, self.radiance_grad, h.num_hits, h.indices, self.R,
-                                   self.S, h.total_hits, v.N_cap, self.dencoded, self.grads[:self.n_table],
-                                   self.grads[self.n_table:])
+            self.net.mlp_backward(None, self.encoded, self.radiance_grad, self.S, h.total_hits, v.N_cap, self.dencoded,
+                                  self.grads[self.n_table:])
+            self._scatter()
             self._reduced = False
             return
         main = torch.cuda.current_stream()
@@ -295,14 +318,22 @@ class Trainer:
         self._side.wait_event(ev)
         with torch.cuda.stream(self._side):
             parallel.allreduce_sum_(self.grads[self.n_table:], self.pg)
-        self.net.hashgrid_backward_rays(None, v.samples, self.dencoded, h.num_hits, h.indices, self.R, self.S,
-                                        self.grads[:self.n_table])
+        self._scatter()
         ev2 = torch.cuda.Event()
         ev2.record(main)
         self._side.wait_event(ev2)
         with torch.cuda.stream(self._side):
             parallel.allreduce_sum_(self.grads[:self.n_table], self.pg)
         self._reduced = True
+
+    def _scatter(self):
+        v, h = self.view, self.view.hits
+        if self.from_hits:
+            self.net.hashgrid_backward_seg(None, h.segments8, self.dencoded, h.num_hits, h.indices, self.R, self.S,
+                                           self.grads[:self.n_table])
+        else:
+            self.net.hashgrid_backward_rays(None, v.samples, self.dencoded, h.num_hits, h.indices, self.R, self.S,
+                                            self.grads[:self.n_table])
 
     def allreduce(self):
         if self.world > 1:
@@ -336,8 +367,9 @@ class Trainer:
         (the reference's own batching, main.cu:612-676: shuffled rays of ALL views, not a range of
         one view).  batch_assemble takes the place of the march: three launches, no host work."""
         v = self.view
-        api.batch_assemble(store, seed, group, first, self.R, v.hits, gt_pixels=self.target)
-        v.stage_sampler()
+        api.batch_assemble(store, seed, group, first, self.R, v.hits, gt_pixels=self.target,
+                           points=not self.from_hits)
+        self._sample()
         v.stage_radiance()
         v.stage_composite()
         self.backward()
@@ -346,7 +378,8 @@ class Trainer:
 
     @property
     def launches_per_step(self):
-        return self.view.launches_per_view + 1 + 1 + 2 + 1   # + loss, compositing bwd, network bwd (2), Adam
+        # + loss, compositing bwd, network bwd (2), Adam; no sampler launch when positions come from the hit records
+        return self.view.launches_per_view + 1 + 1 + 2 + 1 - (1 if self.from_hits else 0)
 
 
 class _EncodedNetworkRadiance:
@@ -358,5 +391,10 @@ class _EncodedNetworkRadiance:
         self.t = trainer
 
     def __call__(self, r):
+        if self.t.from_hits:
+            h = r.hits
+            self.t.net.forward_seg(None, h.segments8, h.num_hits, h.indices, r.R, r.S, radiance=r.radiance,
+                                   encoded_out=self.t.encoded)
+            return
         self.t.net.forward_rays(None, r.samples, r.hits.num_hits, r.hits.indices, r.R, r.S, radiance=r.radiance,
                                 encoded_out=self.t.encoded)

@@ -30,10 +30,11 @@ def main():
     v, h = tr.view, tr.view.hits
 
     def net_bwd():
-        tr.net.backward_rays(None, v.samples, tr.encoded, tr.radiance_grad, h.num_hits, h.indices, tr.R, tr.S,
-                             h.total_hits, v.N_cap, tr.dencoded, tr.grads[:tr.n_table], tr.grads[tr.n_table:])
+        tr.net.mlp_backward(None, tr.encoded, tr.radiance_grad, tr.S, h.total_hits, v.N_cap, tr.dencoded,
+                            tr.grads[tr.n_table:])
+        tr._scatter()
 
-    fns = [v.stage_march, v.stage_sampler, v.stage_radiance, v.stage_composite,
+    fns = [v.stage_march_fused if tr.from_hits else v.stage_march, tr._sample, v.stage_radiance, v.stage_composite,
            lambda: api.l2_loss(v.pixels, tr.target, tr.loss_scale, tr.loss_grad, loss_sum=tr.loss_sum),
            lambda: api.launch_volrender_backward_cuda(None, tr.loss_grad, v.radiance, v.t_vals, h.num_hits, h.indices,
                                                       tr.R, tr.S, tr.radiance_grad),

@@ -204,6 +204,7 @@ def test_store_fed_forward_equals_the_per_view_forward(cuda_api):
     store.add_view(grid, pose, synth.focal_length(), 1.0, W, H, HM)
     assert api.ray_permutation(W * H, 5, W * H).cpu().tolist() == list(range(W * H))
     tr = pipeline.Trainer(grid, net, W, H, synth.focal_length(), 1.0, S, HM, R)
+    tr.from_hits = False        # this test compares the sample buffers too: keep the sampler in the step
     v = tr.view
     v.pose_dev.copy_(pose.reshape(16))
     v.ray_begin = first

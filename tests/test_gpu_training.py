@@ -257,3 +257,51 @@ def test_positions_outside_the_cube_are_clamped_forward_and_backward(cuda_api, o
     gt_o = orc.hashgrid_backward(lv, s, dencoded.cpu().numpy())
     np.testing.assert_allclose(gt.cpu().numpy(), gt_o, rtol=0, atol=1e-4 * np.abs(gt_o).max())
     assert np.isfinite(rad.cpu().numpy()).all()
+
+
+@pytest.mark.parametrize("S", [4, 3])
+def test_forward_and_scatter_from_hit_records_equal_the_sample_buffer_path(cuda_api, S):
+    """rtxnerf_network_forward_seg / rtxnerf_hashgrid_backward_seg rebuild the sample positions from the packed hit
+    records with the sampler's arithmetic: features and radiance must equal the bits of launchSampler +
+    forward_rays, the scatter must equal hashgrid_backward_rays up to the order of its atomics (power-of-two and
+    other S take different t arithmetic)."""
+    import torch
+    api = cuda_api
+    net, lv, table, w = _net(api, seed=31, out_activation=1)
+    G, W, H, HM = 32, 48, 40, 12
+    occ = synth.occupancy_bernoulli(G, 0.2, seed=6)
+    grid = api.OccupancyGrid.from_occupancy(occ, G)
+    R = W * H
+    hb = api.HitBuffers(R, R * HM, want_segments=True)
+    pose = synth.poses(1, seed=8)[0]
+    api.ray_march_csr(grid, _t(pose.reshape(-1)), synth.focal_length(), W / H, W, H, hb, HM)
+    torch.cuda.synchronize()
+    n = int(hb.total_hits.item()) * S
+    assert n > 1000
+    N = R * HM * S
+    t_vals = torch.zeros(N, dtype=torch.float32, device="cuda")
+    samples = torch.zeros((N, 5), dtype=torch.float32, device="cuda")
+    api.launchSampler(hb.start_points, hb.end_points, hb.view_dirs, t_vals, samples, R, G, hb.num_hits, hb.indices,
+                      api.SAMPLING_REGULAR, None, S)
+    outs = []
+    for mode in ("rays", "records"):
+        enc = torch.zeros((N, 32), dtype=torch.float16, device="cuda")
+        rad = torch.zeros((N, 4), dtype=torch.float32, device="cuda")
+        if mode == "rays":
+            net.forward_rays(None, samples, hb.num_hits, hb.indices, R, S, radiance=rad, encoded_out=enc)
+        else:
+            net.forward_seg(None, hb.segments8, hb.num_hits, hb.indices, R, S, radiance=rad, encoded_out=enc)
+        torch.cuda.synchronize()
+        outs.append((enc[:n].cpu().numpy().view(np.uint16), rad[:n].cpu().numpy()))
+    assert np.array_equal(outs[0][0], outs[1][0]), "features from the records differ from features from the samples"
+    assert np.array_equal(outs[0][1], outs[1][1])
+    denc = (torch.randn((N, 32), device="cuda") * 0.01).to(torch.float16)
+    g_rays = torch.zeros((lv["n_entries"], 2), dtype=torch.float32, device="cuda")
+    g_rec = torch.zeros_like(g_rays)
+    net.hashgrid_backward_rays(None, samples, denc, hb.num_hits, hb.indices, R, S, g_rays)
+    net.hashgrid_backward_seg(None, hb.segments8, denc, hb.num_hits, hb.indices, R, S, g_rec)
+    torch.cuda.synchronize()
+    a, b = g_rays.cpu().numpy(), g_rec.cpu().numpy()
+    assert np.count_nonzero(a) > 0
+    np.testing.assert_allclose(b, a, rtol=0, atol=2e-5 * np.abs(a).max())
+    grid.destroy()
