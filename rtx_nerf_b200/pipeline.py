@@ -217,9 +217,10 @@ class FrequencyNetworkRadiance:
 
 class Trainer:
     """One data-parallel training step of the reference's loop (main.cu:612-805) on this rank's
-    rays: march -> sampler -> network forward (features kept) -> compositing -> L2 loss ->
+    rays: march -> [sampler] -> network forward (features kept) -> compositing -> L2 loss ->
     compositing backward -> network backward -> [all-reduce of the flat fp32 gradient buffer]
-    -> Adam.  Every buffer is allocated once; the step is 12 kernel launches plus the collective.
+    -> Adam.  Every buffer is allocated once; the step is 8 kernel launches plus the collective (9 with the
+    sampler: the hash-grid network rebuilds its sample positions from the march's packed hit records, from_hits).
 
     Rays of a step are a contiguous range of one view (ray_begin, n_rays); ranks take different
     views/ranges.  Weights stay replicated: every rank applies the same Adam step to the same
