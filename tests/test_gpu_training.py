@@ -305,3 +305,40 @@ def test_forward_and_scatter_from_hit_records_equal_the_sample_buffer_path(cuda_
     assert np.count_nonzero(a) > 0
     np.testing.assert_allclose(b, a, rtol=0, atol=2e-5 * np.abs(a).max())
     grid.destroy()
+
+
+@pytest.mark.parametrize("S", [3, 4, 5])
+def test_trainer_without_sampler_equals_trainer_with_sampler(cuda_api, S):
+    """Trainer.from_hits (no sampler launch: positions from the packed hit records, t_vals written once at
+    construction) against the same Trainer with the sampler in the step: identical t-values, radiance and pixels,
+    gradients equal up to the scatter's atomic order — power-of-two and other S."""
+    import torch
+    from rtx_nerf_b200 import pipeline
+    api = cuda_api
+    G, W, H, HM, R = 32, 40, 32, 8, 640
+    grid = api.OccupancyGrid.from_occupancy(synth.occupancy_bernoulli(G, 0.25, seed=17), G)
+    lv = synth.hashgrid_levels()
+    pose = _t(synth.poses(1, seed=19)[0].reshape(-1))
+    tgt = torch.rand((R, 3), device="cuda")
+    res = []
+    for from_hits in (True, False):
+        net = api.Network(lv, synth.hashgrid_table(lv, seed=3), synth.mlp_weights(seed=4))
+        tr = pipeline.Trainer(grid, net, W, H, synth.focal_length(), W / H, S, HM, R)
+        tr.from_hits = from_hits
+        v = tr.view
+        v.pose_dev.copy_(pose)
+        v.ray_begin = 100
+        tr.target.copy_(tgt)
+        tr.forward()
+        tr.backward()
+        torch.cuda.synchronize()
+        n = int(v.hits.total_hits.item()) * S
+        assert n > 500
+        res.append((v.t_vals[:n].clone(), v.radiance[:n].clone(), v.pixels.clone(), tr.grads.clone(),
+                    tr.encoded[:n].clone()))
+    a, b = res
+    assert torch.equal(a[0], b[0]), "t_vals written once differ from the sampler's"
+    assert torch.equal(a[4], b[4]) and torch.equal(a[1], b[1]) and torch.equal(a[2], b[2])
+    gmax = float(b[3].abs().max())
+    assert gmax > 0 and float((a[3] - b[3]).abs().max()) <= 2e-5 * gmax
+    grid.destroy()
